@@ -1,0 +1,115 @@
+/* b2ot — C ABI of the B200-native entropic Sinkhorn hot path (libb2ot.so).
+ *
+ * Drop-in boundary for PythonOT/POT's Sinkhorn path.  The reference has no FFI for this path (it
+ * is pure Python over the `nx` array backend, ot/backend.py:245-262), so the entry points below
+ * are what a binding of that path has to call; each one cites the reference lines it replaces
+ * (paths relative to the reference checkout).  Conventions:
+ *
+ *   - every pointer named *_dev / K / M / a / b / u / v / workspace is a DEVICE pointer owned by
+ *     the caller (the Python host allocates with torch); the library never allocates, frees or
+ *     retains them beyond the lifetime of the handle they were given to;
+ *   - matrices are row-major with an explicit leading dimension in ELEMENTS;
+ *   - dtype is B2OT_F32 or B2OT_F64; `stream` is a cudaStream_t passed as void*;
+ *   - work is enqueued on the caller's stream and is asynchronous unless stated otherwise;
+ *   - return value 0 = ok, < 0 = error (message in b2ot_last_error(), thread-local);
+ *   - solver status words: 0 running, 1 converged, 2 numerical guard fired, 3 max-iter.
+ *
+ * There is no CPU fallback anywhere in this library.
+ */
+#ifndef B2OT_H_
+#define B2OT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2OT_F32 0
+#define B2OT_F64 1
+
+#define B2OT_MODE_KNOPP 0 /* scaling domain, ot/bregman/_sinkhorn.py:487-687  */
+#define B2OT_MODE_LOG 1   /* log domain,     ot/bregman/_sinkhorn.py:690-918  */
+
+#define B2OT_STATUS_RUNNING 0
+#define B2OT_STATUS_CONVERGED 1
+#define B2OT_STATUS_NUMERR 2
+#define B2OT_STATUS_MAXITER 3
+
+/* sweep implementation selector for b2ot_dense_create (`variant`) */
+#define B2OT_VARIANT_AUTO 0    /* fused cluster sweep when the layout allows it, else split */
+#define B2OT_VARIANT_FUSED 1   /* one pass over K per iteration: TMA-bulk staged row tiles, cluster/DSMEM row reduce */
+#define B2OT_VARIANT_SPLIT 2   /* two passes (row kernel + column kernel); any shape / alignment */
+
+/* ---- library ---- */
+int b2ot_version(void);
+const char* b2ot_last_error(void);
+int b2ot_device_info(int device, int* sm_count, int* cc_major, int* cc_minor);
+/* number of kernels this library has launched in this process (bench.py's "gpu_launches") */
+unsigned long long b2ot_launch_count(void);
+
+/* ---- Gibbs kernel / scaled cost (once per solve) ----
+ * K = exp(M / (-reg))   replaces nx.exp(M / (-reg)),  ot/bregman/_sinkhorn.py:621
+ * Mr = -M / reg         replaces -M / reg,            ot/bregman/_sinkhorn.py:860
+ * In-place (K == M, ldK == ldM) is allowed. */
+int b2ot_kexp(const void* M, void* K, int64_t n, int64_t m, int64_t ldM, int64_t ldK, double reg, int dtype,
+              void* stream);
+int b2ot_negscale(const void* M, void* Mr, int64_t n, int64_t m, int64_t ldM, int64_t ldMr, double reg, int dtype,
+                  void* stream);
+
+/* ---- dense Sinkhorn solver (scaling and log domain) ----
+ * One handle = one solve on one device (or one row block of a row-sharded solve).
+ * Replaces the loops ot/bregman/_sinkhorn.py:626-670 (knopp) and :880-906 (log).
+ *
+ *   mode KNOPP: K = exp(-M/reg) (n x m), a (n), b (m); u, v are scalings.
+ *   mode LOG  : K = -M/reg      (n x m), a = log(a) (n), b (m), logb = log(b) (m); u, v are log-scalings.
+ *
+ * Row sharding: `n` is the number of LOCAL rows; b, v are replicated.  When an all-reduce hook is
+ * installed the per-iteration column sums (m+1 values of `dtype`, the last one carrying the
+ * numerical-guard flag) are summed across ranks through it, on `stream`, once per iteration.
+ */
+typedef struct b2ot_dense b2ot_dense;
+#define B2OT_OP_SUM 0
+#define B2OT_OP_MAX 1
+/* in-place all-reduce of `count` elements of `dtype` at buf_dev across the row-shard ranks, enqueued on `stream` */
+typedef int (*b2ot_allreduce_fn)(void* buf_dev, int64_t count, int dtype, int op, void* stream, void* ctx);
+
+size_t b2ot_dense_workspace_bytes(int64_t n, int64_t m, int dtype, int max_iter, int check_every);
+
+int b2ot_dense_create(b2ot_dense** handle, int mode, int dtype, int64_t n, int64_t m, int64_t ld, const void* K,
+                      const void* a, const void* b, const void* logb, void* workspace, size_t workspace_bytes,
+                      int max_iter, int check_every, double stop_thr, int variant, void* stream);
+int b2ot_dense_set_allreduce(b2ot_dense* handle, b2ot_allreduce_fn fn, void* ctx);
+/* enqueue: load the initial scalings (u0: n, v0: m; log-scalings in LOG mode) and run the
+ * column-only pass that seeds the first v update (:629 / :881 of the reference loop) */
+int b2ot_dense_init(b2ot_dense* handle, const void* u0, const void* v0);
+/* enqueue n_iters iterations (each: one sweep over K + one finalize); no host sync */
+int b2ot_dense_iterate(b2ot_dense* handle, int n_iters);
+/* synchronise the stream and read the device status word; also services the log-domain
+ * exact-column fallback when the device asked for it */
+int b2ot_dense_poll(b2ot_dense* handle, int* status, int* iter);
+/* init + iterate until status != running, polling every `poll_every` iterations (<= 0: only at the end) */
+int b2ot_dense_solve(b2ot_dense* handle, const void* u0, const void* v0, int poll_every, int* status, int* niter,
+                     int* n_err);
+/* copy the current scalings to u_out (n) / v_out (m) (device) and the error history to err_host (host doubles);
+ * synchronises the stream */
+int b2ot_dense_export(b2ot_dense* handle, void* u_out, void* v_out, double* err_host, int err_capacity, int* n_err);
+/* what the handle resolved to: variant, cluster size, clusters in the grid, pipeline stages, vectors per thread */
+int b2ot_dense_info(const b2ot_dense* handle, int* variant, int* cluster_size, int* n_clusters, int* stages,
+                    int* vecs_per_thread);
+int b2ot_dense_destroy(b2ot_dense* handle);
+
+/* plan: KNOPP out = u_i K_ij v_j (:685-687), LOG out = exp(K_ij + u_i + v_j) (:915-918) */
+int b2ot_dense_plan(int mode, int dtype, const void* K, const void* u, const void* v, void* out, int64_t n,
+                    int64_t m, int64_t ldK, int64_t ldOut, void* stream);
+/* loss <M, plan> without materialising the plan (ot/bregman/_sinkhorn.py:435-438); result: one double at
+ * loss_dev; scratch_dev >= b2ot_dense_loss_scratch_bytes(n, m) */
+size_t b2ot_dense_loss_scratch_bytes(int64_t n, int64_t m);
+int b2ot_dense_loss(int mode, int dtype, const void* K, const void* M, const void* u, const void* v, int64_t n,
+                    int64_t m, int64_t ldK, int64_t ldM, double* loss_dev, void* scratch_dev, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2OT_H_ */

@@ -1,0 +1,21 @@
+"""pot_b200 — B200-native entropic Sinkhorn hot path with PythonOT/POT's signatures.
+
+    import pot_b200 as ot
+    G = ot.sinkhorn(a, b, M, reg)                      # torch CUDA tensors in, torch CUDA tensors out
+    G = ot.bregman.sinkhorn_log(a, b, M, reg)
+    f, g = ot.bregman.empirical_sinkhorn(Xs, Xt, reg, isLazy=True)
+    res = ot.batch.solve_batch(M, reg)
+
+All arithmetic runs in libb2ot.so (hand-written sm_100a CUDA behind the C ABI of include/b2ot.h).
+Importing the package loads that library and fails if it has not been built; there is no CPU path.
+"""
+
+from . import _lib
+
+_lib.load()  # fail loudly when the CUDA library is missing
+
+from . import bregman  # noqa: E402
+from .bregman import sinkhorn, sinkhorn2, sinkhorn_knopp, sinkhorn_log  # noqa: E402
+
+__version__ = "0.1.0"
+__all__ = ["bregman", "sinkhorn", "sinkhorn2", "sinkhorn_knopp", "sinkhorn_log"]

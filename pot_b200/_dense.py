@@ -1,0 +1,175 @@
+"""Host-side wrapper of the dense Sinkhorn solver handle (b2ot_dense_* in include/b2ot.h).
+
+Torch is used for device memory, streams and (row-sharded runs) the all-reduce plumbing;
+every arithmetic step runs in libb2ot.so.
+"""
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+
+_DT = {torch.float32: _lib.F32, torch.float64: _lib.F64}
+
+
+def dtype_code(t):
+    try:
+        return _DT[t]
+    except KeyError:
+        raise TypeError(f"pot_b200 supports float32 and float64 tensors, got {t}") from None
+
+
+def stream_ptr(device):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def cost_transform(M, reg, op):
+    """K = exp(M/(-reg)) (op='kexp', _sinkhorn.py:621) or Mr = -M/reg (op='negscale', :860)."""
+    lib = _lib.load()
+    out = torch.empty((M.shape[0], M.shape[1]), dtype=M.dtype, device=M.device)
+    fn = lib.b2ot_kexp if op == "kexp" else lib.b2ot_negscale
+    with torch.cuda.device(M.device):
+        _lib.check(fn(M.data_ptr(), out.data_ptr(), M.shape[0], M.shape[1], M.stride(0), out.stride(0), float(reg),
+                      dtype_code(M.dtype), stream_ptr(M.device)), "cost transform")
+    return out
+
+
+class DenseSolver:
+    """One dense solve (or one row block of a row-sharded solve) on the current device.
+
+    K     : (n_local, m) device tensor, exp(-M/reg) for mode 'knopp', -M/reg for mode 'log' (unit column stride)
+    a     : (n_local,) a for 'knopp', log(a) for 'log'
+    b     : (m,)
+    logb  : (m,) log(b), 'log' mode only
+    group : torch.distributed process group of the row-shard ranks (None = single device)
+    """
+
+    def __init__(self, mode, K, a, b, logb=None, max_iter=1000, check_every=10, stop_thr=1e-9, variant="auto",
+                 group=None):
+        self.lib = _lib.load()
+        assert K.is_cuda and K.dim() == 2 and K.stride(1) == 1
+        self.mode = _lib.MODE_KNOPP if mode == "knopp" else _lib.MODE_LOG
+        self.K, self.a, self.b, self.logb = K, a, b, logb
+        self.n, self.m = K.shape
+        self.dtype = K.dtype
+        self.device = K.device
+        self.max_iter = int(max_iter)
+        self.group = group
+        code = dtype_code(K.dtype)
+        nbytes = self.lib.b2ot_dense_workspace_bytes(self.n, self.m, code, self.max_iter, int(check_every))
+        self.ws = torch.empty(nbytes, dtype=torch.uint8, device=K.device)
+        var = {"auto": _lib.VARIANT_AUTO, "fused": _lib.VARIANT_FUSED, "split": _lib.VARIANT_SPLIT}[variant]
+        h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.b2ot_dense_create(
+                C.byref(h), self.mode, code, self.n, self.m, K.stride(0), K.data_ptr(), a.data_ptr(), b.data_ptr(),
+                logb.data_ptr() if logb is not None else None, self.ws.data_ptr(), nbytes, self.max_iter,
+                int(check_every), float(stop_thr), var, stream_ptr(self.device)), "b2ot_dense_create")
+        self.h = h
+        self._cb = None
+        if group is not None:
+            self._install_allreduce(group)
+
+    # ---- row-sharded runs: the per-iteration column-sum exchange goes through torch.distributed ----
+    def _install_allreduce(self, group):
+        import torch.distributed as dist
+
+        ws, base = self.ws, self.ws.data_ptr()
+        esize = self.K.element_size()
+        dtype = self.dtype
+
+        def hook(buf, count, _dtype, op, _stream, _ctx):
+            try:
+                off = buf - base
+                t = ws[off:off + count * esize].view(dtype)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX if op == _lib.OP_MAX else dist.ReduceOp.SUM, group=group)
+                return 0
+            except Exception:  # surfaced as an error code through the C ABI
+                import traceback
+                traceback.print_exc()
+                return 1
+
+        self._cb = _lib.ALLREDUCE_FN(hook)
+        _lib.check(self.lib.b2ot_dense_set_allreduce(self.h, self._cb, None), "b2ot_dense_set_allreduce")
+
+    def info(self):
+        v = [C.c_int() for _ in range(5)]
+        _lib.check(self.lib.b2ot_dense_info(self.h, *[C.byref(x) for x in v]), "b2ot_dense_info")
+        names = ("variant", "cluster_size", "n_clusters", "stages", "vecs_per_thread")
+        out = dict(zip(names, (x.value for x in v)))
+        out["variant"] = {1: "fused", 2: "split"}.get(out["variant"], "?")
+        return out
+
+    def init(self, u0, v0):
+        self._u0, self._v0 = u0, v0  # keep alive until the async copies ran
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.b2ot_dense_init(self.h, u0.data_ptr(), v0.data_ptr()), "b2ot_dense_init")
+
+    def iterate(self, k):
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.b2ot_dense_iterate(self.h, int(k)), "b2ot_dense_iterate")
+
+    def poll(self):
+        st, it = C.c_int(), C.c_int()
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.b2ot_dense_poll(self.h, C.byref(st), C.byref(it)), "b2ot_dense_poll")
+        return st.value, it.value
+
+    def solve(self, u0, v0, poll_every=0):
+        """Run to completion.  Returns (status, niter, n_err)."""
+        self._u0, self._v0 = u0, v0
+        st, ni, ne = C.c_int(), C.c_int(), C.c_int()
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.b2ot_dense_solve(self.h, u0.data_ptr(), v0.data_ptr(), int(poll_every), C.byref(st),
+                                                 C.byref(ni), C.byref(ne)), "b2ot_dense_solve")
+        return st.value, ni.value, ne.value
+
+    def export(self):
+        """Returns (u, v, err_list_of_floats)."""
+        u = torch.empty(self.n, dtype=self.dtype, device=self.device)
+        v = torch.empty(self.m, dtype=self.dtype, device=self.device)
+        cap = self.max_iter + 2
+        errs = (C.c_double * cap)()
+        ne = C.c_int()
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.b2ot_dense_export(self.h, u.data_ptr(), v.data_ptr(), errs, cap, C.byref(ne)),
+                       "b2ot_dense_export")
+        return u, v, [errs[i] for i in range(ne.value)]
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.b2ot_dense_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def plan(mode, K, u, v):
+    """KNOPP: u_i K_ij v_j (_sinkhorn.py:685-687); LOG: exp(K_ij + u_i + v_j) (:915-918)."""
+    lib = _lib.load()
+    out = torch.empty_like(K, memory_format=torch.contiguous_format)
+    with torch.cuda.device(K.device):
+        _lib.check(lib.b2ot_dense_plan(_lib.MODE_KNOPP if mode == "knopp" else _lib.MODE_LOG, dtype_code(K.dtype),
+                                       K.data_ptr(), u.data_ptr(), v.data_ptr(), out.data_ptr(), K.shape[0],
+                                       K.shape[1], K.stride(0), out.stride(0), stream_ptr(K.device)),
+                   "b2ot_dense_plan")
+    return out
+
+
+def loss(mode, K, M, u, v):
+    """<M, plan> without materialising the plan (_sinkhorn.py:435-438).  Returns a 0-d float64 tensor."""
+    lib = _lib.load()
+    out = torch.empty((), dtype=torch.float64, device=K.device)
+    scratch = torch.empty(lib.b2ot_dense_loss_scratch_bytes(K.shape[0], K.shape[1]), dtype=torch.uint8,
+                          device=K.device)
+    with torch.cuda.device(K.device):
+        _lib.check(lib.b2ot_dense_loss(_lib.MODE_KNOPP if mode == "knopp" else _lib.MODE_LOG, dtype_code(K.dtype),
+                                       K.data_ptr(), M.data_ptr(), u.data_ptr(), v.data_ptr(), K.shape[0],
+                                       K.shape[1], K.stride(0), M.stride(0), out.data_ptr(), scratch.data_ptr(),
+                                       stream_ptr(K.device)), "b2ot_dense_loss")
+    return out

@@ -1,0 +1,82 @@
+"""ctypes binding of libb2ot.so (the C ABI declared in include/b2ot.h).
+
+The library is the only compute path of this package: if it is missing the import
+fails loudly (there is no CPU or PyTorch fallback).
+"""
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb2ot.so")
+
+F32, F64 = 0, 1
+MODE_KNOPP, MODE_LOG = 0, 1
+ST_RUNNING, ST_CONVERGED, ST_NUMERR, ST_MAXITER = 0, 1, 2, 3
+VARIANT_AUTO, VARIANT_FUSED, VARIANT_SPLIT = 0, 1, 2
+OP_SUM, OP_MAX = 0, 1
+
+ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_void_p)
+
+# name -> (restype, argtypes); every symbol include/b2ot.h declares
+PROTOTYPES = {
+    "b2ot_version": (C.c_int, []),
+    "b2ot_last_error": (C.c_char_p, []),
+    "b2ot_device_info": (C.c_int, [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "b2ot_launch_count": (C.c_ulonglong, []),
+    "b2ot_kexp": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_double, C.c_int,
+                            C.c_void_p]),
+    "b2ot_negscale": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_double,
+                                C.c_int, C.c_void_p]),
+    "b2ot_dense_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int]),
+    "b2ot_dense_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_int64,
+                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
+                                    C.c_int, C.c_int, C.c_double, C.c_int, C.c_void_p]),
+    "b2ot_dense_set_allreduce": (C.c_int, [C.c_void_p, ALLREDUCE_FN, C.c_void_p]),
+    "b2ot_dense_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b2ot_dense_iterate": (C.c_int, [C.c_void_p, C.c_int]),
+    "b2ot_dense_poll": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "b2ot_dense_solve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int),
+                                   C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "b2ot_dense_export": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double), C.c_int,
+                                    C.POINTER(C.c_int)]),
+    "b2ot_dense_info": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_int)] * 5),
+    "b2ot_dense_destroy": (C.c_int, [C.c_void_p]),
+    "b2ot_dense_plan": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                  C.c_int64, C.c_int64, C.c_int64, C.c_void_p]),
+    "b2ot_dense_loss_scratch_bytes": (C.c_size_t, [C.c_int64, C.c_int64]),
+    "b2ot_dense_loss": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                  C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+}
+
+_lib = None
+
+
+class B2otError(RuntimeError):
+    pass
+
+
+def load():
+    """Load libb2ot.so (once) and attach prototypes.  Raises if the library was not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: build the CUDA library first "
+            "(`python -c 'import __graft_entry__ as g; g.build()'` or `make -C pot_b200/csrc`). "
+            "pot_b200 has no CPU fallback."
+        )
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in PROTOTYPES.items():
+        fn = getattr(lib, name)  # AttributeError if the build is stale
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc, what=""):
+    if rc != 0:
+        msg = load().b2ot_last_error()
+        raise B2otError(f"{what} failed (code {rc}): {msg.decode() if msg else '?'}")

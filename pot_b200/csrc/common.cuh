@@ -1,0 +1,205 @@
+// Common device helpers for the b2ot kernels (sm_100a only).
+//
+// PTX wrappers for the Blackwell/Hopper async machinery used by the sweep
+// kernels: mbarrier (local + remote arrive), 1-D bulk async copies
+// (cp.async.bulk -> SASS UBLKCP, the TMA engine's linear mode), thread-block
+// cluster identity, DSMEM stores (mapa + st.shared::cluster) and warp reductions.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#include <stdint.h>
+
+namespace b2ot {
+
+// ----------------------------------------------------------------------------------------------
+// Solver state living in device memory: every kernel of a solve reads it first and turns into a
+// no-op once `status` leaves ST_RUNNING (sticky), so the host never has to sync per iteration.
+// ----------------------------------------------------------------------------------------------
+enum : int {
+  ST_RUNNING = 0,      // iterations are being applied
+  ST_CONVERGED = 1,    // err < stopThr at iteration `niter`
+  ST_NUMERR = 2,       // numerical guard fired at iteration `niter`; (u, v) reverted
+  ST_MAXITER = 3,      // loop exhausted
+  ST_PAUSE_EXACT = 4   // log domain: a column sum underflowed; host must run the exact column pass
+};
+
+struct __align__(16) SolveState {
+  int status;
+  int iter;        // index ii of the iteration the next sweep belongs to
+  int niter;       // reference's log["niter"] (last loop index)
+  int sel_u;       // slot of the current u in the 2-ring
+  int sel_v;       // slot of the current v in the 3-ring
+  int cur_flags;   // guard flags attached to the current (c, v): bit0 c==0, bit1 v nan/inf
+  int next_flags;  // accumulated by finalize blocks for the v being produced
+  int uflag;       // accumulated by the sweep: nan/inf in the u being produced
+  int need_exact;  // accumulated by finalize (log domain): column sum below the underflow guard
+  unsigned int ticket;
+  int n_err;       // entries written to err_hist
+  int pad0;
+  double last_err;
+  double pad1;
+};
+
+constexpr int FLAG_CZERO = 1;
+constexpr int FLAG_VBAD = 2;
+
+template <typename T> struct Vec;
+template <> struct Vec<float> { using type = float4; static constexpr int N = 4; };
+template <> struct Vec<double> { using type = double2; static constexpr int N = 2; };
+
+template <typename T> __device__ __forceinline__ T neg_inf();
+template <> __device__ __forceinline__ float neg_inf<float>() { return -CUDART_INF_F; }
+template <> __device__ __forceinline__ double neg_inf<double>() { return -CUDART_INF; }
+
+// Underflow guard for the row-frame column sums of the log-domain sweep.
+template <typename T> __device__ __forceinline__ T tiny_guard();
+template <> __device__ __forceinline__ float tiny_guard<float>() { return 1e-30f; }
+template <> __device__ __forceinline__ double tiny_guard<double>() { return 1e-290; }
+
+__device__ __forceinline__ float exp_t(float x) { return expf(x); }
+__device__ __forceinline__ double exp_t(double x) { return exp(x); }
+__device__ __forceinline__ float log_t(float x) { return logf(x); }
+__device__ __forceinline__ double log_t(double x) { return log(x); }
+__device__ __forceinline__ float max_t(float a, float b) { return fmaxf(a, b); }
+__device__ __forceinline__ double max_t(double a, double b) { return fmax(a, b); }
+__device__ __forceinline__ bool finite_t(float x) { return isfinite(x); }
+__device__ __forceinline__ bool finite_t(double x) { return isfinite(x); }
+
+// ---- element access on the 16-byte vector types ----
+__device__ __forceinline__ float& elem(float4& v, int i) { return (&v.x)[i]; }
+__device__ __forceinline__ double& elem(double2& v, int i) { return (&v.x)[i]; }
+__device__ __forceinline__ const float& elem(const float4& v, int i) { return (&v.x)[i]; }
+__device__ __forceinline__ const double& elem(const double2& v, int i) { return (&v.x)[i]; }
+__device__ __forceinline__ void fill(float4& v, float x) { v.x = v.y = v.z = v.w = x; }
+__device__ __forceinline__ void fill(double2& v, double x) { v.x = v.y = x; }
+
+// ---- warp reductions (butterfly: every lane ends with the result) ----
+template <typename T> __device__ __forceinline__ T warp_sum(T x) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+  return x;
+}
+template <typename T> __device__ __forceinline__ T warp_max(T x) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) x = max_t(x, __shfl_xor_sync(0xffffffffu, x, o));
+  return x;
+}
+
+// ---- shared-memory addresses ----
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+// ---- mbarrier ----
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+// acquire at cluster scope: pairs with the remote release-arrive of a peer CTA
+__device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait_cluster(bar, parity)) {
+  }
+}
+// arrive on the mbarrier of another CTA of the cluster (address from mapa)
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+
+// ---- cluster identity / barrier / DSMEM ----
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t cluster_nctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t cluster_id_x() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%clusterid.x;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t cluster_count_x() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%nclusterid.x;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t local_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void st_cluster(uint32_t addr, float v) {
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void st_cluster(uint32_t addr, double v) {
+  asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
+}
+
+// ---- bulk async copy global -> shared (TMA linear mode; completes on an mbarrier) ----
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void bulk_g2s_hint(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar,
+                                              uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::
+          "r"(smem_u32(smem_dst)),
+      "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+      : "memory");
+}
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+}  // namespace b2ot

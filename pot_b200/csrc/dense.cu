@@ -1,0 +1,656 @@
+// Host driver + C ABI of the dense Sinkhorn solver (see include/b2ot.h, dense_kernels.cuh).
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+
+#include "../../include/b2ot.h"
+#include "dense_kernels.cuh"
+#include "host_util.h"
+
+using namespace b2ot;
+
+namespace b2ot {
+
+static thread_local char g_err[512] = "";
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+std::atomic<unsigned long long>& launch_counter() {
+  static std::atomic<unsigned long long> c{0};
+  return c;
+}
+
+}  // namespace b2ot
+
+struct b2ot_dense {
+  int mode, dtype;
+  long long n, m, ld, mp;
+  const void *K, *a, *b, *logb;
+  int max_iter, check_every;
+  double stop_thr;
+  int variant;  // resolved: FUSED or SPLIT
+  cudaStream_t stream;
+  // workspace carve-up
+  SolveState* st;
+  double* blk_err;
+  double* err_hist;
+  int err_cap;
+  void *uring, *vring, *cbuf, *partials;
+  // fused sweep configuration
+  int cs, ncl, stages, vpt, W, use_hint;
+  size_t dyn_smem;
+  // split sweep / column-only pass configuration
+  int nsplit, nsplit_lse;
+  int fin_blocks;
+  b2ot_allreduce_fn ar;
+  void* ar_ctx;
+  SolveState* h_state;  // pinned host mirror for polls
+};
+
+static inline size_t esize(int dtype) { return dtype == B2OT_F64 ? 8 : 4; }
+static inline long long padded_m(long long m) { return (m + 1 + 31) / 32 * 32; }  // room for the flag slot
+
+extern "C" int b2ot_version(void) { return 100; }
+extern "C" const char* b2ot_last_error(void) { return b2ot::g_err; }
+extern "C" unsigned long long b2ot_launch_count(void) { return launch_counter().load(); }
+
+extern "C" int b2ot_device_info(int device, int* sm_count, int* cc_major, int* cc_minor) {
+  cudaDeviceProp prop;
+  B2OT_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (sm_count) *sm_count = prop.multiProcessorCount;
+  if (cc_major) *cc_major = prop.major;
+  if (cc_minor) *cc_minor = prop.minor;
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// elementwise entry points
+// ------------------------------------------------------------------------------------------------
+template <typename T, int OP>
+static int launch_cost_transform(const void* M, void* out, long long n, long long m, long long ldM, long long ldO,
+                                 double reg, cudaStream_t s) {
+  if (n <= 0 || m <= 0) return 0;
+  dim3 grid((unsigned)std::min<long long>(n, 1 << 20), (unsigned)((m + 1023) / 1024));
+  cost_transform_kernel<T, OP><<<grid, 256, 0, s>>>((const T*)M, (T*)out, n, m, ldM, ldO, (T)reg);
+  B2OT_CHECK_LAUNCH();
+  return 0;
+}
+extern "C" int b2ot_kexp(const void* M, void* K, int64_t n, int64_t m, int64_t ldM, int64_t ldK, double reg, int dtype,
+                         void* stream) {
+  B2OT_REQUIRE(dtype == B2OT_F32 || dtype == B2OT_F64, "b2ot_kexp: bad dtype %d", dtype);
+  return dtype == B2OT_F32 ? launch_cost_transform<float, 0>(M, K, n, m, ldM, ldK, reg, (cudaStream_t)stream)
+                           : launch_cost_transform<double, 0>(M, K, n, m, ldM, ldK, reg, (cudaStream_t)stream);
+}
+extern "C" int b2ot_negscale(const void* M, void* Mr, int64_t n, int64_t m, int64_t ldM, int64_t ldMr, double reg,
+                             int dtype, void* stream) {
+  B2OT_REQUIRE(dtype == B2OT_F32 || dtype == B2OT_F64, "b2ot_negscale: bad dtype %d", dtype);
+  return dtype == B2OT_F32 ? launch_cost_transform<float, 1>(M, Mr, n, m, ldM, ldMr, reg, (cudaStream_t)stream)
+                           : launch_cost_transform<double, 1>(M, Mr, n, m, ldM, ldMr, reg, (cudaStream_t)stream);
+}
+
+template <typename T>
+static int launch_plan(int mode, const void* K, const void* u, const void* v, void* out, long long n, long long m,
+                       long long ldK, long long ldO, cudaStream_t s) {
+  if (n <= 0 || m <= 0) return 0;
+  dim3 grid((unsigned)std::min<long long>(n, 1 << 20), (unsigned)((m + 1023) / 1024));
+  if (mode == B2OT_MODE_KNOPP)
+    plan_kernel<T, MODE_KNOPP><<<grid, 256, 0, s>>>((const T*)K, (const T*)u, (const T*)v, (T*)out, n, m, ldK, ldO);
+  else
+    plan_kernel<T, MODE_LOG><<<grid, 256, 0, s>>>((const T*)K, (const T*)u, (const T*)v, (T*)out, n, m, ldK, ldO);
+  B2OT_CHECK_LAUNCH();
+  return 0;
+}
+extern "C" int b2ot_dense_plan(int mode, int dtype, const void* K, const void* u, const void* v, void* out, int64_t n,
+                               int64_t m, int64_t ldK, int64_t ldOut, void* stream) {
+  B2OT_REQUIRE(mode == B2OT_MODE_KNOPP || mode == B2OT_MODE_LOG, "b2ot_dense_plan: bad mode %d", mode);
+  B2OT_REQUIRE(dtype == B2OT_F32 || dtype == B2OT_F64, "b2ot_dense_plan: bad dtype %d", dtype);
+  return dtype == B2OT_F32 ? launch_plan<float>(mode, K, u, v, out, n, m, ldK, ldOut, (cudaStream_t)stream)
+                           : launch_plan<double>(mode, K, u, v, out, n, m, ldK, ldOut, (cudaStream_t)stream);
+}
+
+static const int kLossBlocks = 1184;  // 148 SMs x 8
+extern "C" size_t b2ot_dense_loss_scratch_bytes(int64_t, int64_t) { return kLossBlocks * sizeof(double); }
+template <typename T>
+static int launch_loss(int mode, const void* K, const void* M, const void* u, const void* v, long long n, long long m,
+                       long long ldK, long long ldM, double* loss, void* scratch, cudaStream_t s) {
+  const int nb = (int)std::max<long long>(1, std::min<long long>(n, kLossBlocks));
+  if (mode == B2OT_MODE_KNOPP)
+    loss_kernel<T, MODE_KNOPP><<<nb, 256, 0, s>>>((const T*)K, (const T*)M, (const T*)u, (const T*)v, n, m, ldK, ldM,
+                                                  (double*)scratch);
+  else
+    loss_kernel<T, MODE_LOG><<<nb, 256, 0, s>>>((const T*)K, (const T*)M, (const T*)u, (const T*)v, n, m, ldK, ldM,
+                                                (double*)scratch);
+  B2OT_CHECK_LAUNCH();
+  sum_blocks_kernel<<<1, 256, 0, s>>>((const double*)scratch, nb, loss);
+  B2OT_CHECK_LAUNCH();
+  return 0;
+}
+extern "C" int b2ot_dense_loss(int mode, int dtype, const void* K, const void* M, const void* u, const void* v,
+                               int64_t n, int64_t m, int64_t ldK, int64_t ldM, double* loss_dev, void* scratch_dev,
+                               void* stream) {
+  B2OT_REQUIRE(mode == B2OT_MODE_KNOPP || mode == B2OT_MODE_LOG, "b2ot_dense_loss: bad mode %d", mode);
+  B2OT_REQUIRE(dtype == B2OT_F32 || dtype == B2OT_F64, "b2ot_dense_loss: bad dtype %d", dtype);
+  return dtype == B2OT_F32
+             ? launch_loss<float>(mode, K, M, u, v, n, m, ldK, ldM, loss_dev, scratch_dev, (cudaStream_t)stream)
+             : launch_loss<double>(mode, K, M, u, v, n, m, ldK, ldM, loss_dev, scratch_dev, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// dense solver handle
+// ------------------------------------------------------------------------------------------------
+struct WsLayout {
+  size_t off_state, off_blk, off_err, off_u, off_v, off_c, off_p, total;
+  int err_cap;
+};
+static WsLayout ws_layout(long long n, long long m, int dtype, int max_iter, int check_every) {
+  WsLayout L;
+  const size_t sz = esize(dtype);
+  const long long mp = padded_m(m);
+  size_t o = 0;
+  L.off_state = o;
+  o += 256;
+  L.off_blk = o;
+  o += 1024 * sizeof(double);
+  L.err_cap = max_iter / (check_every > 0 ? check_every : 1) + 2;
+  L.off_err = o;
+  o = align_up(o + (size_t)L.err_cap * sizeof(double), 256);
+  L.off_u = o;
+  o = align_up(o + 2 * (size_t)n * sz, 256);
+  L.off_v = o;
+  o = align_up(o + 3 * (size_t)mp * sz, 256);
+  L.off_c = o;
+  o = align_up(o + (size_t)mp * sz, 256);
+  L.off_p = o;
+  o = align_up(o + (size_t)NPMAX * mp * sz, 256);
+  L.total = o;
+  return L;
+}
+extern "C" size_t b2ot_dense_workspace_bytes(int64_t n, int64_t m, int dtype, int max_iter, int check_every) {
+  return ws_layout(n, m, dtype, max_iter, check_every).total;
+}
+
+template <typename T, int VPT, int MODE>
+static int config_fused(b2ot_dense* h) {
+  constexpr int R = rows_per_group(VPT);
+  constexpr int WCAP = NCT * VPT * Vec<T>::N;
+  const size_t stage_bytes = (size_t)R * WCAP * sizeof(T);
+  int stages = (int)((200 * 1024) / stage_bytes);
+  if (stages > SMAX) stages = SMAX;
+  if (stages < 2) stages = 2;
+  const char* env = getenv("B2OT_STAGES");
+  if (env && atoi(env) >= 2 && atoi(env) <= SMAX && (size_t)atoi(env) * stage_bytes <= 216 * 1024) stages = atoi(env);
+  h->stages = stages;
+  h->dyn_smem = stages * stage_bytes;
+  auto kern = fused_sweep_kernel<T, VPT, MODE>;
+  B2OT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->dyn_smem));
+  if (h->cs > 8) B2OT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)h->cs, 1, 1);
+  cfg.blockDim = dim3(NCT, 1, 1);
+  cfg.dynamicSmemBytes = h->dyn_smem;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)h->cs;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int maxcl = 0;
+  B2OT_CUDA(cudaOccupancyMaxActiveClusters(&maxcl, kern, &cfg));
+  B2OT_REQUIRE(maxcl >= 1, "fused sweep: no cluster of size %d fits on this device", h->cs);
+  const long long NG = (h->n + R - 1) / R;
+  long long ncl = std::min<long long>(maxcl, std::max<long long>(NG, 1));
+  const char* envc = getenv("B2OT_CLUSTERS");
+  if (envc && atoi(envc) >= 1) ncl = std::min<long long>(ncl, atoi(envc));
+  if (ncl > NPMAX) ncl = NPMAX;
+  h->ncl = (int)ncl;
+  return 0;
+}
+
+template <typename T, int VPT, int MODE>
+static int launch_fused(b2ot_dense* h) {
+  SweepParams p;
+  p.K = h->K;
+  p.ld = h->ld;
+  p.n = h->n;
+  p.m = h->m;
+  p.mp = h->mp;
+  p.a = h->a;
+  p.uring = h->uring;
+  p.vring = h->vring;
+  p.partials = h->partials;
+  p.st = h->st;
+  p.W = h->W;
+  p.stages = h->stages;
+  p.use_hint = h->use_hint;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(h->ncl * h->cs), 1, 1);
+  cfg.blockDim = dim3(NCT, 1, 1);
+  cfg.dynamicSmemBytes = h->dyn_smem;
+  cfg.stream = h->stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)h->cs;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B2OT_CUDA(cudaLaunchKernelEx(&cfg, fused_sweep_kernel<T, VPT, MODE>, p));
+  count_launch();
+  return 0;
+}
+
+#define B2OT_DISPATCH_FUSED(FN, h)                                         \
+  do {                                                                     \
+    const int key_ = ((h)->dtype == B2OT_F64 ? 100 : 0) + ((h)->mode == B2OT_MODE_LOG ? 10 : 0) + \
+                     ((h)->vpt == 8 ? 3 : (h)->vpt == 4 ? 2 : (h)->vpt == 2 ? 1 : 0);             \
+    switch (key_) {                                                        \
+      case 0: return FN<float, 1, MODE_KNOPP>(h);                          \
+      case 1: return FN<float, 2, MODE_KNOPP>(h);                          \
+      case 2: return FN<float, 4, MODE_KNOPP>(h);                          \
+      case 3: return FN<float, 8, MODE_KNOPP>(h);                          \
+      case 10: return FN<float, 1, MODE_LOG>(h);                           \
+      case 11: return FN<float, 2, MODE_LOG>(h);                           \
+      case 12: return FN<float, 4, MODE_LOG>(h);                           \
+      case 13: return FN<float, 8, MODE_LOG>(h);                           \
+      case 100: return FN<double, 1, MODE_KNOPP>(h);                       \
+      case 101: return FN<double, 2, MODE_KNOPP>(h);                       \
+      case 102: return FN<double, 4, MODE_KNOPP>(h);                       \
+      case 103: return FN<double, 8, MODE_KNOPP>(h);                       \
+      case 110: return FN<double, 1, MODE_LOG>(h);                         \
+      case 111: return FN<double, 2, MODE_LOG>(h);                         \
+      case 112: return FN<double, 4, MODE_LOG>(h);                         \
+      case 113: return FN<double, 8, MODE_LOG>(h);                         \
+      default: break;                                                      \
+    }                                                                      \
+    set_error("internal: bad fused dispatch key %d", key_);                \
+    return -1;                                                             \
+  } while (0)
+
+static int dispatch_config_fused(b2ot_dense* h) { B2OT_DISPATCH_FUSED(config_fused, h); }
+static int dispatch_launch_fused(b2ot_dense* h) { B2OT_DISPATCH_FUSED(launch_fused, h); }
+
+// Decide whether the fused sweep applies and pick (cluster size, vectors per thread, slice width).
+static bool plan_fused(b2ot_dense* h) {
+  const int vec = h->dtype == B2OT_F64 ? 2 : 4;
+  const size_t sz = esize(h->dtype);
+  if (h->m % vec != 0 || h->ld % vec != 0) return false;
+  if (((uintptr_t)h->K) % 16 != 0) return false;
+  if (h->n < 1 || h->m < vec) return false;
+  const long long wcap8 = (long long)NCT * 8 * vec;
+  int max_cs = 8;
+  const char* env = getenv("B2OT_MAX_CLUSTER");
+  if (env && atoi(env) >= 1 && atoi(env) <= CSMAX) max_cs = atoi(env);
+  if (h->m <= wcap8) {
+    h->cs = 1;
+    h->vpt = 8;
+    for (int vpt = 1; vpt <= 8; vpt *= 2) {
+      if ((long long)NCT * vpt * vec >= h->m) {
+        h->vpt = vpt;
+        break;
+      }
+    }
+    h->W = (int)h->m;
+  } else {
+    int cs = 2;
+    while (cs <= max_cs && (long long)cs * wcap8 < h->m) cs *= 2;
+    if (cs > max_cs) return false;
+    h->cs = cs;
+    h->vpt = 8;
+    long long w = (h->m + cs - 1) / cs;
+    w = (w + vec - 1) / vec * vec;
+    h->W = (int)w;
+  }
+  // K streams through L2 once per sweep: mark it evict-first only when it cannot stay resident
+  h->use_hint = ((double)h->n * (double)h->ld * (double)sz > 80.0 * 1024 * 1024) ? 1 : 0;
+  const char* envh = getenv("B2OT_L2_HINT");
+  if (envh) h->use_hint = atoi(envh) ? 1 : 0;
+  return true;
+}
+
+extern "C" int b2ot_dense_create(b2ot_dense** handle, int mode, int dtype, int64_t n, int64_t m, int64_t ld,
+                                 const void* K, const void* a, const void* b, const void* logb, void* workspace,
+                                 size_t workspace_bytes, int max_iter, int check_every, double stop_thr, int variant,
+                                 void* stream) {
+  B2OT_REQUIRE(handle != nullptr, "b2ot_dense_create: null handle pointer");
+  B2OT_REQUIRE(mode == B2OT_MODE_KNOPP || mode == B2OT_MODE_LOG, "b2ot_dense_create: bad mode %d", mode);
+  B2OT_REQUIRE(dtype == B2OT_F32 || dtype == B2OT_F64, "b2ot_dense_create: bad dtype %d", dtype);
+  B2OT_REQUIRE(n >= 1 && m >= 1 && ld >= m, "b2ot_dense_create: bad shape n=%lld m=%lld ld=%lld", (long long)n,
+               (long long)m, (long long)ld);
+  B2OT_REQUIRE(K && a && b && workspace, "b2ot_dense_create: null device pointer");
+  B2OT_REQUIRE(mode == B2OT_MODE_KNOPP || logb != nullptr, "b2ot_dense_create: log mode needs logb");
+  B2OT_REQUIRE(max_iter >= 1 && check_every >= 1, "b2ot_dense_create: max_iter and check_every must be >= 1");
+  const WsLayout L = ws_layout(n, m, dtype, max_iter, check_every);
+  B2OT_REQUIRE(workspace_bytes >= L.total, "b2ot_dense_create: workspace too small (%zu < %zu)", workspace_bytes,
+               L.total);
+  B2OT_REQUIRE(((uintptr_t)workspace) % 256 == 0, "b2ot_dense_create: workspace must be 256-byte aligned");
+
+  b2ot_dense* h = new (std::nothrow) b2ot_dense();
+  B2OT_REQUIRE(h != nullptr, "b2ot_dense_create: out of host memory");
+  memset(h, 0, sizeof(*h));
+  h->mode = mode;
+  h->dtype = dtype;
+  h->n = n;
+  h->m = m;
+  h->ld = ld;
+  h->mp = padded_m(m);
+  h->K = K;
+  h->a = a;
+  h->b = b;
+  h->logb = logb;
+  h->max_iter = max_iter;
+  h->check_every = check_every;
+  h->stop_thr = stop_thr;
+  h->stream = (cudaStream_t)stream;
+  char* ws = (char*)workspace;
+  h->st = (SolveState*)(ws + L.off_state);
+  h->blk_err = (double*)(ws + L.off_blk);
+  h->err_hist = (double*)(ws + L.off_err);
+  h->err_cap = L.err_cap;
+  h->uring = ws + L.off_u;
+  h->vring = ws + L.off_v;
+  h->cbuf = ws + L.off_c;
+  h->partials = ws + L.off_p;
+
+  // column-kernel row split: enough blocks to fill the machine, bounded by the scratch rows
+  int sm = 148;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev);
+  const long long colblocks = (m + 255) / 256;
+  long long ns = (4LL * sm + colblocks - 1) / colblocks;
+  if (ns < 1) ns = 1;
+  if (ns > n) ns = n;
+  if (ns > 64) ns = 64;
+  h->nsplit = (int)ns;
+  h->nsplit_lse = (int)ns;
+  h->fin_blocks = (int)std::min<long long>(colblocks, 1024);
+
+  bool fused_ok = plan_fused(h);
+  if (variant == B2OT_VARIANT_FUSED && !fused_ok) {
+    delete h;
+    set_error("b2ot_dense_create: fused sweep needs 16-byte aligned rows (m, ld multiples of %d), got m=%lld ld=%lld",
+              dtype == B2OT_F64 ? 2 : 4, (long long)m, (long long)ld);
+    return -1;
+  }
+  h->variant = (variant == B2OT_VARIANT_SPLIT || !fused_ok) ? B2OT_VARIANT_SPLIT : B2OT_VARIANT_FUSED;
+  if (h->variant == B2OT_VARIANT_FUSED) {
+    int rc = dispatch_config_fused(h);
+    if (rc != 0) {
+      if (variant == B2OT_VARIANT_FUSED) {
+        delete h;
+        return rc;
+      }
+      h->variant = B2OT_VARIANT_SPLIT;
+    }
+  }
+  if (cudaMallocHost((void**)&h->h_state, sizeof(SolveState)) != cudaSuccess) {
+    delete h;
+    set_error("b2ot_dense_create: cudaMallocHost failed");
+    return -2;
+  }
+  *handle = h;
+  return 0;
+}
+
+extern "C" int b2ot_dense_set_allreduce(b2ot_dense* h, b2ot_allreduce_fn fn, void* ctx) {
+  B2OT_REQUIRE(h != nullptr, "b2ot_dense_set_allreduce: null handle");
+  h->ar = fn;
+  h->ar_ctx = ctx;
+  return 0;
+}
+
+extern "C" int b2ot_dense_info(const b2ot_dense* h, int* variant, int* cluster_size, int* n_clusters, int* stages,
+                               int* vecs_per_thread) {
+  B2OT_REQUIRE(h != nullptr, "b2ot_dense_info: null handle");
+  if (variant) *variant = h->variant;
+  if (cluster_size) *cluster_size = h->variant == B2OT_VARIANT_FUSED ? h->cs : 0;
+  if (n_clusters) *n_clusters = h->variant == B2OT_VARIANT_FUSED ? h->ncl : h->nsplit;
+  if (stages) *stages = h->variant == B2OT_VARIANT_FUSED ? h->stages : 0;
+  if (vecs_per_thread) *vecs_per_thread = h->variant == B2OT_VARIANT_FUSED ? h->vpt : 0;
+  return 0;
+}
+
+extern "C" int b2ot_dense_destroy(b2ot_dense* h) {
+  if (h == nullptr) return 0;
+  if (h->h_state) cudaFreeHost(h->h_state);
+  delete h;
+  return 0;
+}
+
+// ---- launch helpers ---------------------------------------------------------------------------
+static SplitParams split_params(const b2ot_dense* h, int u_slot_xor, int nsplit, int expect_status) {
+  SplitParams p;
+  p.K = h->K;
+  p.ld = h->ld;
+  p.n = h->n;
+  p.m = h->m;
+  p.mp = h->mp;
+  p.a = h->a;
+  p.uring = h->uring;
+  p.vring = h->vring;
+  p.partials = h->partials;
+  p.st = h->st;
+  p.u_slot_xor = u_slot_xor;
+  p.nsplit = nsplit;
+  p.expect_status = expect_status;
+  return p;
+}
+
+template <typename T>
+static int launch_cols(const b2ot_dense* h, int u_slot_xor) {
+  const SplitParams p = split_params(h, u_slot_xor, h->nsplit, ST_RUNNING);
+  dim3 grid((unsigned)((h->m + 255) / 256), (unsigned)h->nsplit);
+  if (h->mode == B2OT_MODE_KNOPP)
+    cols_kernel<T, MODE_KNOPP><<<grid, 256, 0, h->stream>>>(p);
+  else
+    cols_kernel<T, MODE_LOG><<<grid, 256, 0, h->stream>>>(p);
+  B2OT_CHECK_LAUNCH();
+  return 0;
+}
+template <typename T>
+static int launch_rows(const b2ot_dense* h) {
+  const SplitParams p = split_params(h, 0, h->nsplit, ST_RUNNING);
+  const unsigned grid = (unsigned)((h->n + 7) / 8);
+  if (h->mode == B2OT_MODE_KNOPP)
+    rows_kernel<T, MODE_KNOPP><<<grid, 256, 0, h->stream>>>(p);
+  else
+    rows_kernel<T, MODE_LOG><<<grid, 256, 0, h->stream>>>(p);
+  B2OT_CHECK_LAUNCH();
+  return 0;
+}
+
+static int call_allreduce(const b2ot_dense* h, void* buf, long long count, int op) {
+  const int rc = h->ar(buf, count, h->dtype, op, (void*)h->stream, h->ar_ctx);
+  B2OT_REQUIRE(rc == 0, "all-reduce hook failed with code %d", rc);
+  return 0;
+}
+
+template <typename T>
+static int launch_finalize(const b2ot_dense* h, int nsrc, int init) {
+  FinParams p;
+  const bool multi = h->ar != nullptr;
+  if (multi) {
+    const unsigned g = (unsigned)((h->m + 1 + 255) / 256);
+    reduce_partials_kernel<T><<<g, 256, 0, h->stream>>>(h->partials, h->mp, nsrc, h->cbuf, h->m, h->st, ST_RUNNING);
+    B2OT_CHECK_LAUNCH();
+    int rc = call_allreduce(h, h->cbuf, h->m + 1, 0);
+    if (rc) return rc;
+    p.src = h->cbuf;
+    p.src_ld = h->mp;
+    p.nsrc = 1;
+    p.extra_flag = (const char*)h->cbuf + (size_t)h->m * sizeof(T);
+  } else {
+    p.src = h->partials;
+    p.src_ld = h->mp;
+    p.nsrc = nsrc;
+    p.extra_flag = nullptr;
+  }
+  p.b = h->b;
+  p.logb = h->logb;
+  p.vring = h->vring;
+  p.cbuf = h->cbuf;
+  p.m = h->m;
+  p.mp = h->mp;
+  p.st = h->st;
+  p.blk_err = h->blk_err;
+  p.err_hist = h->err_hist;
+  p.max_iter = h->max_iter;
+  p.check_every = h->check_every;
+  p.stop_thr = h->stop_thr;
+  p.init = init;
+  if (h->mode == B2OT_MODE_KNOPP)
+    finalize_kernel<T, MODE_KNOPP><<<h->fin_blocks, 256, 0, h->stream>>>(p);
+  else
+    finalize_kernel<T, MODE_LOG><<<h->fin_blocks, 256, 0, h->stream>>>(p);
+  B2OT_CHECK_LAUNCH();
+  return 0;
+}
+
+// exact column log-sum-exp step: v_next = logb - LSE_i(K_ij + u_i)
+template <typename T>
+static int launch_exact_cols(const b2ot_dense* h, int expect_status, int advance_iter) {
+  const int ns = h->nsplit_lse;
+  const SplitParams sp = split_params(h, 0, ns, expect_status);
+  dim3 grid((unsigned)((h->m + 255) / 256), (unsigned)ns);
+  cols_lse_kernel<T><<<grid, 256, 0, h->stream>>>(sp);
+  B2OT_CHECK_LAUNCH();
+  LseParams lp;
+  lp.partials = h->partials;
+  lp.m = h->m;
+  lp.mp = h->mp;
+  lp.nsplit = ns;
+  lp.logb = h->logb;
+  lp.vring = h->vring;
+  lp.st = h->st;
+  lp.expect_status = expect_status;
+  lp.advance_iter = advance_iter;
+  lp.max_iter = h->max_iter;
+  const unsigned g1 = (unsigned)((h->m + 255) / 256);
+  lse_combine_kernel<T><<<g1, 256, 0, h->stream>>>(lp);
+  B2OT_CHECK_LAUNCH();
+  char* P = (char*)h->partials;
+  if (h->ar) {
+    int rc = call_allreduce(h, P + (size_t)(2 * ns + 1) * h->mp * sizeof(T), h->m, 1);
+    if (rc) return rc;
+  }
+  lse_rescale_kernel<T><<<g1, 256, 0, h->stream>>>(lp);
+  B2OT_CHECK_LAUNCH();
+  if (h->ar) {
+    int rc = call_allreduce(h, P + (size_t)(2 * ns + 2) * h->mp * sizeof(T), h->m, 0);
+    if (rc) return rc;
+  }
+  lse_finish_kernel<T><<<g1, 256, 0, h->stream>>>(lp);
+  B2OT_CHECK_LAUNCH();
+  lse_advance_kernel<<<1, 1, 0, h->stream>>>(h->st, expect_status, advance_iter);
+  B2OT_CHECK_LAUNCH();
+  return 0;
+}
+
+template <typename T>
+static int dense_init_t(b2ot_dense* h, const void* u0, const void* v0) {
+  B2OT_CUDA(cudaMemsetAsync(h->st, 0, 256, h->stream));
+  B2OT_CUDA(cudaMemcpyAsync(h->uring, u0, (size_t)h->n * sizeof(T), cudaMemcpyDeviceToDevice, h->stream));
+  B2OT_CUDA(cudaMemcpyAsync(h->vring, v0, (size_t)h->m * sizeof(T), cudaMemcpyDeviceToDevice, h->stream));
+  if (h->mode == B2OT_MODE_KNOPP) {
+    int rc = launch_cols<T>(h, 0);  // c0 = K^T u0
+    if (rc) return rc;
+    return launch_finalize<T>(h, h->nsplit, 1);
+  }
+  return launch_exact_cols<T>(h, ST_RUNNING, 0);  // v0' = logb - LSE_i(Mr + u0)
+}
+
+template <typename T>
+static int dense_iterate_t(b2ot_dense* h, int n_iters) {
+  for (int it = 0; it < n_iters; ++it) {
+    int nsrc;
+    if (h->variant == B2OT_VARIANT_FUSED) {
+      int rc = dispatch_launch_fused(h);
+      if (rc) return rc;
+      nsrc = h->ncl;
+    } else {
+      int rc = launch_rows<T>(h);
+      if (rc) return rc;
+      rc = launch_cols<T>(h, 1);
+      if (rc) return rc;
+      nsrc = h->nsplit;
+    }
+    int rc = launch_finalize<T>(h, nsrc, 0);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
+extern "C" int b2ot_dense_init(b2ot_dense* h, const void* u0, const void* v0) {
+  B2OT_REQUIRE(h && u0 && v0, "b2ot_dense_init: null argument");
+  return h->dtype == B2OT_F32 ? dense_init_t<float>(h, u0, v0) : dense_init_t<double>(h, u0, v0);
+}
+
+extern "C" int b2ot_dense_iterate(b2ot_dense* h, int n_iters) {
+  B2OT_REQUIRE(h != nullptr, "b2ot_dense_iterate: null handle");
+  return h->dtype == B2OT_F32 ? dense_iterate_t<float>(h, n_iters) : dense_iterate_t<double>(h, n_iters);
+}
+
+extern "C" int b2ot_dense_poll(b2ot_dense* h, int* status, int* iter) {
+  B2OT_REQUIRE(h != nullptr, "b2ot_dense_poll: null handle");
+  for (int guard = 0; guard < 4; ++guard) {
+    B2OT_CUDA(cudaMemcpyAsync(h->h_state, h->st, sizeof(SolveState), cudaMemcpyDeviceToHost, h->stream));
+    B2OT_CUDA(cudaStreamSynchronize(h->stream));
+    if (h->h_state->status != ST_PAUSE_EXACT) break;
+    // log domain: a row-frame column sum underflowed; redo this v update with the exact column pass
+    int rc = h->dtype == B2OT_F32 ? launch_exact_cols<float>(h, ST_PAUSE_EXACT, 1)
+                                  : launch_exact_cols<double>(h, ST_PAUSE_EXACT, 1);
+    if (rc) return rc;
+  }
+  if (status) *status = h->h_state->status;
+  if (iter) *iter = h->h_state->iter;
+  return 0;
+}
+
+extern "C" int b2ot_dense_solve(b2ot_dense* h, const void* u0, const void* v0, int poll_every, int* status,
+                                int* niter, int* n_err) {
+  B2OT_REQUIRE(h != nullptr, "b2ot_dense_solve: null handle");
+  int rc = b2ot_dense_init(h, u0, v0);
+  if (rc) return rc;
+  int st = ST_RUNNING, it = 0;
+  while (st == ST_RUNNING) {
+    int chunk = h->max_iter - it;
+    if (poll_every > 0 && chunk > poll_every) chunk = poll_every;
+    if (chunk < 1) chunk = 1;
+    rc = b2ot_dense_iterate(h, chunk);
+    if (rc) return rc;
+    rc = b2ot_dense_poll(h, &st, &it);
+    if (rc) return rc;
+  }
+  if (status) *status = st;
+  if (niter) *niter = h->h_state->niter;
+  if (n_err) *n_err = h->h_state->n_err;
+  return 0;
+}
+
+extern "C" int b2ot_dense_export(b2ot_dense* h, void* u_out, void* v_out, double* err_host, int err_capacity,
+                                 int* n_err) {
+  B2OT_REQUIRE(h != nullptr, "b2ot_dense_export: null handle");
+  const long long mx = h->n > h->m ? h->n : h->m;
+  const unsigned grid = (unsigned)((mx + 255) / 256);
+  if (h->dtype == B2OT_F32)
+    export_kernel<float><<<grid, 256, 0, h->stream>>>(h->uring, h->vring, h->n, h->m, h->mp, h->st, u_out, v_out);
+  else
+    export_kernel<double><<<grid, 256, 0, h->stream>>>(h->uring, h->vring, h->n, h->m, h->mp, h->st, u_out, v_out);
+  B2OT_CHECK_LAUNCH();
+  B2OT_CUDA(cudaMemcpyAsync(h->h_state, h->st, sizeof(SolveState), cudaMemcpyDeviceToHost, h->stream));
+  B2OT_CUDA(cudaStreamSynchronize(h->stream));
+  int ne = h->h_state->n_err;
+  if (ne > h->err_cap) ne = h->err_cap;
+  if (n_err) *n_err = ne;
+  if (err_host != nullptr && err_capacity > 0 && ne > 0) {
+    const int k = ne < err_capacity ? ne : err_capacity;
+    B2OT_CUDA(cudaMemcpyAsync(err_host, h->err_hist, (size_t)k * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    B2OT_CUDA(cudaStreamSynchronize(h->stream));
+  }
+  return 0;
+}

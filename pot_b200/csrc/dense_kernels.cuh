@@ -1,0 +1,764 @@
+// Device kernels of the dense Sinkhorn solver (scaling domain and log domain), sm_100a.
+//
+// Hot kernel: fused_sweep_kernel — ONE pass over K per Sinkhorn iteration.
+//   * A thread-block cluster owns whole rows: CTA c of the cluster owns the column slice
+//     [c*W, (c+1)*W).  Row-group tiles (R rows x W columns) stream into a multi-stage
+//     shared-memory ring with 1-D TMA bulk copies (cp.async.bulk + mbarrier tx), issued by one
+//     elected thread as soon as a stage has been drained.
+//   * All warps pull a tile into registers (freeing the stage at once), form the partial
+//     row sums (K v)_i of their slice, reduce them warp -> CTA -> cluster (DSMEM stores +
+//     remote mbarrier arrive), obtain u_i = a_i / (K v)_i, and immediately accumulate the tile's
+//     contribution u_i K_ij into per-thread column accumulators that live in registers for the
+//     whole sweep.  K is read from HBM exactly once per iteration (the reference makes two GEMV
+//     passes, ot/bregman/_sinkhorn.py:629-631).
+//   * Log domain: same structure; the row pass is a (max, sum-exp) reduction and the column
+//     accumulators collect the row-frame plan entries e_ij * f_i, which equal
+//     exp(Mr_ij + u_i + v_j): their column sums are the column marginal, so the next
+//     v = v + log b - log(colsum) needs no second exp per element (ot/bregman/_sinkhorn.py:881-889).
+//
+// Reference iteration order is "v then u"; one fused sweep P(v) -> (u, K^T u) covers the u update
+// of iteration ii and the K^T u of iteration ii+1, the finalize kernel derives v, the marginal
+// error ||v * K^T u - b|| (:653-654) and the numerical guard (:633-645) from the same column sums.
+#pragma once
+
+#include "common.cuh"
+
+namespace b2ot {
+
+constexpr int MODE_KNOPP = 0;
+constexpr int MODE_LOG = 1;
+
+constexpr int NCW = 8;            // warps per CTA of the fused sweep
+constexpr int NCT = NCW * 32;     // threads per CTA (8 warps = 2 per SM sub-partition: full 255-register budget)
+constexpr int SMAX = 8;           // max pipeline stages
+constexpr int CSMAX = 16;         // max cluster size
+constexpr int NPMAX = 160;        // rows of the partial-sum scratch (>= clusters in a grid)
+
+__host__ __device__ constexpr int rows_per_group(int vpt) { return vpt >= 2 ? 16 / vpt : 8; }
+
+struct SweepParams {
+  const void* K;        // n x m, leading dimension ld (elements)
+  long long ld, n, m, mp;
+  const void* a;        // KNOPP: a ; LOG: log a        (n)
+  void* uring;          // 2 x n
+  const void* vring;    // 3 x mp
+  void* partials;       // NPMAX x mp   (row q = column sums produced by cluster q)
+  SolveState* st;
+  int W;                // columns per CTA slice (multiple of the vector width)
+  int stages;
+  int use_hint;         // L2 evict-first on the K stream (K much larger than L2)
+};
+
+template <typename T, int VPT, int MODE>
+__global__ void __launch_bounds__(NCT, 1) fused_sweep_kernel(const SweepParams p) {
+  using V = typename Vec<T>::type;
+  constexpr int VEC = Vec<T>::N;
+  constexpr int R = rows_per_group(VPT);
+  constexpr int PAY = (MODE == MODE_LOG) ? 2 : 1;
+  constexpr int NQ = R * PAY;
+  constexpr int WCAP = NCT * VPT * VEC;
+
+  __shared__ __align__(16) uint64_t full_bar[SMAX];
+  __shared__ __align__(16) uint64_t exch_bar[2];
+  __shared__ __align__(16) T red[NCW][NQ];
+  __shared__ __align__(16) T exch[2][NQ][CSMAX];
+  extern __shared__ __align__(128) unsigned char dyn_smem[];
+  T* const stage_base = reinterpret_cast<T*>(dyn_smem);
+
+  if (p.st->status != ST_RUNNING) return;  // sticky stop: uniform over the grid
+  const int sel_u = p.st->sel_u;
+  const int sel_v = p.st->sel_v;
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int lane = tid & 31;
+  const uint32_t crank = cluster_ctarank();
+  const uint32_t csize = cluster_nctarank();
+  const long long cid = cluster_id_x();
+  const long long ncl = cluster_count_x();
+  const long long col0 = (long long)crank * p.W;
+  const long long wrem = p.m - col0;
+  const int wc = wrem <= 0 ? 0 : (wrem > p.W ? p.W : (int)wrem);  // valid columns of my slice
+  const long long NG = (p.n + R - 1) / R;
+  const int S = p.stages;
+  const T* const Kg = reinterpret_cast<const T*>(p.K);
+  const uint32_t row_bytes = (uint32_t)wc * (uint32_t)sizeof(T);
+  const uint64_t pol = p.use_hint ? l2_policy_evict_first() : 0ull;
+
+  // Producer step (one elected thread): stream row group g into stage s with TMA bulk copies.
+  auto issue_group = [&](long long g, int s) {
+    const long long row0 = g * R;
+    const int rv = (p.n - row0) < R ? (int)(p.n - row0) : R;
+    if (row_bytes == 0) {
+      mbar_arrive(&full_bar[s]);
+      return;
+    }
+    mbar_arrive_expect_tx(&full_bar[s], row_bytes * (uint32_t)rv);
+    for (int r = 0; r < rv; ++r) {
+      T* dst = stage_base + ((size_t)s * R + r) * WCAP;
+      const T* src = Kg + (row0 + r) * p.ld + col0;
+      if (p.use_hint)
+        bulk_g2s_hint(dst, src, row_bytes, &full_bar[s], pol);
+      else
+        bulk_g2s(dst, src, row_bytes, &full_bar[s]);
+    }
+  };
+
+  if (tid == 0) {
+    for (int s = 0; s < S; ++s) mbar_init(&full_bar[s], 1);
+    mbar_init(&exch_bar[0], csize);
+    mbar_init(&exch_bar[1], csize);
+    fence_mbar_init();
+    // prologue: fill the ring
+    for (int s = 0; s < S; ++s) {
+      const long long g = cid + (long long)s * ncl;
+      if (g < NG) issue_group(g, s);
+    }
+  }
+  __syncthreads();
+  cluster_sync_all();  // every CTA's barriers exist before any remote arrive
+
+  const T* vcur = reinterpret_cast<const T*>(p.vring) + (long long)sel_v * p.mp + col0;
+  T* unew = reinterpret_cast<T*>(p.uring) + (long long)(sel_u ^ 1) * p.n;
+  const T* ag = reinterpret_cast<const T*>(p.a);
+
+  V vreg[VPT];
+  V acc[VPT];
+#pragma unroll
+  for (int k = 0; k < VPT; ++k) {
+    const int e = (k * NCT + tid) * VEC;
+    if (e < wc)
+      vreg[k] = *reinterpret_cast<const V*>(vcur + e);
+    else
+      fill(vreg[k], (T)0);
+    fill(acc[k], (T)0);
+  }
+
+  int cs_log2 = 0;
+  while ((1u << cs_log2) < csize) ++cs_log2;
+
+  int s = 0;          // ring slot of the current group
+  uint32_t ph = 0;    // its mbarrier phase parity
+  long long it = 0;
+  for (long long g = cid; g < NG; g += ncl, ++it) {
+    const int par = (int)(it & 1);
+    const uint32_t eph = (uint32_t)((it >> 1) & 1);
+    const long long row0 = g * R;
+    const int rv = (p.n - row0) < R ? (int)(p.n - row0) : R;
+
+    T areg[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) areg[r] = (r < rv) ? ag[row0 + r] : (T)0;
+
+    // ---- tile: shared -> registers ----
+    mbar_wait(&full_bar[s], ph);
+    V kreg[R][VPT];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const T* srow = stage_base + ((size_t)s * R + r) * WCAP;
+#pragma unroll
+      for (int k = 0; k < VPT; ++k) {
+        const int e = (k * NCT + tid) * VEC;
+        if (r < rv && e < wc)
+          kreg[r][k] = *reinterpret_cast<const V*>(srow + e);
+        else
+          fill(kreg[r][k], MODE == MODE_LOG ? neg_inf<T>() : (T)0);
+      }
+    }
+
+    // ---- phase A: partial row reductions over my column slice ----
+    T wref[R];  // LOG: this warp's exp reference per row
+    if (MODE == MODE_KNOPP) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        T s0 = (T)0, s1 = (T)0;
+#pragma unroll
+        for (int k = 0; k < VPT; ++k) {
+#pragma unroll
+          for (int i = 0; i < VEC; i += 2) {
+            s0 = fma(elem(kreg[r][k], i), elem(vreg[k], i), s0);
+            s1 = fma(elem(kreg[r][k], i + 1), elem(vreg[k], i + 1), s1);
+          }
+        }
+        const T tot = warp_sum(s0 + s1);
+        if (lane == 0) red[warp][r] = tot;
+        wref[r] = (T)0;
+      }
+    } else {
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        T mx = neg_inf<T>();
+#pragma unroll
+        for (int k = 0; k < VPT; ++k) {
+#pragma unroll
+          for (int i = 0; i < VEC; ++i) {
+            const T x = elem(kreg[r][k], i) + elem(vreg[k], i);
+            elem(kreg[r][k], i) = x;
+            mx = max_t(mx, x);
+          }
+        }
+        mx = warp_max(mx);
+        const T ref = (mx == neg_inf<T>()) ? (T)0 : mx;
+        T sm0 = (T)0, sm1 = (T)0;
+#pragma unroll
+        for (int k = 0; k < VPT; ++k) {
+#pragma unroll
+          for (int i = 0; i < VEC; i += 2) {
+            const T e0 = exp_t(elem(kreg[r][k], i) - ref);
+            const T e1 = exp_t(elem(kreg[r][k], i + 1) - ref);
+            elem(kreg[r][k], i) = e0;
+            elem(kreg[r][k], i + 1) = e1;
+            sm0 += e0;
+            sm1 += e1;
+          }
+        }
+        const T sm = warp_sum(sm0 + sm1);
+        wref[r] = ref;
+        if (lane == 0) {
+          red[warp][2 * r] = mx;
+          red[warp][2 * r + 1] = sm;
+        }
+      }
+    }
+    // Every warp has consumed its part of stage s (the values feed the reductions above), so
+    // after this barrier the stage can be refilled.
+    __syncthreads();
+
+    // ---- warp 0: refill the ring, CTA-level combine, push to every CTA of the cluster (DSMEM) ----
+    if (warp == 0) {
+      if (lane == 0) {
+        const long long gn = g + (long long)S * ncl;
+        if (gn < NG) issue_group(gn, s);
+      }
+      __syncwarp();
+      const int w = lane & 7;    // source warp
+      const int sub = lane >> 3; // 4 payload rows handled per step
+      if (MODE == MODE_KNOPP) {
+#pragma unroll
+        for (int q0 = 0; q0 < NQ; q0 += 4) {
+          const int q = q0 + sub;
+          T x = (q < NQ) ? red[w][q < NQ ? q : 0] : (T)0;
+          x += __shfl_xor_sync(0xffffffffu, x, 4);
+          x += __shfl_xor_sync(0xffffffffu, x, 2);
+          x += __shfl_xor_sync(0xffffffffu, x, 1);
+#pragma unroll
+          for (int qq = 0; qq < 4; ++qq) {
+            const T tot = __shfl_sync(0xffffffffu, x, qq * 8);
+            if (q0 + qq < NQ && lane < (int)csize)
+              st_cluster(mapa_u32(smem_u32(&exch[par][(q0 + qq) < NQ ? (q0 + qq) : 0][crank]), (uint32_t)lane), tot);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int r0 = 0; r0 < R; r0 += 4) {
+          const int r = r0 + sub;
+          const int rc = r < R ? r : 0;
+          const T mxw = (r < R) ? red[w][2 * rc] : neg_inf<T>();
+          const T smw = (r < R) ? red[w][2 * rc + 1] : (T)0;
+          T M = mxw;
+          M = max_t(M, __shfl_xor_sync(0xffffffffu, M, 4));
+          M = max_t(M, __shfl_xor_sync(0xffffffffu, M, 2));
+          M = max_t(M, __shfl_xor_sync(0xffffffffu, M, 1));
+          T sc = (mxw == neg_inf<T>()) ? (T)0 : smw * exp_t(mxw - M);
+          sc += __shfl_xor_sync(0xffffffffu, sc, 4);
+          sc += __shfl_xor_sync(0xffffffffu, sc, 2);
+          sc += __shfl_xor_sync(0xffffffffu, sc, 1);
+#pragma unroll
+          for (int qq = 0; qq < 4; ++qq) {
+            const T Mq = __shfl_sync(0xffffffffu, M, qq * 8);
+            const T Sq = __shfl_sync(0xffffffffu, sc, qq * 8);
+            if (r0 + qq < R && lane < (int)csize) {
+              const int rr = (r0 + qq) < R ? (r0 + qq) : 0;
+              st_cluster(mapa_u32(smem_u32(&exch[par][2 * rr][crank]), (uint32_t)lane), Mq);
+              st_cluster(mapa_u32(smem_u32(&exch[par][2 * rr + 1][crank]), (uint32_t)lane), Sq);
+            }
+          }
+        }
+      }
+      if (lane < (int)csize) mbar_arrive_remote(mapa_u32(smem_u32(&exch_bar[par]), (uint32_t)lane));
+    }
+
+    // ---- all warps: wait for every CTA's payload, finish the row scalars ----
+    mbar_wait_cluster(&exch_bar[par], eph);
+
+    T urow[R];  // KNOPP: u_i ; LOG: f_i (row-frame factor for this warp)
+    if (MODE == MODE_KNOPP) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        T sum = (T)0;
+        for (int c = 0; c < (int)csize; ++c) sum += exch[par][r][c];
+        const T u = areg[r] / sum;
+        urow[r] = (r < rv) ? u : (T)0;
+        if (crank == 0 && tid == r && r < rv) {
+          unew[row0 + r] = u;
+          if (!finite_t(u)) atomicOr(&p.st->uflag, 1);
+        }
+      }
+    } else {
+      // lane (r_l, c_l) combines the (max, sum) pair of CTA c_l for row r_l
+      const int r_l = lane >> cs_log2;
+      const int c_l = lane & ((int)csize - 1);
+      const bool lv = r_l < R;
+      const int rcl = lv ? r_l : 0;
+      const T mxc = lv ? exch[par][2 * rcl][c_l] : neg_inf<T>();
+      const T smc = lv ? exch[par][2 * rcl + 1][c_l] : (T)0;
+      T M = mxc;
+      for (int o = (int)csize >> 1; o > 0; o >>= 1) M = max_t(M, __shfl_xor_sync(0xffffffffu, M, o));
+      T sc = (mxc == neg_inf<T>()) ? (T)0 : smc * exp_t(mxc - M);
+      for (int o = (int)csize >> 1; o > 0; o >>= 1) sc += __shfl_xor_sync(0xffffffffu, sc, o);
+      const T lse_l = M + log_t(sc);
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const T lse = __shfl_sync(0xffffffffu, lse_l, (r << cs_log2) & 31);
+        const T u = areg[r] - lse;
+        urow[r] = (r < rv) ? exp_t(wref[r] + u) : (T)0;
+        if (crank == 0 && tid == r && r < rv) unew[row0 + r] = u;
+      }
+    }
+
+    // ---- phase B: the resident tile feeds the column accumulators ----
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+#pragma unroll
+      for (int k = 0; k < VPT; ++k) {
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) elem(acc[k], i) = fma(elem(kreg[r][k], i), urow[r], elem(acc[k], i));
+      }
+    }
+
+    if (++s == S) {
+      s = 0;
+      ph ^= 1u;
+    }
+  }
+
+  // ---- one flush per sweep: this cluster's column sums ----
+  T* pout = reinterpret_cast<T*>(p.partials) + cid * p.mp + col0;
+#pragma unroll
+  for (int k = 0; k < VPT; ++k) {
+    const int e = (k * NCT + tid) * VEC;
+    if (e < wc) *reinterpret_cast<V*>(pout + e) = acc[k];
+  }
+  cluster_sync_all();  // no CTA leaves while a peer could still address its shared memory
+}
+
+// ------------------------------------------------------------------------------------------------
+// Split (two-pass) sweep: any shape, any alignment.  Also provides the column-only pass that seeds
+// the first v update.
+// ------------------------------------------------------------------------------------------------
+struct SplitParams {
+  const void* K;
+  long long ld, n, m, mp;
+  const void* a;
+  void* uring;
+  const void* vring;
+  void* partials;
+  SolveState* st;
+  int u_slot_xor;   // cols kernel: 0 = current u, 1 = the u just produced
+  int nsplit;       // row chunks of the column kernel
+  int expect_status;
+};
+
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256) rows_kernel(const SplitParams p) {
+  if (p.st->status != ST_RUNNING) return;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * 8 + warp;
+  if (row >= p.n) return;
+  const T* kr = reinterpret_cast<const T*>(p.K) + row * p.ld;
+  const T* v = reinterpret_cast<const T*>(p.vring) + (long long)p.st->sel_v * p.mp;
+  T* unew = reinterpret_cast<T*>(p.uring) + (long long)(p.st->sel_u ^ 1) * p.n;
+  const T ai = reinterpret_cast<const T*>(p.a)[row];
+  if (MODE == MODE_KNOPP) {
+    T s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+    long long j = lane;
+    for (; j + 96 < p.m; j += 128) {
+      s0 = fma(kr[j], v[j], s0);
+      s1 = fma(kr[j + 32], v[j + 32], s1);
+      s2 = fma(kr[j + 64], v[j + 64], s2);
+      s3 = fma(kr[j + 96], v[j + 96], s3);
+    }
+    for (; j < p.m; j += 32) s0 = fma(kr[j], v[j], s0);
+    const T tot = warp_sum((s0 + s1) + (s2 + s3));
+    if (lane == 0) {
+      const T u = ai / tot;
+      unew[row] = u;
+      if (!finite_t(u)) atomicOr(&p.st->uflag, 1);
+    }
+  } else {
+    T mx = neg_inf<T>();
+    for (long long j = lane; j < p.m; j += 32) mx = max_t(mx, kr[j] + v[j]);
+    mx = warp_max(mx);
+    const T ref = (mx == neg_inf<T>()) ? (T)0 : mx;
+    T s0 = 0, s1 = 0;
+    long long j = lane;
+    for (; j + 32 < p.m; j += 64) {
+      s0 += exp_t((kr[j] + v[j]) - ref);
+      s1 += exp_t((kr[j + 32] + v[j + 32]) - ref);
+    }
+    for (; j < p.m; j += 32) s0 += exp_t((kr[j] + v[j]) - ref);
+    const T tot = warp_sum(s0 + s1);
+    if (lane == 0) unew[row] = ai - (ref + log_t(tot));
+  }
+}
+
+// KNOPP: partial_j = sum_i K_ij u_i ; LOG: partial_j = sum_i exp(K_ij + u_i + v_j)
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256) cols_kernel(const SplitParams p) {
+  if (p.st->status != p.expect_status) return;
+  const long long j = (long long)blockIdx.x * 256 + threadIdx.x;
+  const long long rows_per = (p.n + p.nsplit - 1) / p.nsplit;
+  const long long r0 = (long long)blockIdx.y * rows_per;
+  const long long r1 = (r0 + rows_per < p.n) ? r0 + rows_per : p.n;
+  if (j >= p.m) return;
+  const T* Kc = reinterpret_cast<const T*>(p.K) + j;
+  const T* u = reinterpret_cast<const T*>(p.uring) + (long long)(p.st->sel_u ^ p.u_slot_xor) * p.n;
+  T vj = (T)0;
+  if (MODE == MODE_LOG) vj = (reinterpret_cast<const T*>(p.vring) + (long long)p.st->sel_v * p.mp)[j];
+  T a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+  long long i = r0;
+  if (MODE == MODE_KNOPP) {
+    for (; i + 3 < r1; i += 4) {
+      a0 = fma(Kc[i * p.ld], u[i], a0);
+      a1 = fma(Kc[(i + 1) * p.ld], u[i + 1], a1);
+      a2 = fma(Kc[(i + 2) * p.ld], u[i + 2], a2);
+      a3 = fma(Kc[(i + 3) * p.ld], u[i + 3], a3);
+    }
+    for (; i < r1; ++i) a0 = fma(Kc[i * p.ld], u[i], a0);
+  } else {
+    for (; i + 1 < r1; i += 2) {
+      a0 += exp_t((Kc[i * p.ld] + u[i]) + vj);
+      a1 += exp_t((Kc[(i + 1) * p.ld] + u[i + 1]) + vj);
+    }
+    for (; i < r1; ++i) a0 += exp_t((Kc[i * p.ld] + u[i]) + vj);
+  }
+  reinterpret_cast<T*>(p.partials)[(long long)blockIdx.y * p.mp + j] = (a0 + a1) + (a2 + a3);
+}
+
+// Exact column log-sum-exp partials (online max): rows [0,nsplit) of `partials` = max, rows
+// [nsplit, 2 nsplit) = sum.  Used for the first v update of the log domain (u given) and as the
+// fallback when a row-frame column sum underflows.
+template <typename T>
+__global__ void __launch_bounds__(256) cols_lse_kernel(const SplitParams p) {
+  if (p.st->status != p.expect_status) return;
+  const long long j = (long long)blockIdx.x * 256 + threadIdx.x;
+  const long long rows_per = (p.n + p.nsplit - 1) / p.nsplit;
+  const long long r0 = (long long)blockIdx.y * rows_per;
+  const long long r1 = (r0 + rows_per < p.n) ? r0 + rows_per : p.n;
+  if (j >= p.m) return;
+  const T* Kc = reinterpret_cast<const T*>(p.K) + j;
+  const T* u = reinterpret_cast<const T*>(p.uring) + (long long)(p.st->sel_u ^ p.u_slot_xor) * p.n;
+  T mx = neg_inf<T>(), sm = (T)0;
+  for (long long i = r0; i < r1; ++i) {
+    const T x = Kc[i * p.ld] + u[i];
+    if (x == neg_inf<T>()) continue;
+    if (x > mx) {
+      sm = sm * exp_t(mx - x) + (T)1;  // exp(-inf) = 0 on the first hit
+      mx = x;
+    } else {
+      sm += exp_t(x - mx);
+    }
+  }
+  T* P = reinterpret_cast<T*>(p.partials);
+  P[(long long)blockIdx.y * p.mp + j] = mx;
+  P[(long long)(p.nsplit + blockIdx.y) * p.mp + j] = sm;
+}
+
+struct LseParams {
+  void* partials;
+  long long m, mp;
+  int nsplit;
+  const void* logb;
+  void* vring;
+  SolveState* st;
+  int expect_status;
+  int advance_iter;  // 0: seeding pass (iteration counter untouched), 1: fallback inside iteration
+  int max_iter;
+};
+// rows 2ns: local max, 2ns+1: max to be all-reduced(max), 2ns+2: rescaled sum to be all-reduced(sum)
+template <typename T>
+__global__ void __launch_bounds__(256) lse_combine_kernel(const LseParams p) {
+  if (p.st->status != p.expect_status) return;
+  const long long j = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (j >= p.m) return;
+  T* P = reinterpret_cast<T*>(p.partials);
+  T M = neg_inf<T>();
+  for (int y = 0; y < p.nsplit; ++y) M = max_t(M, P[(long long)y * p.mp + j]);
+  T S = (T)0;
+  for (int y = 0; y < p.nsplit; ++y) {
+    const T my = P[(long long)y * p.mp + j];
+    if (my != neg_inf<T>()) S += P[(long long)(p.nsplit + y) * p.mp + j] * exp_t(my - M);
+  }
+  P[(long long)(2 * p.nsplit) * p.mp + j] = M;
+  P[(long long)(2 * p.nsplit + 1) * p.mp + j] = M;
+  P[(long long)(2 * p.nsplit + 2) * p.mp + j] = S;
+}
+template <typename T>
+__global__ void __launch_bounds__(256) lse_rescale_kernel(const LseParams p) {
+  if (p.st->status != p.expect_status) return;
+  const long long j = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (j >= p.m) return;
+  T* P = reinterpret_cast<T*>(p.partials);
+  const T Ml = P[(long long)(2 * p.nsplit) * p.mp + j];
+  const T Mg = P[(long long)(2 * p.nsplit + 1) * p.mp + j];
+  T& S = P[(long long)(2 * p.nsplit + 2) * p.mp + j];
+  S = (Ml == neg_inf<T>()) ? (T)0 : S * exp_t(Ml - Mg);
+}
+template <typename T>
+__global__ void __launch_bounds__(256) lse_finish_kernel(const LseParams p) {
+  if (p.st->status != p.expect_status) return;
+  const long long j = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (j >= p.m) return;
+  const T* P = reinterpret_cast<const T*>(p.partials);
+  const T Mg = P[(long long)(2 * p.nsplit + 1) * p.mp + j];
+  const T S = P[(long long)(2 * p.nsplit + 2) * p.mp + j];
+  const int nxt = (p.st->sel_v + 1) % 3;
+  T* vnext = reinterpret_cast<T*>(p.vring) + (long long)nxt * p.mp;
+  vnext[j] = reinterpret_cast<const T*>(p.logb)[j] - (Mg + log_t(S));
+}
+__global__ void lse_advance_kernel(SolveState* st, int expect_status, int advance_iter) {
+  if (st->status != expect_status) return;
+  st->sel_v = (st->sel_v + 1) % 3;
+  if (advance_iter) st->iter += 1;
+  st->status = ST_RUNNING;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Finalize: column sums -> v update, marginal error, guard flags, stop decision (all on device).
+// ------------------------------------------------------------------------------------------------
+struct FinParams {
+  const void* src;      // nsrc rows of column sums (stride src_ld)
+  long long src_ld;
+  int nsrc;
+  const void* extra_flag;  // optional: T value != 0 means "some rank produced a non-finite u"
+  const void* b;
+  const void* logb;
+  void* vring;
+  void* cbuf;
+  long long m, mp;
+  SolveState* st;
+  double* blk_err;
+  double* err_hist;
+  int max_iter, check_every;
+  double stop_thr;
+  int init;             // KNOPP seeding pass: only v0 = b / (K^T u0) and its guard flags
+};
+
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
+  __shared__ double sred[256];
+  __shared__ int sflags;
+  __shared__ int s_last;
+  SolveState* st = p.st;
+  if (st->status != ST_RUNNING) return;
+  const int tid = threadIdx.x;
+  const int sel_v = st->sel_v;
+  const int nxt = (sel_v + 1) % 3;
+  const T* vcur = reinterpret_cast<const T*>(p.vring) + (long long)sel_v * p.mp;
+  T* vnext = reinterpret_cast<T*>(p.vring) + (long long)nxt * p.mp;
+  const T* src = reinterpret_cast<const T*>(p.src);
+  const T* b = reinterpret_cast<const T*>(p.b);
+  const T* logb = reinterpret_cast<const T*>(p.logb);
+  T* cbuf = reinterpret_cast<T*>(p.cbuf);
+  if (tid == 0) sflags = 0;
+  __syncthreads();
+
+  double e2 = 0.0;
+  int flags = 0;
+  for (long long j = (long long)blockIdx.x * 256 + tid; j < p.m; j += (long long)gridDim.x * 256) {
+    T c = (T)0;
+    for (int q = 0; q < p.nsrc; ++q) c += src[(long long)q * p.src_ld + j];
+    const T bj = b[j];
+    const T vj = vcur[j];
+    T vn;
+    if (MODE == MODE_KNOPP) {
+      const T d = vj * c - bj;  // column marginal of diag(u) K diag(v) minus b
+      e2 += (double)d * (double)d;
+      vn = bj / c;
+      if (c == (T)0) flags |= FLAG_CZERO;
+      if (!finite_t(vn)) flags |= FLAG_VBAD;
+    } else {
+      const T d = c - bj;
+      e2 += (double)d * (double)d;
+      vn = vj + (logb[j] - log_t(c));
+      if (!(c >= tiny_guard<T>())) flags |= 4;
+    }
+    cbuf[j] = c;
+    vnext[j] = vn;
+  }
+  sred[tid] = e2;
+  if (flags) atomicOr(&sflags, flags);
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (tid < o) sred[tid] += sred[tid + o];
+    __syncthreads();
+  }
+  if (tid == 0) {
+    p.blk_err[blockIdx.x] = sred[0];
+    if (sflags & 3) atomicOr(&st->next_flags, sflags & 3);
+    if (sflags & 4) atomicOr(&st->need_exact, 1);
+    __threadfence();
+    const unsigned int t = atomicAdd(&st->ticket, 1u);
+    s_last = (t == gridDim.x - 1) ? 1 : 0;
+  }
+  __syncthreads();
+  if (!s_last) return;
+
+  // ---- last block: deterministic error total + stop decision ----
+  __threadfence();
+  double x = 0.0;
+  for (unsigned int i = tid; i < gridDim.x; i += 256) x += __ldcg(&p.blk_err[i]);
+  sred[tid] = x;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (tid < o) sred[tid] += sred[tid + o];
+    __syncthreads();
+  }
+  if (tid != 0) return;
+  const int nflags = atomicOr(&st->next_flags, 0);
+  const int nexact = atomicOr(&st->need_exact, 0);
+  int uflag = atomicOr(&st->uflag, 0);
+  if (p.extra_flag != nullptr && *reinterpret_cast<const T*>(p.extra_flag) != (T)0) uflag = 1;
+  const int ii = st->iter;
+  if (p.init) {
+    st->sel_v = nxt;
+    st->cur_flags = nflags;
+  } else if (MODE == MODE_KNOPP && (st->cur_flags != 0 || uflag != 0)) {
+    // reference guard (_sinkhorn.py:633-645): come back to the previous (u, v) and stop
+    st->status = ST_NUMERR;
+    st->niter = ii;
+    st->sel_v = (sel_v + 2) % 3;
+  } else {
+    st->sel_u ^= 1;  // the u of this sweep becomes current
+    bool stop = false;
+    if (ii % p.check_every == 0) {
+      const double err = sqrt(sred[0]);
+      p.err_hist[st->n_err] = err;
+      st->n_err += 1;
+      st->last_err = err;
+      if (err < p.stop_thr) {
+        st->status = ST_CONVERGED;
+        st->niter = ii;
+        stop = true;
+      }
+    }
+    if (!stop) {
+      if (ii + 1 >= p.max_iter) {
+        st->status = ST_MAXITER;
+        st->niter = ii;
+      } else if (MODE == MODE_LOG && nexact) {
+        st->status = ST_PAUSE_EXACT;  // v_next unusable for some columns: exact column pass needed
+      } else {
+        st->sel_v = nxt;
+        st->iter = ii + 1;
+        st->cur_flags = nflags;
+      }
+    }
+  }
+  st->next_flags = 0;
+  st->uflag = 0;
+  st->need_exact = 0;
+  st->ticket = 0;
+  __threadfence();
+}
+
+// Row-sharded runs: collapse this rank's partial rows into the all-reduce buffer (m values + flag).
+template <typename T>
+__global__ void __launch_bounds__(256) reduce_partials_kernel(const void* partials, long long mp, int nsrc,
+                                                              void* cbuf, long long m, SolveState* st,
+                                                              int expect_status) {
+  if (st->status != expect_status) return;
+  const long long j = (long long)blockIdx.x * 256 + threadIdx.x;
+  const T* P = reinterpret_cast<const T*>(partials);
+  T* c = reinterpret_cast<T*>(cbuf);
+  if (j < m) {
+    T s = (T)0;
+    for (int q = 0; q < nsrc; ++q) s += P[(long long)q * mp + j];
+    c[j] = s;
+  } else if (j == m) {
+    c[m] = (T)(atomicOr(&st->uflag, 0) ? 1 : 0);
+  }
+}
+
+template <typename T>
+__global__ void export_kernel(const void* uring, const void* vring, long long n, long long m, long long mp,
+                              const SolveState* st, void* u_out, void* v_out) {
+  const T* u = reinterpret_cast<const T*>(uring) + (long long)st->sel_u * n;
+  const T* v = reinterpret_cast<const T*>(vring) + (long long)st->sel_v * mp;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (u_out != nullptr && i < n) reinterpret_cast<T*>(u_out)[i] = u[i];
+  if (v_out != nullptr && i < m) reinterpret_cast<T*>(v_out)[i] = v[i];
+}
+
+// ------------------------------------------------------------------------------------------------
+// Elementwise: Gibbs kernel / scaled cost, plan, loss.
+// ------------------------------------------------------------------------------------------------
+template <typename T, int OP>  // OP 0: exp(M / (-reg)) ; 1: -M / reg
+__global__ void __launch_bounds__(256) cost_transform_kernel(const T* __restrict__ M, T* __restrict__ out, long long n,
+                                                             long long m, long long ldM, long long ldO, T reg) {
+  const long long j0 = ((long long)blockIdx.y * 256 + threadIdx.x) * 4;
+  for (long long i = blockIdx.x; i < n; i += gridDim.x) {
+    const T* mr = M + i * ldM;
+    T* orow = out + i * ldO;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const long long j = j0 + k;
+      if (j < m) orow[j] = (OP == 0) ? exp_t(mr[j] / (-reg)) : (-mr[j]) / reg;
+    }
+  }
+}
+
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256) plan_kernel(const T* __restrict__ K, const T* __restrict__ u,
+                                                   const T* __restrict__ v, T* __restrict__ out, long long n,
+                                                   long long m, long long ldK, long long ldO) {
+  const long long j0 = ((long long)blockIdx.y * 256 + threadIdx.x) * 4;
+  for (long long i = blockIdx.x; i < n; i += gridDim.x) {
+    const T ui = u[i];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const long long j = j0 + k;
+      if (j < m) {
+        const T kij = K[i * ldK + j];
+        out[i * ldO + j] = (MODE == MODE_KNOPP) ? (ui * kij) * v[j] : exp_t((kij + ui) + v[j]);
+      }
+    }
+  }
+}
+
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256) loss_kernel(const T* __restrict__ K, const T* __restrict__ M,
+                                                   const T* __restrict__ u, const T* __restrict__ v, long long n,
+                                                   long long m, long long ldK, long long ldM, double* blk_out) {
+  __shared__ double sred[256];
+  double acc = 0.0;
+  for (long long i = blockIdx.x; i < n; i += gridDim.x) {
+    const T ui = u[i];
+    for (long long j = threadIdx.x; j < m; j += 256) {
+      const T kij = K[i * ldK + j];
+      const T g = (MODE == MODE_KNOPP) ? (ui * kij) * v[j] : exp_t((kij + ui) + v[j]);
+      acc += (double)(M[i * ldM + j] * g);
+    }
+  }
+  sred[threadIdx.x] = acc;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) sred[threadIdx.x] += sred[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) blk_out[blockIdx.x] = sred[0];
+}
+__global__ void sum_blocks_kernel(const double* blk, int nblk, double* out) {
+  __shared__ double sred[256];
+  double x = 0.0;
+  for (int i = threadIdx.x; i < nblk; i += 256) x += blk[i];
+  sred[threadIdx.x] = x;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) sred[threadIdx.x] += sred[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *out = sred[0];
+}
+
+}  // namespace b2ot

@@ -1,0 +1,47 @@
+// Host-side helpers shared by the b2ot translation units: thread-local error text,
+// launch counter, CUDA error check macro.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+
+namespace b2ot {
+
+void set_error(const char* fmt, ...);
+std::atomic<unsigned long long>& launch_counter();
+
+inline void count_launch(int n = 1) { launch_counter().fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+
+#define B2OT_CUDA(call)                                                                          \
+  do {                                                                                           \
+    cudaError_t e_ = (call);                                                                     \
+    if (e_ != cudaSuccess) {                                                                     \
+      ::b2ot::set_error("%s:%d: %s failed: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+      return -2;                                                                                 \
+    }                                                                                            \
+  } while (0)
+
+#define B2OT_CHECK_LAUNCH()                                                                      \
+  do {                                                                                           \
+    cudaError_t e_ = cudaGetLastError();                                                         \
+    if (e_ != cudaSuccess) {                                                                     \
+      ::b2ot::set_error("%s:%d: kernel launch failed: %s", __FILE__, __LINE__, cudaGetErrorString(e_)); \
+      return -3;                                                                                 \
+    }                                                                                            \
+    ::b2ot::count_launch();                                                                      \
+  } while (0)
+
+#define B2OT_REQUIRE(cond, ...)            \
+  do {                                     \
+    if (!(cond)) {                         \
+      ::b2ot::set_error(__VA_ARGS__);      \
+      return -1;                           \
+    }                                      \
+  } while (0)
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+}  // namespace b2ot

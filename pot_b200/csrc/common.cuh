@@ -176,6 +176,21 @@ __device__ __forceinline__ void st_cluster(uint32_t addr, double v) {
   asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
 }
 
+// One-sided DSMEM put: stores two values into a peer CTA's shared memory and signals that CTA's
+// mbarrier with the byte count (complete_tx) -- no fence, no separate arrive.
+__device__ __forceinline__ void st_async_v2(uint32_t dst_cluster_addr, float x, float y, uint32_t bar_cluster_addr) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];" ::"r"(
+                   dst_cluster_addr),
+               "f"(x), "f"(y), "r"(bar_cluster_addr)
+               : "memory");
+}
+__device__ __forceinline__ void st_async_v2(uint32_t dst_cluster_addr, double x, double y, uint32_t bar_cluster_addr) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f64 [%0], {%1, %2}, [%3];" ::"r"(
+                   dst_cluster_addr),
+               "d"(x), "d"(y), "r"(bar_cluster_addr)
+               : "memory");
+}
+
 // ---- bulk async copy global -> shared (TMA linear mode; completes on an mbarrier) ----
 __device__ __forceinline__ uint64_t l2_policy_evict_first() {
   uint64_t p;

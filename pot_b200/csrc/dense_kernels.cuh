@@ -6,8 +6,9 @@
 //     shared-memory ring with 1-D TMA bulk copies (cp.async.bulk + mbarrier tx), issued by one
 //     elected thread as soon as a stage has been drained.
 //   * All warps pull a tile into registers (freeing the stage at once), form the partial
-//     row sums (K v)_i of their slice, reduce them warp -> CTA -> cluster (DSMEM stores +
-//     remote mbarrier arrive), obtain u_i = a_i / (K v)_i, and immediately accumulate the tile's
+//     row sums (K v)_i of their slice; every warp pushes its partials into all CTAs of the
+//     cluster with one-sided DSMEM puts (st.async + mbarrier complete_tx: no fences, no CTA
+//     barrier), each warp then forms u_i = a_i / (K v)_i and immediately accumulates the tile's
 //     contribution u_i K_ij into per-thread column accumulators that live in registers for the
 //     whole sweep.  K is read from HBM exactly once per iteration (the reference makes two GEMV
 //     passes, ot/bregman/_sinkhorn.py:629-631).
@@ -55,13 +56,14 @@ __global__ void __launch_bounds__(NCT, 1) fused_sweep_kernel(const SweepParams p
   constexpr int VEC = Vec<T>::N;
   constexpr int R = rows_per_group(VPT);
   constexpr int PAY = (MODE == MODE_LOG) ? 2 : 1;
-  constexpr int NQ = R * PAY;
+  constexpr int NQ = R * PAY;          // payload values per warp per row group (always even)
+  constexpr int NCH = NQ / 2;          // ... sent as NCH two-element puts
   constexpr int WCAP = NCT * VPT * VEC;
+  constexpr int NSRCMAX = (R > 2) ? NCW : CSMAX * NCW;  // R > 2 only occurs with a single-CTA "cluster"
 
   __shared__ __align__(16) uint64_t full_bar[SMAX];
   __shared__ __align__(16) uint64_t exch_bar[2];
-  __shared__ __align__(16) T red[NCW][NQ];
-  __shared__ __align__(16) T exch[2][NQ][CSMAX];
+  __shared__ __align__(16) T exch[2][NSRCMAX][NQ];      // [parity][source warp of the cluster][payload]
   extern __shared__ __align__(128) unsigned char dyn_smem[];
   T* const stage_base = reinterpret_cast<T*>(dyn_smem);
 
@@ -84,6 +86,8 @@ __global__ void __launch_bounds__(NCT, 1) fused_sweep_kernel(const SweepParams p
   const T* const Kg = reinterpret_cast<const T*>(p.K);
   const uint32_t row_bytes = (uint32_t)wc * (uint32_t)sizeof(T);
   const uint64_t pol = p.use_hint ? l2_policy_evict_first() : 0ull;
+  const int nsrc = (int)csize * NCW;                              // warps in the cluster
+  const uint32_t exch_bytes = (uint32_t)nsrc * NQ * (uint32_t)sizeof(T);
 
   // Producer step (one elected thread): stream row group g into stage s with TMA bulk copies.
   auto issue_group = [&](long long g, int s) {
@@ -106,8 +110,8 @@ __global__ void __launch_bounds__(NCT, 1) fused_sweep_kernel(const SweepParams p
 
   if (tid == 0) {
     for (int s = 0; s < S; ++s) mbar_init(&full_bar[s], 1);
-    mbar_init(&exch_bar[0], csize);
-    mbar_init(&exch_bar[1], csize);
+    mbar_init(&exch_bar[0], 1);
+    mbar_init(&exch_bar[1], 1);
     fence_mbar_init();
     // prologue: fill the ring
     for (int s = 0; s < S; ++s) {
@@ -116,7 +120,7 @@ __global__ void __launch_bounds__(NCT, 1) fused_sweep_kernel(const SweepParams p
     }
   }
   __syncthreads();
-  cluster_sync_all();  // every CTA's barriers exist before any remote arrive
+  cluster_sync_all();  // every CTA's barriers exist before any remote put
 
   const T* vcur = reinterpret_cast<const T*>(p.vring) + (long long)sel_v * p.mp + col0;
   T* unew = reinterpret_cast<T*>(p.uring) + (long long)(sel_u ^ 1) * p.n;
@@ -136,6 +140,11 @@ __global__ void __launch_bounds__(NCT, 1) fused_sweep_kernel(const SweepParams p
 
   int cs_log2 = 0;
   while ((1u << cs_log2) < csize) ++cs_log2;
+  // this lane's put: payload chunk `my_ch` to peer CTA `my_peer`
+  const int my_peer = lane & ((int)csize - 1);
+  const int my_ch = lane >> cs_log2;
+  const bool sender = my_ch < NCH;
+  const uint32_t my_slot = crank * NCW + (uint32_t)warp;   // where this warp's payload lands in every CTA
 
   int s = 0;          // ring slot of the current group
   uint32_t ph = 0;    // its mbarrier phase parity
@@ -145,6 +154,8 @@ __global__ void __launch_bounds__(NCT, 1) fused_sweep_kernel(const SweepParams p
     const uint32_t eph = (uint32_t)((it >> 1) & 1);
     const long long row0 = g * R;
     const int rv = (p.n - row0) < R ? (int)(p.n - row0) : R;
+
+    if (tid == 0) mbar_arrive_expect_tx(&exch_bar[par], exch_bytes);  // arm this group's exchange
 
     T areg[R];
 #pragma unroll
@@ -166,7 +177,8 @@ __global__ void __launch_bounds__(NCT, 1) fused_sweep_kernel(const SweepParams p
       }
     }
 
-    // ---- phase A: partial row reductions over my column slice ----
+    // ---- phase A: this warp's partial row reductions over its columns ----
+    T pay[NQ];
     T wref[R];  // LOG: this warp's exp reference per row
     if (MODE == MODE_KNOPP) {
 #pragma unroll
@@ -180,25 +192,38 @@ __global__ void __launch_bounds__(NCT, 1) fused_sweep_kernel(const SweepParams p
             s1 = fma(elem(kreg[r][k], i + 1), elem(vreg[k], i + 1), s1);
           }
         }
-        const T tot = warp_sum(s0 + s1);
-        if (lane == 0) red[warp][r] = tot;
+        pay[r] = s0 + s1;
         wref[r] = (T)0;
       }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) pay[r] += __shfl_xor_sync(0xffffffffu, pay[r], o);
+      }
     } else {
+      T mx[R];
 #pragma unroll
       for (int r = 0; r < R; ++r) {
-        T mx = neg_inf<T>();
+        T m0 = neg_inf<T>();
 #pragma unroll
         for (int k = 0; k < VPT; ++k) {
 #pragma unroll
           for (int i = 0; i < VEC; ++i) {
             const T x = elem(kreg[r][k], i) + elem(vreg[k], i);
             elem(kreg[r][k], i) = x;
-            mx = max_t(mx, x);
+            m0 = max_t(m0, x);
           }
         }
-        mx = warp_max(mx);
-        const T ref = (mx == neg_inf<T>()) ? (T)0 : mx;
+        mx[r] = m0;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) mx[r] = max_t(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], o));
+      }
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const T ref = (mx[r] == neg_inf<T>()) ? (T)0 : mx[r];
         T sm0 = (T)0, sm1 = (T)0;
 #pragma unroll
         for (int k = 0; k < VPT; ++k) {
@@ -212,82 +237,57 @@ __global__ void __launch_bounds__(NCT, 1) fused_sweep_kernel(const SweepParams p
             sm1 += e1;
           }
         }
-        const T sm = warp_sum(sm0 + sm1);
         wref[r] = ref;
-        if (lane == 0) {
-          red[warp][2 * r] = mx;
-          red[warp][2 * r + 1] = sm;
-        }
+        pay[2 * r] = mx[r];
+        pay[2 * r + 1] = sm0 + sm1;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) pay[2 * r + 1] += __shfl_xor_sync(0xffffffffu, pay[2 * r + 1], o);
       }
     }
-    // Every warp has consumed its part of stage s (the values feed the reductions above), so
-    // after this barrier the stage can be refilled.
-    __syncthreads();
 
-    // ---- warp 0: refill the ring, CTA-level combine, push to every CTA of the cluster (DSMEM) ----
-    if (warp == 0) {
-      if (lane == 0) {
-        const long long gn = g + (long long)S * ncl;
-        if (gn < NG) issue_group(gn, s);
-      }
-      __syncwarp();
-      const int w = lane & 7;    // source warp
-      const int sub = lane >> 3; // 4 payload rows handled per step
-      if (MODE == MODE_KNOPP) {
+    // ---- push this warp's payload into every CTA of the cluster (st.async + complete_tx) ----
+    if (sender) {
+      T x0 = pay[0], x1 = pay[1];
 #pragma unroll
-        for (int q0 = 0; q0 < NQ; q0 += 4) {
-          const int q = q0 + sub;
-          T x = (q < NQ) ? red[w][q < NQ ? q : 0] : (T)0;
-          x += __shfl_xor_sync(0xffffffffu, x, 4);
-          x += __shfl_xor_sync(0xffffffffu, x, 2);
-          x += __shfl_xor_sync(0xffffffffu, x, 1);
-#pragma unroll
-          for (int qq = 0; qq < 4; ++qq) {
-            const T tot = __shfl_sync(0xffffffffu, x, qq * 8);
-            if (q0 + qq < NQ && lane < (int)csize)
-              st_cluster(mapa_u32(smem_u32(&exch[par][(q0 + qq) < NQ ? (q0 + qq) : 0][crank]), (uint32_t)lane), tot);
-          }
-        }
-      } else {
-#pragma unroll
-        for (int r0 = 0; r0 < R; r0 += 4) {
-          const int r = r0 + sub;
-          const int rc = r < R ? r : 0;
-          const T mxw = (r < R) ? red[w][2 * rc] : neg_inf<T>();
-          const T smw = (r < R) ? red[w][2 * rc + 1] : (T)0;
-          T M = mxw;
-          M = max_t(M, __shfl_xor_sync(0xffffffffu, M, 4));
-          M = max_t(M, __shfl_xor_sync(0xffffffffu, M, 2));
-          M = max_t(M, __shfl_xor_sync(0xffffffffu, M, 1));
-          T sc = (mxw == neg_inf<T>()) ? (T)0 : smw * exp_t(mxw - M);
-          sc += __shfl_xor_sync(0xffffffffu, sc, 4);
-          sc += __shfl_xor_sync(0xffffffffu, sc, 2);
-          sc += __shfl_xor_sync(0xffffffffu, sc, 1);
-#pragma unroll
-          for (int qq = 0; qq < 4; ++qq) {
-            const T Mq = __shfl_sync(0xffffffffu, M, qq * 8);
-            const T Sq = __shfl_sync(0xffffffffu, sc, qq * 8);
-            if (r0 + qq < R && lane < (int)csize) {
-              const int rr = (r0 + qq) < R ? (r0 + qq) : 0;
-              st_cluster(mapa_u32(smem_u32(&exch[par][2 * rr][crank]), (uint32_t)lane), Mq);
-              st_cluster(mapa_u32(smem_u32(&exch[par][2 * rr + 1][crank]), (uint32_t)lane), Sq);
-            }
-          }
+      for (int c = 1; c < NCH; ++c) {
+        if (my_ch == c) {
+          x0 = pay[2 * c];
+          x1 = pay[2 * c + 1];
         }
       }
-      if (lane < (int)csize) mbar_arrive_remote(mapa_u32(smem_u32(&exch_bar[par]), (uint32_t)lane));
+      const uint32_t dst = mapa_u32(smem_u32(&exch[par][my_slot][0]) + (uint32_t)(2 * my_ch * sizeof(T)), (uint32_t)my_peer);
+      const uint32_t bar = mapa_u32(smem_u32(&exch_bar[par]), (uint32_t)my_peer);
+      st_async_v2(dst, x0, x1, bar);
     }
 
-    // ---- all warps: wait for every CTA's payload, finish the row scalars ----
-    mbar_wait_cluster(&exch_bar[par], eph);
+    // ---- wait for the payloads of all warps of the cluster ----
+    // Completion also proves that every warp of this CTA has drained stage s: refill it.
+    mbar_wait(&exch_bar[par], eph);
+    if (tid == 0) {
+      const long long gn = g + (long long)S * ncl;
+      if (gn < NG) issue_group(gn, s);
+    }
 
     T urow[R];  // KNOPP: u_i ; LOG: f_i (row-frame factor for this warp)
     if (MODE == MODE_KNOPP) {
+      T tot[R];
 #pragma unroll
       for (int r = 0; r < R; ++r) {
-        T sum = (T)0;
-        for (int c = 0; c < (int)csize; ++c) sum += exch[par][r][c];
-        const T u = areg[r] / sum;
+        T x = (T)0;
+        for (int src = lane; src < nsrc; src += 32) x += exch[par][src][r];
+        tot[r] = x;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) tot[r] += __shfl_xor_sync(0xffffffffu, tot[r], o);
+      }
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const T u = areg[r] / tot[r];
         urow[r] = (r < rv) ? u : (T)0;
         if (crank == 0 && tid == r && r < rv) {
           unew[row0 + r] = u;
@@ -295,22 +295,35 @@ __global__ void __launch_bounds__(NCT, 1) fused_sweep_kernel(const SweepParams p
         }
       }
     } else {
-      // lane (r_l, c_l) combines the (max, sum) pair of CTA c_l for row r_l
-      const int r_l = lane >> cs_log2;
-      const int c_l = lane & ((int)csize - 1);
-      const bool lv = r_l < R;
-      const int rcl = lv ? r_l : 0;
-      const T mxc = lv ? exch[par][2 * rcl][c_l] : neg_inf<T>();
-      const T smc = lv ? exch[par][2 * rcl + 1][c_l] : (T)0;
-      T M = mxc;
-      for (int o = (int)csize >> 1; o > 0; o >>= 1) M = max_t(M, __shfl_xor_sync(0xffffffffu, M, o));
-      T sc = (mxc == neg_inf<T>()) ? (T)0 : smc * exp_t(mxc - M);
-      for (int o = (int)csize >> 1; o > 0; o >>= 1) sc += __shfl_xor_sync(0xffffffffu, sc, o);
-      const T lse_l = M + log_t(sc);
+      T M[R], Ssum[R];
 #pragma unroll
       for (int r = 0; r < R; ++r) {
-        const T lse = __shfl_sync(0xffffffffu, lse_l, (r << cs_log2) & 31);
-        const T u = areg[r] - lse;
+        T m0 = neg_inf<T>();
+        for (int src = lane; src < nsrc; src += 32) m0 = max_t(m0, exch[par][src][2 * r]);
+        M[r] = m0;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) M[r] = max_t(M[r], __shfl_xor_sync(0xffffffffu, M[r], o));
+      }
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        T x = (T)0;
+        for (int src = lane; src < nsrc; src += 32) {
+          const T ms = exch[par][src][2 * r];
+          if (ms != neg_inf<T>()) x += exch[par][src][2 * r + 1] * exp_t(ms - M[r]);
+        }
+        Ssum[r] = x;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) Ssum[r] += __shfl_xor_sync(0xffffffffu, Ssum[r], o);
+      }
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const T u = areg[r] - (M[r] + log_t(Ssum[r]));
         urow[r] = (r < rv) ? exp_t(wref[r] + u) : (T)0;
         if (crank == 0 && tid == r && r < rv) unew[row0 + r] = u;
       }

@@ -59,6 +59,15 @@ template <> __device__ __forceinline__ double tiny_guard<double>() { return 1e-2
 
 __device__ __forceinline__ float exp_t(float x) { return expf(x); }
 __device__ __forceinline__ double exp_t(double x) { return exp(x); }
+// Per-element exponential of the log-domain row pass, argument d = x - rowmax <= 0.  fp32: one FMUL
+// + MUFU.EX2 (ex2.approx); its error grows with |d|, i.e. it is at the 1e-7 level for the entries
+// that carry the sum and only reaches ~1e-5 relative on entries that are e^-100 of it.
+__device__ __forceinline__ float exp_elem(float d) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(d * 1.4426950408889634f));
+  return y;
+}
+__device__ __forceinline__ double exp_elem(double d) { return exp(d); }
 __device__ __forceinline__ float log_t(float x) { return logf(x); }
 __device__ __forceinline__ double log_t(double x) { return log(x); }
 __device__ __forceinline__ float max_t(float a, float b) { return fmaxf(a, b); }
@@ -188,6 +197,17 @@ __device__ __forceinline__ void st_async_v2(uint32_t dst_cluster_addr, double x,
   asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f64 [%0], {%1, %2}, [%3];" ::"r"(
                    dst_cluster_addr),
                "d"(x), "d"(y), "r"(bar_cluster_addr)
+               : "memory");
+}
+
+__device__ __forceinline__ void st_async_1(uint32_t dst_cluster_addr, float x, uint32_t bar_cluster_addr) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.f32 [%0], %1, [%2];" ::"r"(dst_cluster_addr),
+               "f"(x), "r"(bar_cluster_addr)
+               : "memory");
+}
+__device__ __forceinline__ void st_async_1(uint32_t dst_cluster_addr, double x, uint32_t bar_cluster_addr) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.f64 [%0], %1, [%2];" ::"r"(dst_cluster_addr),
+               "d"(x), "r"(bar_cluster_addr)
                : "memory");
 }
 

@@ -41,7 +41,7 @@ struct b2ot_dense {
   int err_cap;
   void *uring, *vring, *cbuf, *partials;
   // fused sweep configuration
-  int cs, ncl, stages, vpt, W, use_hint;
+  int cs, ncl, stages, vpt, nw, occ, W, use_hint;
   size_t dyn_smem;
   // split sweep / column-only pass configuration
   int nsplit, nsplit_lse;
@@ -173,24 +173,24 @@ extern "C" size_t b2ot_dense_workspace_bytes(int64_t n, int64_t m, int dtype, in
   return ws_layout(n, m, dtype, max_iter, check_every).total;
 }
 
-template <typename T, int VPT, int MODE>
+template <typename T, int VPT, int MODE, int NW, int OCC>
 static int config_fused(b2ot_dense* h) {
-  constexpr int R = rows_per_group(VPT);
-  constexpr int WCAP = NCT * VPT * Vec<T>::N;
+  constexpr int R = rows_per_group(VPT, NW, OCC);
+  constexpr int WCAP = NW * 32 * VPT * Vec<T>::N;
   const size_t stage_bytes = (size_t)R * WCAP * sizeof(T);
-  int stages = (int)((200 * 1024) / stage_bytes);
+  int stages = (int)(((OCC == 2 ? 100 : 200) * 1024) / stage_bytes);
   if (stages > SMAX) stages = SMAX;
   if (stages < 2) stages = 2;
   const char* env = getenv("B2OT_STAGES");
-  if (env && atoi(env) >= 2 && atoi(env) <= SMAX && (size_t)atoi(env) * stage_bytes <= 216 * 1024) stages = atoi(env);
+  if (env && atoi(env) >= 2 && atoi(env) <= SMAX && (size_t)atoi(env) * stage_bytes <= (size_t)(OCC == 2 ? 104 : 216) * 1024) stages = atoi(env);
   h->stages = stages;
   h->dyn_smem = stages * stage_bytes;
-  auto kern = fused_sweep_kernel<T, VPT, MODE>;
+  auto kern = fused_sweep_kernel<T, VPT, MODE, NW, OCC>;
   B2OT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->dyn_smem));
   if (h->cs > 8) B2OT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)h->cs, 1, 1);
-  cfg.blockDim = dim3(NCT, 1, 1);
+  cfg.blockDim = dim3(NW * 32, 1, 1);
   cfg.dynamicSmemBytes = h->dyn_smem;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -211,7 +211,7 @@ static int config_fused(b2ot_dense* h) {
   return 0;
 }
 
-template <typename T, int VPT, int MODE>
+template <typename T, int VPT, int MODE, int NW, int OCC>
 static int launch_fused(b2ot_dense* h) {
   SweepParams p;
   p.K = h->K;
@@ -229,7 +229,7 @@ static int launch_fused(b2ot_dense* h) {
   p.use_hint = h->use_hint;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(h->ncl * h->cs), 1, 1);
-  cfg.blockDim = dim3(NCT, 1, 1);
+  cfg.blockDim = dim3(NW * 32, 1, 1);
   cfg.dynamicSmemBytes = h->dyn_smem;
   cfg.stream = h->stream;
   cudaLaunchAttribute attr[1];
@@ -239,36 +239,49 @@ static int launch_fused(b2ot_dense* h) {
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  B2OT_CUDA(cudaLaunchKernelEx(&cfg, fused_sweep_kernel<T, VPT, MODE>, p));
+  B2OT_CUDA(cudaLaunchKernelEx(&cfg, fused_sweep_kernel<T, VPT, MODE, NW, OCC>, p));
   count_launch();
   return 0;
 }
 
-#define B2OT_DISPATCH_FUSED(FN, h)                                         \
-  do {                                                                     \
-    const int key_ = ((h)->dtype == B2OT_F64 ? 100 : 0) + ((h)->mode == B2OT_MODE_LOG ? 10 : 0) + \
-                     ((h)->vpt == 8 ? 3 : (h)->vpt == 4 ? 2 : (h)->vpt == 2 ? 1 : 0);             \
-    switch (key_) {                                                        \
-      case 0: return FN<float, 1, MODE_KNOPP>(h);                          \
-      case 1: return FN<float, 2, MODE_KNOPP>(h);                          \
-      case 2: return FN<float, 4, MODE_KNOPP>(h);                          \
-      case 3: return FN<float, 8, MODE_KNOPP>(h);                          \
-      case 10: return FN<float, 1, MODE_LOG>(h);                           \
-      case 11: return FN<float, 2, MODE_LOG>(h);                           \
-      case 12: return FN<float, 4, MODE_LOG>(h);                           \
-      case 13: return FN<float, 8, MODE_LOG>(h);                           \
-      case 100: return FN<double, 1, MODE_KNOPP>(h);                       \
-      case 101: return FN<double, 2, MODE_KNOPP>(h);                       \
-      case 102: return FN<double, 4, MODE_KNOPP>(h);                       \
-      case 103: return FN<double, 8, MODE_KNOPP>(h);                       \
-      case 110: return FN<double, 1, MODE_LOG>(h);                         \
-      case 111: return FN<double, 2, MODE_LOG>(h);                         \
-      case 112: return FN<double, 4, MODE_LOG>(h);                         \
-      case 113: return FN<double, 8, MODE_LOG>(h);                         \
-      default: break;                                                      \
-    }                                                                      \
-    set_error("internal: bad fused dispatch key %d", key_);                \
-    return -1;                                                             \
+#define B2OT_FUSED_CASES(FN, h, T, MODE)                          \
+  if ((h)->nw == 8 && (h)->occ == 1) {                             \
+    switch ((h)->vpt) {                                            \
+      case 1: return FN<T, 1, MODE, 8, 1>(h);                      \
+      case 2: return FN<T, 2, MODE, 8, 1>(h);                      \
+      case 4: return FN<T, 4, MODE, 8, 1>(h);                      \
+      case 8: return FN<T, 8, MODE, 8, 1>(h);                      \
+      default: break;                                              \
+    }                                                              \
+  } else if ((h)->nw == 8 && (h)->occ == 2) {                      \
+    switch ((h)->vpt) {                                            \
+      case 1: return FN<T, 1, MODE, 8, 2>(h);                      \
+      case 2: return FN<T, 2, MODE, 8, 2>(h);                      \
+      case 4: return FN<T, 4, MODE, 8, 2>(h);                      \
+      default: break;                                              \
+    }                                                              \
+  } else if ((h)->nw == 16) {                                      \
+    switch ((h)->vpt) {                                            \
+      case 1: return FN<T, 1, MODE, 16, 1>(h);                     \
+      case 2: return FN<T, 2, MODE, 16, 1>(h);                     \
+      case 4: return FN<T, 4, MODE, 16, 1>(h);                     \
+      default: break;                                              \
+    }                                                              \
+  }
+
+#define B2OT_DISPATCH_FUSED(FN, h)                                                   \
+  do {                                                                               \
+    if ((h)->dtype == B2OT_F32 && (h)->mode == B2OT_MODE_KNOPP) {                    \
+      B2OT_FUSED_CASES(FN, h, float, MODE_KNOPP)                                     \
+    } else if ((h)->dtype == B2OT_F32) {                                             \
+      B2OT_FUSED_CASES(FN, h, float, MODE_LOG)                                       \
+    } else if ((h)->mode == B2OT_MODE_KNOPP) {                                       \
+      B2OT_FUSED_CASES(FN, h, double, MODE_KNOPP)                                    \
+    } else {                                                                         \
+      B2OT_FUSED_CASES(FN, h, double, MODE_LOG)                                      \
+    }                                                                                \
+    set_error("internal: bad fused dispatch (nw=%d vpt=%d)", (h)->nw, (h)->vpt);     \
+    return -1;                                                                       \
   } while (0)
 
 static int dispatch_config_fused(b2ot_dense* h) { B2OT_DISPATCH_FUSED(config_fused, h); }
@@ -281,15 +294,25 @@ static bool plan_fused(b2ot_dense* h) {
   if (h->m % vec != 0 || h->ld % vec != 0) return false;
   if (((uintptr_t)h->K) % 16 != 0) return false;
   if (h->n < 1 || h->m < vec) return false;
-  const long long wcap8 = (long long)NCT * 8 * vec;
-  int max_cs = 8;
+  // CTA shape: 16 warps for the MUFU-heavy log domain, 8 warps for the scaling domain
+  h->nw = 8;
+  h->occ = 1;
+  const char* envw = getenv("B2OT_WARPS");
+  if (envw && (atoi(envw) == 8 || atoi(envw) == 16)) h->nw = atoi(envw);
+  const char* envo = getenv("B2OT_OCC");
+  if (envo && (atoi(envo) == 1 || atoi(envo) == 2)) h->occ = atoi(envo);
+  if (h->nw == 16) h->occ = 1;
+  const int vptmax = (h->nw == 8 && h->occ == 1) ? 8 : 4;
+  const long long nct = 32LL * h->nw;
+  const long long wcapmax = nct * vptmax * vec;
+  int max_cs = (h->occ == 2) ? 16 : 8;
   const char* env = getenv("B2OT_MAX_CLUSTER");
   if (env && atoi(env) >= 1 && atoi(env) <= CSMAX) max_cs = atoi(env);
-  if (h->m <= wcap8) {
+  if (h->m <= wcapmax) {
     h->cs = 1;
-    h->vpt = 8;
-    for (int vpt = 1; vpt <= 8; vpt *= 2) {
-      if ((long long)NCT * vpt * vec >= h->m) {
+    h->vpt = vptmax;
+    for (int vpt = 1; vpt <= vptmax; vpt *= 2) {
+      if (nct * vpt * vec >= h->m) {
         h->vpt = vpt;
         break;
       }
@@ -297,10 +320,10 @@ static bool plan_fused(b2ot_dense* h) {
     h->W = (int)h->m;
   } else {
     int cs = 2;
-    while (cs <= max_cs && (long long)cs * wcap8 < h->m) cs *= 2;
+    while (cs <= max_cs && (long long)cs * wcapmax < h->m) cs *= 2;
     if (cs > max_cs) return false;
     h->cs = cs;
-    h->vpt = 8;
+    h->vpt = vptmax;
     long long w = (h->m + cs - 1) / cs;
     w = (w + vec - 1) / vec * vec;
     h->W = (int)w;

@@ -29,13 +29,19 @@ namespace b2ot {
 constexpr int MODE_KNOPP = 0;
 constexpr int MODE_LOG = 1;
 
-constexpr int NCW = 8;            // warps per CTA of the fused sweep
-constexpr int NCT = NCW * 32;     // threads per CTA (8 warps = 2 per SM sub-partition: full 255-register budget)
+// The fused sweep comes in three CTA shapes:
+//   NW = 8,  OCC = 1: 255-register budget, 64 K values per thread per row group (scaling domain);
+//   NW = 16, OCC = 1: 128 registers, half the per-thread work, 4 warps per SM sub-partition;
+//   NW = 8,  OCC = 2: 128 registers, half-width column slices, TWO independent CTAs per SM so that
+//                     one CTA's MUFU-heavy row pass overlaps the other's exchange/combine latency.
 constexpr int SMAX = 8;           // max pipeline stages
 constexpr int CSMAX = 16;         // max cluster size
 constexpr int NPMAX = 160;        // rows of the partial-sum scratch (>= clusters in a grid)
 
-__host__ __device__ constexpr int rows_per_group(int vpt) { return vpt >= 2 ? 16 / vpt : 8; }
+// rows per group: the register tile holds R x VPT vectors = 16 (NW = 8) or 8 (NW = 16) vectors per thread
+__host__ __device__ constexpr int rows_per_group(int vpt, int nw, int occ) {
+  return ((nw == 8 && occ == 1) ? 16 : 8) / vpt > 8 ? 8 : ((nw == 8 && occ == 1) ? 16 : 8) / vpt;
+}
 
 struct SweepParams {
   const void* K;        // n x m, leading dimension ld (elements)
@@ -50,11 +56,12 @@ struct SweepParams {
   int use_hint;         // L2 evict-first on the K stream (K much larger than L2)
 };
 
-template <typename T, int VPT, int MODE>
-__global__ void __launch_bounds__(NCT, 1) fused_sweep_kernel(const SweepParams p) {
+template <typename T, int VPT, int MODE, int NCW, int OCC>
+__global__ void __launch_bounds__(NCW * 32, OCC) fused_sweep_kernel(const SweepParams p) {
   using V = typename Vec<T>::type;
   constexpr int VEC = Vec<T>::N;
-  constexpr int R = rows_per_group(VPT);
+  constexpr int NCT = NCW * 32;
+  constexpr int R = rows_per_group(VPT, NCW, OCC);
   constexpr int PAY = (MODE == MODE_LOG) ? 2 : 1;
   constexpr int NQ = R * PAY;          // payload values per warp per row group (always even)
   constexpr int NCH = NQ / 2;          // ... sent as NCH two-element puts
@@ -138,6 +145,8 @@ __global__ void __launch_bounds__(NCT, 1) fused_sweep_kernel(const SweepParams p
     fill(acc[k], (T)0);
   }
 
+  const bool full_cols = ((VPT - 1) * NCT + tid) * VEC + VEC <= wc;  // all of this thread's vectors are in range
+
   int cs_log2 = 0;
   while ((1u << cs_log2) < csize) ++cs_log2;
   // this lane's put: payload chunk `my_ch` to peer CTA `my_peer`
@@ -164,16 +173,25 @@ __global__ void __launch_bounds__(NCT, 1) fused_sweep_kernel(const SweepParams p
     // ---- tile: shared -> registers ----
     mbar_wait(&full_bar[s], ph);
     V kreg[R][VPT];
+    if (full_cols && rv == R) {  // interior tile: unmasked loads
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
-      const T* srow = stage_base + ((size_t)s * R + r) * WCAP;
+      for (int r = 0; r < R; ++r) {
+        const T* srow = stage_base + ((size_t)s * R + r) * WCAP + tid * VEC;
 #pragma unroll
-      for (int k = 0; k < VPT; ++k) {
-        const int e = (k * NCT + tid) * VEC;
-        if (r < rv && e < wc)
-          kreg[r][k] = *reinterpret_cast<const V*>(srow + e);
-        else
-          fill(kreg[r][k], MODE == MODE_LOG ? neg_inf<T>() : (T)0);
+        for (int k = 0; k < VPT; ++k) kreg[r][k] = *reinterpret_cast<const V*>(srow + k * NCT * VEC);
+      }
+    } else {
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const T* srow = stage_base + ((size_t)s * R + r) * WCAP;
+#pragma unroll
+        for (int k = 0; k < VPT; ++k) {
+          const int e = (k * NCT + tid) * VEC;
+          if (r < rv && e < wc)
+            kreg[r][k] = *reinterpret_cast<const V*>(srow + e);
+          else
+            fill(kreg[r][k], MODE == MODE_LOG ? neg_inf<T>() : (T)0);
+        }
       }
     }
 
@@ -229,8 +247,8 @@ __global__ void __launch_bounds__(NCT, 1) fused_sweep_kernel(const SweepParams p
         for (int k = 0; k < VPT; ++k) {
 #pragma unroll
           for (int i = 0; i < VEC; i += 2) {
-            const T e0 = exp_t(elem(kreg[r][k], i) - ref);
-            const T e1 = exp_t(elem(kreg[r][k], i + 1) - ref);
+            const T e0 = exp_elem(elem(kreg[r][k], i) - ref);
+            const T e1 = exp_elem(elem(kreg[r][k], i + 1) - ref);
             elem(kreg[r][k], i) = e0;
             elem(kreg[r][k], i + 1) = e1;
             sm0 += e0;

@@ -1,0 +1,6 @@
+#!/bin/bash
+mkdir -p gpurun_out
+export B2OT_WARPS=8
+python scripts/prof_case.py --mode log --n 16384 --m 16384 --iters 3 > gpurun_out/plain.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:fused_sweep -s 4 -c 1 -f -o gpurun_out/prof_log16k_v2 python scripts/prof_case.py --mode log --n 16384 --m 16384 --iters 3 > gpurun_out/ncu2.log 2>&1
+tail -2 gpurun_out/ncu2.log

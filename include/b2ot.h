@@ -86,6 +86,9 @@ int b2ot_dense_set_allreduce(b2ot_dense* handle, b2ot_allreduce_fn fn, void* ctx
 int b2ot_dense_init(b2ot_dense* handle, const void* u0, const void* v0);
 /* enqueue n_iters iterations (each: one sweep over K + one finalize); no host sync */
 int b2ot_dense_iterate(b2ot_dense* handle, int n_iters);
+/* measurement aid: run n_iters iterations with CUDA events (recorded on the solve's stream) around every
+ * sweep launch; returns the average duration of the sweep alone and of a whole iteration (milliseconds) */
+int b2ot_dense_profile(b2ot_dense* handle, int n_iters, float* sweep_ms_avg, float* iter_ms_avg);
 /* synchronise the stream and read the device status word; also services the log-domain
  * exact-column fallback when the device asked for it */
 int b2ot_dense_poll(b2ot_dense* handle, int* status, int* iter);

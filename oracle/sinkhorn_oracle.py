@@ -66,6 +66,32 @@ def _as_arrays(a, b, M):
     return a, b, M
 
 
+def knopp_loop(K, Kp, b, u, v, numItermax, stopThr, hist):
+    """The hot loop of sinkhorn_knopp (ot/bregman/_sinkhorn.py:626-663), split out so bench.py can time
+    the iterations without the one-off K / Kp / plan passes.  Returns (u, v, last index, stopped)."""
+    multi = b.ndim > 1
+    ii = 0
+    for ii in range(numItermax):
+        u_old, v_old = u, v
+        KtU = np.dot(K.T, u)
+        v = b / KtU
+        u = 1.0 / np.dot(Kp, v)
+        if (np.any(KtU == 0) or np.any(np.isnan(u)) or np.any(np.isnan(v))
+                or np.any(np.isinf(u)) or np.any(np.isinf(v))):
+            warnings.warn("Warning: numerical errors at iteration %d" % ii)
+            return u_old, v_old, ii, True
+        if ii % 10 == 0:
+            if multi:
+                marg = np.einsum("ik,ij,jk->jk", u, K, v)
+            else:
+                marg = np.einsum("i,ij,j->j", u, K, v)
+            err = np.linalg.norm(marg - b)
+            hist["err"].append(err)
+            if err < stopThr:
+                return u, v, ii, True
+    return u, v, ii, False
+
+
 def sinkhorn_knopp(a, b, M, reg, numItermax=1000, stopThr=1e-9, log=False,
                    warn=True, warmstart=None):
     """Scaling-domain Sinkhorn-Knopp (ot/bregman/_sinkhorn.py:588-687).
@@ -88,29 +114,7 @@ def sinkhorn_knopp(a, b, M, reg, numItermax=1000, stopThr=1e-9, log=False,
         u, v = np.exp(warmstart[0]), np.exp(warmstart[1])
     K = np.exp(M / (-reg))
     Kp = (1 / a).reshape(-1, 1) * K
-    ii = 0
-    converged_or_broke = False
-    for ii in range(numItermax):
-        u_old, v_old = u, v
-        KtU = np.dot(K.T, u)
-        v = b / KtU
-        u = 1.0 / np.dot(Kp, v)
-        if (np.any(KtU == 0) or np.any(np.isnan(u)) or np.any(np.isnan(v))
-                or np.any(np.isinf(u)) or np.any(np.isinf(v))):
-            warnings.warn("Warning: numerical errors at iteration %d" % ii)
-            u, v = u_old, v_old
-            converged_or_broke = True
-            break
-        if ii % 10 == 0:
-            if multi:
-                marg = np.einsum("ik,ij,jk->jk", u, K, v)
-            else:
-                marg = np.einsum("i,ij,j->j", u, K, v)
-            err = np.linalg.norm(marg - b)
-            hist["err"].append(err)
-            if err < stopThr:
-                converged_or_broke = True
-                break
+    u, v, ii, converged_or_broke = knopp_loop(K, Kp, b, u, v, numItermax, stopThr, hist)
     if not converged_or_broke and warn:
         warnings.warn(_NOCONV)
     hist["niter"] = ii

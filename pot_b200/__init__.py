@@ -14,8 +14,8 @@ from . import _lib
 
 _lib.load()  # fail loudly when the CUDA library is missing
 
-from . import bregman  # noqa: E402
+from . import bregman, host, sharded  # noqa: E402
 from .bregman import sinkhorn, sinkhorn2, sinkhorn_knopp, sinkhorn_log  # noqa: E402
 
 __version__ = "0.1.0"
-__all__ = ["bregman", "sinkhorn", "sinkhorn2", "sinkhorn_knopp", "sinkhorn_log"]
+__all__ = ["bregman", "host", "sharded", "sinkhorn", "sinkhorn2", "sinkhorn_knopp", "sinkhorn_log"]

@@ -110,6 +110,13 @@ class DenseSolver:
         with torch.cuda.device(self.device):
             _lib.check(self.lib.b2ot_dense_iterate(self.h, int(k)), "b2ot_dense_iterate")
 
+    def profile(self, k):
+        """k iterations with CUDA events around each sweep launch -> (sweep_ms_avg, iter_ms_avg)."""
+        a, b = C.c_float(), C.c_float()
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.b2ot_dense_profile(self.h, int(k), C.byref(a), C.byref(b)), "b2ot_dense_profile")
+        return a.value, b.value
+
     def poll(self):
         st, it = C.c_int(), C.c_int()
         with torch.cuda.device(self.device):

@@ -35,6 +35,7 @@ PROTOTYPES = {
     "b2ot_dense_set_allreduce": (C.c_int, [C.c_void_p, ALLREDUCE_FN, C.c_void_p]),
     "b2ot_dense_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "b2ot_dense_iterate": (C.c_int, [C.c_void_p, C.c_int]),
+    "b2ot_dense_profile": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "b2ot_dense_poll": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "b2ot_dense_solve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int),
                                    C.POINTER(C.c_int), C.POINTER(C.c_int)]),

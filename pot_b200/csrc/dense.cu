@@ -3,6 +3,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <vector>
 
 #include "../../include/b2ot.h"
 #include "dense_kernels.cuh"
@@ -616,6 +617,46 @@ extern "C" int b2ot_dense_init(b2ot_dense* h, const void* u0, const void* v0) {
 extern "C" int b2ot_dense_iterate(b2ot_dense* h, int n_iters) {
   B2OT_REQUIRE(h != nullptr, "b2ot_dense_iterate: null handle");
   return h->dtype == B2OT_F32 ? dense_iterate_t<float>(h, n_iters) : dense_iterate_t<double>(h, n_iters);
+}
+
+// Run n_iters iterations with CUDA events bracketing every sweep launch (events are recorded on the
+// launch stream).  Reports the average duration of the sweep kernel(s) alone and of a whole iteration.
+extern "C" int b2ot_dense_profile(b2ot_dense* h, int n_iters, float* sweep_ms_avg, float* iter_ms_avg) {
+  B2OT_REQUIRE(h != nullptr && n_iters >= 1 && n_iters <= 4096, "b2ot_dense_profile: bad arguments");
+  std::vector<cudaEvent_t> ev(2 * (size_t)n_iters + 1);
+  for (auto& e : ev) B2OT_CUDA(cudaEventCreate(&e));
+  int rc = 0;
+  for (int it = 0; it < n_iters && rc == 0; ++it) {
+    B2OT_CUDA(cudaEventRecord(ev[2 * it], h->stream));
+    int nsrc = 0;
+    if (h->variant == B2OT_VARIANT_FUSED) {
+      rc = dispatch_launch_fused(h);
+      nsrc = h->ncl;
+    } else {
+      rc = h->dtype == B2OT_F32 ? launch_rows<float>(h) : launch_rows<double>(h);
+      if (rc == 0) rc = h->dtype == B2OT_F32 ? launch_cols<float>(h, 1) : launch_cols<double>(h, 1);
+      nsrc = h->nsplit;
+    }
+    if (rc) break;
+    B2OT_CUDA(cudaEventRecord(ev[2 * it + 1], h->stream));
+    rc = h->dtype == B2OT_F32 ? launch_finalize<float>(h, nsrc, 0) : launch_finalize<double>(h, nsrc, 0);
+  }
+  if (rc == 0) {
+    B2OT_CUDA(cudaEventRecord(ev[2 * n_iters], h->stream));
+    B2OT_CUDA(cudaStreamSynchronize(h->stream));
+    double sweep = 0.0;
+    for (int it = 0; it < n_iters; ++it) {
+      float ms = 0.f;
+      B2OT_CUDA(cudaEventElapsedTime(&ms, ev[2 * it], ev[2 * it + 1]));
+      sweep += ms;
+    }
+    float total = 0.f;
+    B2OT_CUDA(cudaEventElapsedTime(&total, ev[0], ev[2 * n_iters]));
+    if (sweep_ms_avg) *sweep_ms_avg = (float)(sweep / n_iters);
+    if (iter_ms_avg) *iter_ms_avg = total / n_iters;
+  }
+  for (auto& e : ev) cudaEventDestroy(e);
+  return rc;
 }
 
 extern "C" int b2ot_dense_poll(b2ot_dense* h, int* status, int* iter) {

@@ -112,6 +112,31 @@ size_t b2ot_dense_loss_scratch_bytes(int64_t n, int64_t m);
 int b2ot_dense_loss(int mode, int dtype, const void* K, const void* M, const void* u, const void* v, int64_t n,
                     int64_t m, int64_t ldK, int64_t ldM, double* loss_dev, void* scratch_dev, void* stream);
 
+/* ---- batched Sinkhorn (ot.batch): B independent n x m problems, each solved on chip ----
+ * Replaces bregman_projection_batch (ot/batch/_utils.py:46-162; mode KNOPP, potentials = scalings f, g),
+ * bregman_log_projection_batch (ot/batch/_utils.py:165-290; mode LOG, potentials = log-scalings u, v) and
+ * the value epilogue of solve_batch (ot/batch/_linear.py:317-345, entropy_batch ot/batch/_utils.py:4-22).
+ *
+ *   X (B, n, m) contiguous: `transform` 0 = X is the kernel K (KNOPP) / log-kernel (LOG) itself,
+ *                           1 = X is the cost M, K = exp(-M/reg) (_linear.py:323), 2 = X is M, K = -M/reg (:318);
+ *   a (B, n), b (B, m); pa (B, n), pb (B, m) receive the potentials;
+ *   T_out / logT_out (B, n, m), value_linear / value_reg (B doubles, device) may be null;
+ *   value_linear = sum M * T needs Mval (B, n, m); value_reg = sum T log(T + 1e-16) (reg_type 1, "entropy")
+ *   or sum T log(T / (a b^T) + 1e-16) (reg_type 2, "kl"): the caller forms value = value_linear + reg * value_reg;
+ *   update order f then g; every 10th iteration (it % 10 == 0) the maximum over the batch of the L2 row-marginal
+ *   violation is tested against tol with `<` on the device (:144-149, :273-278);
+ *   *n_iters (host, may be null) = last iteration index, as the reference reports it.  Reading it synchronises
+ *   the stream; with tol <= 0 the whole solve is a single launch and nothing synchronises.
+ * Returns -4 when the shape does not fit the on-chip solver (see b2ot_batch_config). */
+#define B2OT_BATCH_FORCE_EXACT 1 /* flags: always use the exact column pass of the log domain (test hook) */
+size_t b2ot_batch_workspace_bytes(int64_t B);
+int b2ot_batch_config(int mode, int dtype, int64_t n, int64_t m, int* cluster_size, int* smem_bytes,
+                      int* cols_per_lane);
+int b2ot_batch_solve(int mode, int dtype, int64_t B, int64_t n, int64_t m, const void* X, int transform, double reg,
+                     const void* Mval, const void* a, const void* b, void* pa, void* pb, void* T_out, void* logT_out,
+                     double* value_linear, double* value_reg, int reg_type, int max_iter, double tol, void* workspace,
+                     size_t workspace_bytes, int* n_iters, int flags, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

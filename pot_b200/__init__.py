@@ -14,8 +14,10 @@ from . import _lib
 
 _lib.load()  # fail loudly when the CUDA library is missing
 
-from . import bregman, host, sharded  # noqa: E402
+from . import batch, bregman, host, sharded, utils  # noqa: E402
+from .batch import solve_batch  # noqa: E402
 from .bregman import sinkhorn, sinkhorn2, sinkhorn_knopp, sinkhorn_log  # noqa: E402
 
 __version__ = "0.1.0"
-__all__ = ["bregman", "host", "sharded", "sinkhorn", "sinkhorn2", "sinkhorn_knopp", "sinkhorn_log"]
+__all__ = ["batch", "bregman", "host", "sharded", "utils", "sinkhorn", "sinkhorn2", "sinkhorn_knopp", "sinkhorn_log",
+           "solve_batch"]

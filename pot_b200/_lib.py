@@ -15,6 +15,7 @@ MODE_KNOPP, MODE_LOG = 0, 1
 ST_RUNNING, ST_CONVERGED, ST_NUMERR, ST_MAXITER = 0, 1, 2, 3
 VARIANT_AUTO, VARIANT_FUSED, VARIANT_SPLIT = 0, 1, 2
 OP_SUM, OP_MAX = 0, 1
+BATCH_FORCE_EXACT = 1
 
 ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_void_p)
 
@@ -48,6 +49,13 @@ PROTOTYPES = {
     "b2ot_dense_loss_scratch_bytes": (C.c_size_t, [C.c_int64, C.c_int64]),
     "b2ot_dense_loss": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                   C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b2ot_batch_workspace_bytes": (C.c_size_t, [C.c_int64]),
+    "b2ot_batch_config": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_int64, C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                    C.POINTER(C.c_int)]),
+    "b2ot_batch_solve": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_int,
+                                   C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double,
+                                   C.c_void_p, C.c_size_t, C.POINTER(C.c_int), C.c_int, C.c_void_p]),
 }
 
 _lib = None

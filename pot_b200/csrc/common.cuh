@@ -41,6 +41,9 @@ struct __align__(16) SolveState {
   double pad1;
 };
 
+constexpr int MODE_KNOPP = 0;  // scaling domain
+constexpr int MODE_LOG = 1;    // log domain
+
 constexpr int FLAG_CZERO = 1;
 constexpr int FLAG_VBAD = 2;
 

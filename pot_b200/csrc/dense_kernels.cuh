@@ -26,9 +26,6 @@
 
 namespace b2ot {
 
-constexpr int MODE_KNOPP = 0;
-constexpr int MODE_LOG = 1;
-
 // The fused sweep comes in three CTA shapes:
 //   NW = 8,  OCC = 1: 255-register budget, 64 K values per thread per row group (scaling domain);
 //   NW = 16, OCC = 1: 128 registers, half the per-thread work, 4 warps per SM sub-partition;

@@ -178,7 +178,11 @@ def test_log_underflow_falls_back():
     r = ot.solve_batch(dev(M), 1.0, dev(a), dev(b), max_iter=20, tol=0, solver="log_sinkhorn")
     assert torch.isfinite(r.plan).all() and torch.isfinite(r.potentials[1]).all()
     logclose(r.potentials[1], ref["potentials"][1], 1e-4, "v")
-    close(r.plan, ref["plan"], 1e-4, "plan")
+    # K, u, v are O(1e3) here: one fp32 ulp of the exponent K + u + v is ~1e-4, so two correctly rounded fp32
+    # evaluations of the plan differ by ~1e-3 relative.  Compare with the fp64 oracle at that conditioning.
+    ref64 = orc.solve_batch(M.astype(np.float64), 1.0, a.astype(np.float64), b.astype(np.float64), max_iter=20,
+                            tol=0, solver="log_sinkhorn")
+    close(r.plan, ref64["plan"], 5e-3, "plan")
 
 
 def test_stop_test_couples_the_batch():

@@ -137,6 +137,56 @@ int b2ot_batch_solve(int mode, int dtype, int64_t B, int64_t n, int64_t m, const
                      double* value_linear, double* value_reg, int reg_type, int max_iter, double tol, void* workspace,
                      size_t workspace_bytes, int* n_iters, int flags, void* stream);
 
+/* ---- online-cost (empirical) Sinkhorn: cost rebuilt from the point clouds, never materialised ----
+ * Replaces the lazy branch of ot.bregman.empirical_sinkhorn (ot/bregman/_empirical.py:193-271): log-domain
+ * updates f = log a - LSE_j(g_j - C_ij/reg), g = log b - LSE_i(f_i - C_ij/reg) (f first, :218-233) with
+ * C = max(|x|^2 + |y|^2 - 2 x.y, 0) (ot/utils.py:292-299; metric EUCLIDEAN takes the square root, :300-301);
+ * every 10th iteration ((it + 1) % 10 == 0) the L1 violation of the ROW marginal is tested with `<=` (:235-256),
+ * on the device.  (f, g) are log-scalings, as the reference returns them.
+ *
+ *   Xs (n x d, leading dimension ldXs), Xt (m x d), a / loga (n), logb (m): device pointers kept by the handle;
+ *   row sharding: n = LOCAL source points, Xt / g / logb replicated; with an all-reduce hook installed the column
+ *   log-sum-exp partials are combined across ranks (one max + one sum all-reduce of m values per iteration) and
+ *   the marginal check is summed (one double, every 10th iteration). */
+#define B2OT_METRIC_SQEUCLIDEAN 0
+#define B2OT_METRIC_EUCLIDEAN 1
+#define B2OT_EMP_AUTO 0   /* tensor-core sweep (tcgen05, 3xTF32) when dtype/shape allow it, else the register-tiled sweep */
+#define B2OT_EMP_SIMT 1   /* register-tiled FMA sweep: any d, fp32 and fp64 */
+#define B2OT_EMP_TC 2     /* tcgen05 sweep: fp32, sqeuclidean */
+typedef struct b2ot_emp b2ot_emp;
+size_t b2ot_emp_workspace_bytes(int64_t n, int64_t m, int dtype, int max_iter);
+int b2ot_emp_create(b2ot_emp** handle, int dtype, int64_t n, int64_t m, int d, const void* Xs, int64_t ldXs,
+                    const void* Xt, int64_t ldXt, const void* a, const void* loga, const void* logb, double reg,
+                    int metric, void* workspace, size_t workspace_bytes, int max_iter, double stop_thr, int variant,
+                    void* stream);
+int b2ot_emp_set_allreduce(b2ot_emp* handle, b2ot_allreduce_fn fn, void* ctx);
+/* enqueue: load the initial potentials f0 (n), g0 (m) and compute the squared norms */
+int b2ot_emp_init(b2ot_emp* handle, const void* f0, const void* g0);
+/* enqueue n_iters iterations (row sweep, f update + pending check, column sweep, g update); no host sync */
+int b2ot_emp_iterate(b2ot_emp* handle, int n_iters);
+int b2ot_emp_poll(b2ot_emp* handle, int* status, int* iter);
+/* init + iterate until status != running, polling every `poll_every` iterations (<= 0: only at the end) */
+int b2ot_emp_solve(b2ot_emp* handle, const void* f0, const void* g0, int poll_every, int* status, int* niter,
+                   int* n_err);
+int b2ot_emp_export(b2ot_emp* handle, void* f_out, void* g_out, double* err_host, int err_capacity, int* n_err);
+int b2ot_emp_destroy(b2ot_emp* handle);
+
+/* cost matrix out = dist(X, Y) (ot.dist / euclidean_distances, ot/utils.py:270-307, :400-526), metrics above;
+ * scratch_dev >= b2ot_dist_scratch_bytes(n, m, dtype) */
+size_t b2ot_dist_scratch_bytes(int64_t n, int64_t m, int dtype);
+int b2ot_dist(int dtype, const void* X, const void* Y, int64_t n, int64_t m, int d, int64_t ldX, int64_t ldY, int metric,
+              void* out, int64_t ldOut, void* scratch_dev, void* stream);
+/* block of the lazy plan: out_ij = exp(f_i + g_j - C_ij/reg) for the n x m block whose points / potentials start at
+ * the given pointers (get_sinkhorn_lazytensor, ot/bregman/_empirical.py:26-71); scratch as for b2ot_dist */
+int b2ot_emp_plan_block(int dtype, const void* Xs, const void* Xt, const void* f, const void* g, int64_t n, int64_t m,
+                        int d, int64_t ldXs, int64_t ldXt, double reg, int metric, void* out, int64_t ldOut,
+                        void* scratch_dev, void* stream);
+/* loss <C, plan> = sum_ij C_ij exp(f_i + g_j - C_ij/reg) reduced on the fly (lazy branch of empirical_sinkhorn2,
+ * ot/bregman/_empirical.py:466-483); result: one double at loss_dev; scratch >= b2ot_emp_loss_scratch_bytes */
+size_t b2ot_emp_loss_scratch_bytes(int64_t n, int64_t m, int dtype);
+int b2ot_emp_loss(int dtype, const void* Xs, const void* Xt, const void* f, const void* g, int64_t n, int64_t m, int d,
+                  int64_t ldXs, int64_t ldXt, double reg, int metric, double* loss_dev, void* scratch_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

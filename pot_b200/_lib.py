@@ -56,7 +56,32 @@ PROTOTYPES = {
                                    C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double,
                                    C.c_void_p, C.c_size_t, C.POINTER(C.c_int), C.c_int, C.c_void_p]),
+    "b2ot_emp_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int, C.c_int]),
+    "b2ot_emp_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.c_int64, C.c_int, C.c_void_p,
+                                  C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double,
+                                  C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_double, C.c_int, C.c_void_p]),
+    "b2ot_emp_set_allreduce": (C.c_int, [C.c_void_p, ALLREDUCE_FN, C.c_void_p]),
+    "b2ot_emp_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b2ot_emp_iterate": (C.c_int, [C.c_void_p, C.c_int]),
+    "b2ot_emp_poll": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "b2ot_emp_solve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int),
+                                 C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "b2ot_emp_export": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double), C.c_int,
+                                  C.POINTER(C.c_int)]),
+    "b2ot_emp_destroy": (C.c_int, [C.c_void_p]),
+    "b2ot_dist_scratch_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int]),
+    "b2ot_dist": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_int64, C.c_int64,
+                            C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "b2ot_emp_plan_block": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64,
+                                      C.c_int, C.c_int64, C.c_int64, C.c_double, C.c_int, C.c_void_p, C.c_int64,
+                                      C.c_void_p, C.c_void_p]),
+    "b2ot_emp_loss_scratch_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int]),
+    "b2ot_emp_loss": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int,
+                                C.c_int64, C.c_int64, C.c_double, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
+
+METRIC_SQEUCLIDEAN, METRIC_EUCLIDEAN = 0, 1
+EMP_AUTO, EMP_SIMT, EMP_TC = 0, 1, 2
 
 _lib = None
 

@@ -1,0 +1,194 @@
+"""GPU parity tests of the online-cost (empirical) Sinkhorn path, ot.dist and the lazy plan against the golden
+vectors of the reference and the CPU oracle.  Everything goes through libb2ot.so (b2ot_emp_*, b2ot_dist).
+
+Tolerances (north_star): potentials / plan within 1e-10 relative in fp64 and 1e-4 relative in fp32 at a fixed
+iteration count (stopThr = -1 disables the reference's `<=` stop test).
+"""
+import warnings
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+if torch.cuda.is_available():
+    import pot_b200 as ot
+    from pot_b200 import _lib
+from oracle import sinkhorn_oracle as orc
+
+DEV = "cuda:0"
+EMP = [f"emp_{t}_{s}" for t in ("f64", "f32") for s in ("40x50x3", "64x32x8", "37x41x2")]
+
+
+def tol_of(x):
+    return 1e-10 if x in ("f64", np.float64, torch.float64) else 1e-4
+
+
+def dev(x):
+    return torch.as_tensor(np.ascontiguousarray(x), device=DEV)
+
+
+def close(x, ref, tol, what, floor_rel=1e-6):
+    x = x.detach().cpu().numpy().astype(np.float64)
+    ref = np.asarray(ref, dtype=np.float64)
+    assert x.shape == ref.shape, (what, x.shape, ref.shape)
+    err = np.abs(x - ref) / (np.abs(ref) + floor_rel * np.abs(ref).max())
+    assert err.max() < tol, f"{what}: rel err {err.max():.3e} >= {tol}"
+
+
+def logclose(x, ref, tol, what):
+    x = x.detach().cpu().numpy().astype(np.float64)
+    ref = np.asarray(ref, dtype=np.float64)
+    err = np.abs(x - ref).max() / max(1.0, np.abs(ref).max())
+    assert err < tol, f"{what}: err {err:.3e} >= {tol}"
+
+
+def errs_close(errs, ref, dtype):
+    e = np.array([float(x) for x in errs])
+    r = np.asarray(ref, dtype=np.float64)
+    assert e.shape == r.shape, (e, r)
+    floor = 1e-13 if dtype == "f64" else 3e-6  # L1 error over n rows bottoms out at n * eps
+    assert np.all(np.abs(e - r) <= 2e-3 * r + floor), (e, r)
+
+
+@pytest.mark.parametrize("case", EMP)
+def test_lazy_golden_fixed_iterations(golden, case):
+    tag = case.split("_")[1]
+    xs, xt, a, b = (golden(case, k) for k in ("xs", "xt", "a", "b"))
+    reg, its = float(golden(case, "reg")), int(golden(case, "its"))
+    tol = tol_of(tag)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        f, g, lg = ot.empirical_sinkhorn(dev(xs), dev(xt), reg, dev(a), dev(b), numIterMax=its, stopThr=-1,
+                                         isLazy=True, batchSize=tuple(int(x) for x in golden(case, "bs")), log=True)
+    assert f.dtype == torch.as_tensor(xs).dtype and f.is_cuda
+    assert lg["niter"] == int(golden(case, "niter")) == its - 1
+    logclose(f, golden(case, "f"), tol, "f")
+    logclose(g, golden(case, "g"), tol, "g")
+    errs_close(lg["err"], golden(case, "err"), tag)
+    assert lg["u"] is f and lg["v"] is g
+    # lazy plan: full and block reads
+    lp = lg["lazy_plan"]
+    assert lp.shape == (xs.shape[0], xt.shape[0])
+    close(lp[:], golden(case, "plan"), 10 * tol, "lazy_plan[:]")
+    close(lp[3:11, 5:20], golden(case, "plan_block"), 10 * tol, "block")  # the fixture's block (make_golden.py)
+    row = lp[5]
+    assert row.shape == (1, xt.shape[0])
+    close(row, golden(case, "plan")[5:6], 10 * tol, "lazy_plan[5]")
+
+
+@pytest.mark.parametrize("case", EMP)
+def test_lazy_golden_converged(golden, case):
+    """The device-side stop test (`err <= stopThr` at (it + 1) % 10 == 0) fires at the reference's iteration."""
+    tag = case.split("_")[1]
+    xs, xt, a, b = (golden(case, k) for k in ("xs", "xt", "a", "b"))
+    reg, thr = float(golden(case, "reg")), float(golden(case + "/conv", "thr"))
+    f, g, lg = ot.empirical_sinkhorn(dev(xs), dev(xt), reg, dev(a), dev(b), numIterMax=3000, stopThr=thr, isLazy=True,
+                                     batchSize=7, log=True)
+    assert lg["niter"] == int(golden(case + "/conv", "niter"))
+    assert len(lg["err"]) == len(golden(case + "/conv", "err"))
+    logclose(f, golden(case + "/conv", "f"), 10 * tol_of(tag), "f")
+    logclose(g, golden(case + "/conv", "g"), 10 * tol_of(tag), "g")
+
+
+def test_default_weights_and_nonlazy(golden):
+    xs, xt = golden("emp_default", "xs"), golden("emp_default", "xt")
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        f, g = ot.empirical_sinkhorn(dev(xs), dev(xt), 0.7, numIterMax=50, stopThr=-1, isLazy=True, batchSize=7)
+        G = ot.empirical_sinkhorn(dev(xs), dev(xt), 0.7, numIterMax=50, stopThr=0)
+    logclose(f, golden("emp_default", "f"), 1e-10, "f")
+    logclose(g, golden("emp_default", "g"), 1e-10, "g")
+    close(G, golden("emp_default", "plan"), 1e-10, "plan (non-lazy)")
+    # doctest of the reference (_empirical.py:159-167)
+    x = torch.arange(2, dtype=torch.float64, device=DEV).reshape(2, 1)
+    P = ot.empirical_sinkhorn(x, x.clone(), 0.1)
+    close(P, golden("doctest", "emp_2x2"), 1e-10, "doctest plan")
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("shape", [(1, 1, 1), (5, 3, 1), (70, 130, 2), (129, 64, 17), (300, 257, 64), (1000, 777, 5)])
+def test_dist(dtype, shape):
+    n, m, d = shape
+    rng = np.random.RandomState(n + m)
+    X, Y = rng.randn(n, d).astype(dtype), (rng.randn(m, d) + 0.5).astype(dtype)
+    tol = 1e-12 if dtype == np.float64 else 2e-5
+    C = ot.dist(dev(X), dev(Y))
+    ref = orc.sqeuclidean(X.astype(np.float64), Y.astype(np.float64))
+    assert C.shape == (n, m) and float(C.min()) >= 0
+    np.testing.assert_allclose(C.cpu().numpy(), ref, rtol=tol, atol=tol * max(1.0, ref.max()))
+    E = ot.dist(dev(X), dev(Y), metric="euclidean")
+    np.testing.assert_allclose(E.cpu().numpy(), np.sqrt(ref), rtol=1e3 * tol, atol=3e-3 if dtype == np.float32 else 1e-7)
+    S = ot.dist(dev(X))
+    assert torch.all(torch.diagonal(S) == 0) and S.shape == (n, n)
+    with pytest.raises(NotImplementedError):
+        ot.dist(dev(X), dev(Y), metric="cityblock")
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("shape", [(1, 9, 2), (65, 64, 3), (200, 333, 16), (513, 190, 64), (257, 1030, 7)])
+def test_lazy_vs_oracle(dtype, shape):
+    """Ragged sizes across the 64 x 64 tiling and the reduction splits; non-uniform weights; warm start."""
+    n, m, d = shape
+    rng = np.random.RandomState(7 * n + m)
+    xs = (rng.randn(n, d) / np.sqrt(d)).astype(dtype)
+    xt = (rng.randn(m, d) / np.sqrt(d) + 0.3).astype(dtype)
+    a = rng.rand(n) + 0.2
+    b = rng.rand(m) + 0.2
+    a, b = (a / a.sum()).astype(dtype), (b / b.sum()).astype(dtype)
+    ws = (rng.randn(n).astype(dtype) * 0.1, rng.randn(m).astype(dtype) * 0.1)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        fr, gr, lr = orc.empirical_sinkhorn_lazy(xs, xt, 0.5, a, b, numIterMax=20, stopThr=-1, batchSize=50, log=True,
+                                                 warmstart=ws)
+        f, g, lg = ot.empirical_sinkhorn(dev(xs), dev(xt), 0.5, dev(a), dev(b), numIterMax=20, stopThr=-1, isLazy=True,
+                                         log=True, warmstart=(dev(ws[0]), dev(ws[1])))
+    tol = tol_of(dtype)
+    logclose(f, fr, tol, "f")
+    logclose(g, gr, tol, "g")
+    assert lg["niter"] == lr["niter"] == 19 and len(lg["err"]) == 2
+    # marginal violation of the lazy plan (g was updated last: column marginal exact up to round-off)
+    P = lg["lazy_plan"][:]
+    assert float(torch.abs(P.sum(0) - dev(b)).max()) < (1e-12 if dtype == np.float64 else 1e-6)
+    loss = ot.empirical_sinkhorn2(dev(xs), dev(xt), 0.5, dev(a), dev(b), numIterMax=20, stopThr=-1, isLazy=True,
+                                  warn=False, warmstart=(dev(ws[0]), dev(ws[1])))
+    C = orc.sqeuclidean(xs, xt)
+    ref_loss = float(np.sum(C * np.exp(fr[:, None] + gr[None, :] - C / 0.5)))
+    assert abs(float(loss) - ref_loss) <= 10 * tol * abs(ref_loss)
+
+
+def test_warnings_errors_and_dtype():
+    rng = np.random.RandomState(0)
+    xs, xt = dev(rng.randn(20, 2)), dev(rng.randn(30, 2))
+    with pytest.warns(UserWarning, match="did not converge"):
+        ot.empirical_sinkhorn(xs, xt, 1.0, numIterMax=5, stopThr=0, isLazy=True)
+    with warnings.catch_warnings():
+        warnings.simplefilter("error")
+        ot.empirical_sinkhorn(xs, xt, 1.0, numIterMax=5, stopThr=0, isLazy=True, warn=False)
+    with pytest.raises(ValueError, match="Batch size"):
+        ot.empirical_sinkhorn(xs, xt, 1.0, isLazy=True, batchSize=(1, 2, 3))
+    with pytest.raises(ValueError, match="no CPU fallback"):
+        ot.empirical_sinkhorn(xs.cpu(), xt.cpu(), 1.0, isLazy=True)
+    with pytest.raises(NotImplementedError):
+        ot.empirical_sinkhorn(xs, xt, 1.0, isLazy=True, metric="cosine")
+    f, g = ot.empirical_sinkhorn(xs.float(), xt.float(), 1.0, numIterMax=30, isLazy=True, warn=False)
+    assert f.dtype == torch.float32 and g.dtype == torch.float32 and f.device == xs.device
+    # euclidean metric runs through the same sweep
+    f, g, lg = ot.empirical_sinkhorn(xs, xt, 1.0, numIterMax=200, isLazy=True, metric="euclidean", log=True)
+    P = lg["lazy_plan"][:]
+    assert float(torch.abs(P.sum(1) - 1.0 / 20).sum()) < 1e-8
+    assert lg["niter"] < 199
+
+
+def test_lazy_equals_dense_log_solver():
+    """Reference test_lazy_empirical_sinkhorn: the lazy plan has the marginals of the dense solution (atol 1e-5)."""
+    rng = np.random.RandomState(3)
+    xs, xt = rng.rand(100, 2), rng.rand(120, 2)
+    M = orc.sqeuclidean(xs, xt)
+    f, g, lg = ot.empirical_sinkhorn(dev(xs), dev(xt), 1.0, numIterMax=1000, isLazy=True, batchSize=(1, 3), log=True)
+    G = ot.sinkhorn([], [], dev(M), 1.0, stopThr=1e-10)
+    P = lg["lazy_plan"][:]
+    np.testing.assert_allclose(P.sum(1).cpu().numpy(), G.sum(1).cpu().numpy(), atol=1e-5)
+    np.testing.assert_allclose(P.sum(0).cpu().numpy(), G.sum(0).cpu().numpy(), atol=1e-5)
+    np.testing.assert_allclose(P.cpu().numpy(), G.cpu().numpy(), atol=1e-5)

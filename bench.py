@@ -44,6 +44,9 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n", type=int, default=65536, help="problem size n = m (default: the headline 65536)")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: per-iteration exchange of K^T u (peer = fused NVLink peer-memory exchange, "
+                         "nccl = torch.distributed all-reduce baseline)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     return ap.parse_args()
@@ -232,12 +235,12 @@ def ours(args):
         b_host = torch.full((m,), 1.0 / m, dtype=torch.float32).pin_memory()
         torch.cuda.synchronize(dev)
         sinkhorn_from_host(a_host, b_host, M_host, REG, numItermax=min(W, 5), stopThr=0.0, device=dev, group=group,
-                           n_total=n)  # warm-up solve (allocator, NCCL channels, kernel images)
+                           n_total=n, exchange=args.exchange)  # warm-up solve (allocator, NCCL channels, kernel images)
         barrier()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
         res = sinkhorn_from_host(a_host, b_host, M_host, REG, numItermax=K_steps, stopThr=0.0, device=dev,
-                                 group=group, n_total=n)
+                                 group=group, n_total=n, exchange=args.exchange)
         ev1.record()
         barrier()
         t_e2e = max_over_ranks(ev0.elapsed_time(ev1) * 1e-3)
@@ -254,7 +257,7 @@ def ours(args):
                              _lib.F32, _dense.stream_ptr(dev)), "b2ot_kexp")
     Kmat = Mdev
     solver = _dense.DenseSolver("knopp", Kmat, a_loc, b, None, max_iter=10 ** 7, check_every=10, stop_thr=0.0,
-                                group=group)
+                                group=group, exchange=args.exchange)
     u0 = torch.full((nloc,), 1.0 / n, dtype=torch.float32, device=dev)
     v0 = torch.full((m,), 1.0 / m, dtype=torch.float32, device=dev)
     solver.init(u0, v0)
@@ -308,7 +311,8 @@ def ours(args):
             "config": {"workload": f"ot.bregman.sinkhorn_knopp dense fp32 n=m={n} (K = {4 * n * m / 2 ** 30:.0f} GiB), "
                                    f"reg={REG}, uniform weights, 2-D Gaussian clouds (seed {SEED}), fixed iterations "
                                    "(stopThr=0)",
-                       "sharding": f"rows split over {world} rank(s), one all-reduce of K^T u (m+1 floats) per iteration"
+                       "sharding": f"rows split over {world} rank(s), one exchange of K^T u (m+1 floats) per iteration, "
+                                   f"exchange={args.exchange}"
                                    if world > 1 else "single GPU",
                        "l2": "inputs larger than L2 (K per rank = %.1f GiB >> 126 MB): no flush needed"
                              % (4 * nloc * m / 2 ** 30),

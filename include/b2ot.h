@@ -187,6 +187,32 @@ size_t b2ot_emp_loss_scratch_bytes(int64_t n, int64_t m, int dtype);
 int b2ot_emp_loss(int dtype, const void* Xs, const void* Xt, const void* f, const void* g, int64_t n, int64_t m, int d,
                   int64_t ldXs, int64_t ldXt, double reg, int metric, double* loss_dev, void* scratch_dev, void* stream);
 
+/* ---- row-sharded runs: one-shot all-reduce over NVLink peer memory (one process per GPU, one node) ----
+ * The reference has no multi-device path (no NCCL / MPI call site anywhere in /root/reference/ot); this is the
+ * exchange step of the row-sharded solvers: per iteration each rank stores its reduced column vector into a slot
+ * of every peer's exchange buffer (peer-mapped with CUDA IPC) and publishes a flag; the solver's own finalize
+ * kernel waits on the flags and sums the slots in rank order (bit-identical on every rank).  See csrc/comm.cuh.
+ *
+ *   b2ot_comm_alloc   cudaMalloc + zero an exchange buffer on the current device, return its IPC handle
+ *   b2ot_comm_open    map a peer's buffer from its handle (exchanged by the host, e.g. torch.distributed)
+ *   b2ot_comm_create  bufs[q] = rank q's buffer as seen from this process (own pointer at q == rank);
+ *                     slot size = (bytes - 4096) / (2 * nranks), at most 8 ranks
+ * The library allocates nothing else; these buffers are the one exception to "the caller owns all memory". */
+#define B2OT_IPC_HANDLE_BYTES 64
+typedef struct b2ot_comm b2ot_comm;
+int b2ot_comm_alloc(size_t bytes, void** buf_dev, unsigned char* ipc_handle);
+int b2ot_comm_free(void* buf_dev);
+int b2ot_comm_open(const unsigned char* ipc_handle, void** peer_ptr);
+int b2ot_comm_close(void* peer_ptr);
+int b2ot_comm_create(b2ot_comm** comm, int nranks, int rank, void* const* bufs, size_t bytes);
+int b2ot_comm_destroy(b2ot_comm* comm);
+size_t b2ot_comm_slot_bytes(const b2ot_comm* comm);
+/* in-place all-reduce (B2OT_OP_SUM / B2OT_OP_MAX) of count elements through the exchange buffers, on `stream` */
+int b2ot_comm_allreduce(b2ot_comm* comm, void* buf_dev, int64_t count, int dtype, int op, void* stream);
+/* attach to a solver handle (replaces the all-reduce hook); the communicator must outlive the handle */
+int b2ot_dense_set_comm(b2ot_dense* handle, b2ot_comm* comm);
+int b2ot_emp_set_comm(b2ot_emp* handle, b2ot_comm* comm);
+
 #ifdef __cplusplus
 }
 #endif

@@ -43,10 +43,11 @@ class DenseSolver:
     b     : (m,)
     logb  : (m,) log(b), 'log' mode only
     group : torch.distributed process group of the row-shard ranks (None = single device)
+    exchange : "peer" (default; one-shot NVLink peer-memory exchange inside the library's kernels) or "nccl"
     """
 
     def __init__(self, mode, K, a, b, logb=None, max_iter=1000, check_every=10, stop_thr=1e-9, variant="auto",
-                 group=None):
+                 group=None, exchange="peer"):
         self.lib = _lib.load()
         assert K.is_cuda and K.dim() == 2 and K.stride(1) == 1
         self.mode = _lib.MODE_KNOPP if mode == "knopp" else _lib.MODE_LOG
@@ -68,10 +69,19 @@ class DenseSolver:
                 int(check_every), float(stop_thr), var, stream_ptr(self.device)), "b2ot_dense_create")
         self.h = h
         self._cb = None
+        self.comm = None
         if group is not None:
-            self._install_allreduce(group)
+            if exchange == "peer":  # NVLink peer-memory exchange fused into the put / finalize kernels
+                from .comm import get_comm
 
-    # ---- row-sharded runs: the per-iteration column-sum exchange goes through torch.distributed ----
+                self.comm = get_comm(group, self.device, (self.m + 1) * 8)
+                _lib.check(self.lib.b2ot_dense_set_comm(self.h, self.comm.h), "b2ot_dense_set_comm")
+            elif exchange == "nccl":  # baseline: one NCCL all-reduce per iteration through torch.distributed
+                self._install_allreduce(group)
+            else:
+                raise ValueError(f"unknown exchange {exchange!r} (peer | nccl)")
+
+    # ---- baseline exchange: the per-iteration column-sum all-reduce goes through torch.distributed ----
     def _install_allreduce(self, group):
         import torch.distributed as dist
 
@@ -130,6 +140,8 @@ class DenseSolver:
         with torch.cuda.device(self.device):
             _lib.check(self.lib.b2ot_dense_solve(self.h, u0.data_ptr(), v0.data_ptr(), int(poll_every), C.byref(st),
                                                  C.byref(ni), C.byref(ne)), "b2ot_dense_solve")
+        if st.value == _lib.ST_COMM_TIMEOUT:
+            raise _lib.B2otError("row-sharded solve: a peer rank never published its exchange flag (timeout)")
         return st.value, ni.value, ne.value
 
     def export(self):

@@ -78,8 +78,20 @@ PROTOTYPES = {
     "b2ot_emp_loss_scratch_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int]),
     "b2ot_emp_loss": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int,
                                 C.c_int64, C.c_int64, C.c_double, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b2ot_comm_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p), C.c_char_p]),
+    "b2ot_comm_free": (C.c_int, [C.c_void_p]),
+    "b2ot_comm_open": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
+    "b2ot_comm_close": (C.c_int, [C.c_void_p]),
+    "b2ot_comm_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.POINTER(C.c_void_p), C.c_size_t]),
+    "b2ot_comm_destroy": (C.c_int, [C.c_void_p]),
+    "b2ot_comm_slot_bytes": (C.c_size_t, [C.c_void_p]),
+    "b2ot_comm_allreduce": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p]),
+    "b2ot_dense_set_comm": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "b2ot_emp_set_comm": (C.c_int, [C.c_void_p, C.c_void_p]),
 }
 
+ST_COMM_TIMEOUT = 5
+IPC_HANDLE_BYTES = 64
 METRIC_SQEUCLIDEAN, METRIC_EUCLIDEAN = 0, 1
 EMP_AUTO, EMP_SIMT, EMP_TC = 0, 1, 2
 

@@ -1,0 +1,131 @@
+// One-shot all-reduce over NVLink peer memory for the row-sharded solvers (sm_100a, one process per GPU).
+//
+// Every rank owns one "exchange buffer" of identical layout, mapped into every peer with CUDA IPC:
+//
+//   [0, 1 KiB)    flags  : u64 flag[parity][source rank]  -- the sequence number of the last complete put
+//   [1 KiB, 4 KiB) local scratch (block ticket)
+//   [4 KiB, ...)  data   : slot[parity][source rank][slot_bytes]
+//
+// An exchange with sequence number s (parity s & 1):
+//   put  : each rank reduces its local partial rows and STORES the result straight into slot[s&1][rank] of
+//          every peer's buffer (NVLink writes, fire and forget); the last block fences at system scope and
+//          then publishes flag[s&1][rank] = s on every peer (st.release.sys).
+//   take : the consumer kernel (the solver's finalize kernel itself on the hot path) spins on its LOCAL flags
+//          until all ranks have published s (ld.acquire.sys), then sums the nranks slots in rank order -- the
+//          same order on every rank, so all ranks see bit-identical totals and take identical stop decisions.
+// Two parities suffice: a rank can only start the put of s + 2 after it consumed s + 1, which needs every
+// peer's put of s + 1, which those peers issue after they consumed s.
+// The per-iteration traffic is one m-vector per peer (256 KiB at m = 65536): latency-bound, no NCCL launch,
+// no separate reduce kernel on the hot path.
+#pragma once
+
+#include "common.cuh"
+
+namespace b2ot {
+
+constexpr int COMM_MAX_RANKS = 8;
+constexpr size_t COMM_DATA_OFFSET = 4096;
+constexpr int ST_COMM_TIMEOUT = 5;  // solver status: a peer never published its flag
+
+struct CommView {
+  unsigned long long* flags[COMM_MAX_RANKS];  // flag area of rank q's buffer
+  unsigned char* data[COMM_MAX_RANKS];        // data area of rank q's buffer
+  unsigned int* ticket;                       // local
+  int nranks, rank;
+  unsigned long long slot_bytes;
+};
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+template <typename T>
+__device__ __forceinline__ T* comm_slot(const CommView& c, int owner, int parity, int src_rank) {
+  return reinterpret_cast<T*>(c.data[owner] + (size_t)(parity * c.nranks + src_rank) * c.slot_bytes);
+}
+
+// Block-wide wait until every rank has published sequence number `seq`.  Returns false on timeout (20 s).
+__device__ __forceinline__ bool comm_wait(const CommView& c, unsigned long long seq) {
+  __shared__ int s_ok;
+  if (threadIdx.x == 0) s_ok = 1;
+  __syncthreads();
+  if ((int)threadIdx.x < c.nranks) {
+    const unsigned long long* f = c.flags[c.rank] + (seq & 1ull) * COMM_MAX_RANKS + threadIdx.x;
+    const unsigned long long t0 = global_timer_ns();
+    while (ld_acquire_sys(f) < seq) {
+      if (global_timer_ns() - t0 > 20000000000ull) {
+        s_ok = 0;
+        break;
+      }
+    }
+  }
+  __syncthreads();
+  return s_ok != 0;
+}
+
+// put: dst_q[j] = sum over nsrc local rows of src[row * ld + j] for j < count; optional extra element at index
+// `count` carrying (*flag_src != 0).  No-op unless *status == expect_status (status may be null).
+template <typename T>
+__global__ void __launch_bounds__(256) comm_put_kernel(const CommView c, const T* __restrict__ src, long long ld, int nsrc,
+                                                       long long count, const int* flag_src, const int* status,
+                                                       int expect_status, unsigned long long seq) {
+  __shared__ int s_last;
+  if (status != nullptr && *status != expect_status) return;
+  const int par = (int)(seq & 1ull);
+  const long long total = count + (flag_src != nullptr ? 1 : 0);
+  for (long long j = (long long)blockIdx.x * 256 + threadIdx.x; j < total; j += (long long)gridDim.x * 256) {
+    T s = (T)0;
+    if (j < count) {
+      for (int q = 0; q < nsrc; ++q) s += src[(long long)q * ld + j];
+    } else {
+      s = (T)(atomicOr(const_cast<int*>(flag_src), 0) ? 1 : 0);
+    }
+    for (int q = 0; q < c.nranks; ++q) comm_slot<T>(c, q, par, c.rank)[j] = s;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int t = atomicAdd(c.ticket, 1u);
+    s_last = (t == gridDim.x - 1) ? 1 : 0;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence_system();
+  if ((int)threadIdx.x < c.nranks)
+    st_release_sys(c.flags[threadIdx.x] + (size_t)par * COMM_MAX_RANKS + c.rank, seq);
+  if (threadIdx.x == 0) *c.ticket = 0;
+}
+
+// take (generic): dst[j] = reduce over ranks of slot[q][j], in place all-reduce result for the caller.
+// op 0 = sum, 1 = max.  On timeout sets *err_status = ST_COMM_TIMEOUT (when given).
+template <typename T>
+__global__ void __launch_bounds__(256) comm_take_kernel(const CommView c, T* __restrict__ dst, long long count, int op,
+                                                        const int* gate_status, int expect_status, int* err_status,
+                                                        unsigned long long seq) {
+  if (gate_status != nullptr && *gate_status != expect_status) return;
+  if (!comm_wait(c, seq)) {
+    if (err_status != nullptr && threadIdx.x == 0) *err_status = ST_COMM_TIMEOUT;
+    return;
+  }
+  const int par = (int)(seq & 1ull);
+  for (long long j = (long long)blockIdx.x * 256 + threadIdx.x; j < count; j += (long long)gridDim.x * 256) {
+    T r = __ldcg(comm_slot<T>(c, c.rank, par, 0) + j);
+    for (int q = 1; q < c.nranks; ++q) {
+      const T x = __ldcg(comm_slot<T>(c, c.rank, par, q) + j);
+      r = (op == 0) ? r + x : max_t(r, x);
+    }
+    dst[j] = r;
+  }
+}
+
+}  // namespace b2ot

@@ -1,4 +1,5 @@
 // Host driver + C ABI of the dense Sinkhorn solver (see include/b2ot.h, dense_kernels.cuh).
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -6,6 +7,7 @@
 #include <vector>
 
 #include "../../include/b2ot.h"
+#include "comm_host.h"
 #include "dense_kernels.cuh"
 #include "host_util.h"
 
@@ -49,6 +51,7 @@ struct b2ot_dense {
   int fin_blocks;
   b2ot_allreduce_fn ar;
   void* ar_ctx;
+  b2ot_comm* comm;  // NVLink peer-memory exchange (takes precedence over the hook)
   SolveState* h_state;  // pinned host mirror for polls
 };
 
@@ -428,6 +431,17 @@ extern "C" int b2ot_dense_set_allreduce(b2ot_dense* h, b2ot_allreduce_fn fn, voi
   return 0;
 }
 
+extern "C" int b2ot_dense_set_comm(b2ot_dense* h, b2ot_comm* comm) {
+  B2OT_REQUIRE(h != nullptr, "b2ot_dense_set_comm: null handle");
+  if (comm != nullptr) {
+    const size_t need = (size_t)(h->m + 1) * esize(h->dtype);
+    B2OT_REQUIRE(comm->view.slot_bytes >= need, "b2ot_dense_set_comm: exchange slots hold %llu bytes, %zu needed",
+                 comm->view.slot_bytes, need);
+  }
+  h->comm = comm;
+  return 0;
+}
+
 extern "C" int b2ot_dense_info(const b2ot_dense* h, int* variant, int* cluster_size, int* n_clusters, int* stages,
                                int* vecs_per_thread) {
   B2OT_REQUIRE(h != nullptr, "b2ot_dense_info: null handle");
@@ -489,6 +503,7 @@ static int launch_rows(const b2ot_dense* h) {
 }
 
 static int call_allreduce(const b2ot_dense* h, void* buf, long long count, int op) {
+  if (h->comm) return comm_allreduce(h->comm, buf, count, h->dtype, op, &h->st->status, h->stream);
   const int rc = h->ar(buf, count, h->dtype, op, (void*)h->stream, h->ar_ctx);
   B2OT_REQUIRE(rc == 0, "all-reduce hook failed with code %d", rc);
   return 0;
@@ -497,8 +512,27 @@ static int call_allreduce(const b2ot_dense* h, void* buf, long long count, int o
 template <typename T>
 static int launch_finalize(const b2ot_dense* h, int nsrc, int init) {
   FinParams p;
-  const bool multi = h->ar != nullptr;
-  if (multi) {
+  memset(&p, 0, sizeof(p));
+  const bool multi = h->ar != nullptr || h->comm != nullptr;
+  if (h->comm) {
+    // fused exchange: "put" reduces this rank's partial rows straight into every peer's slot, the finalize
+    // kernel below is the "take" (waits on the flags, sums the slots in rank order)
+    b2ot_comm* c = h->comm;
+    const unsigned long long seq = ++c->seq;
+    const unsigned g = (unsigned)std::min<long long>((h->m + 1 + 255) / 256, 296);
+    comm_put_kernel<T><<<g, 256, 0, h->stream>>>(c->view, (const T*)h->partials, h->mp, nsrc, h->m, &h->st->uflag,
+                                                 &h->st->status, ST_RUNNING, seq);
+    B2OT_CHECK_LAUNCH();
+    p.src = c->view.data[c->view.rank] + (size_t)((seq & 1ull) * c->view.nranks) * c->view.slot_bytes;
+    p.src_ld = (long long)(c->view.slot_bytes / sizeof(T));
+    p.nsrc = c->view.nranks;
+    p.extra_flag = (const char*)p.src + (size_t)h->m * sizeof(T);
+    p.extra_flag_ld = p.src_ld;
+    p.extra_flag_n = c->view.nranks;
+    p.use_comm = 1;
+    p.seq = seq;
+    p.comm = c->view;
+  } else if (multi) {
     const unsigned g = (unsigned)((h->m + 1 + 255) / 256);
     reduce_partials_kernel<T><<<g, 256, 0, h->stream>>>(h->partials, h->mp, nsrc, h->cbuf, h->m, h->st, ST_RUNNING);
     B2OT_CHECK_LAUNCH();
@@ -508,6 +542,8 @@ static int launch_finalize(const b2ot_dense* h, int nsrc, int init) {
     p.src_ld = h->mp;
     p.nsrc = 1;
     p.extra_flag = (const char*)h->cbuf + (size_t)h->m * sizeof(T);
+    p.extra_flag_ld = 0;
+    p.extra_flag_n = 1;
   } else {
     p.src = h->partials;
     p.src_ld = h->mp;
@@ -558,13 +594,13 @@ static int launch_exact_cols(const b2ot_dense* h, int expect_status, int advance
   lse_combine_kernel<T><<<g1, 256, 0, h->stream>>>(lp);
   B2OT_CHECK_LAUNCH();
   char* P = (char*)h->partials;
-  if (h->ar) {
+  if (h->ar || h->comm) {
     int rc = call_allreduce(h, P + (size_t)(2 * ns + 1) * h->mp * sizeof(T), h->m, 1);
     if (rc) return rc;
   }
   lse_rescale_kernel<T><<<g1, 256, 0, h->stream>>>(lp);
   B2OT_CHECK_LAUNCH();
-  if (h->ar) {
+  if (h->ar || h->comm) {
     int rc = call_allreduce(h, P + (size_t)(2 * ns + 2) * h->mp * sizeof(T), h->m, 0);
     if (rc) return rc;
   }

@@ -23,6 +23,7 @@
 #pragma once
 
 #include "common.cuh"
+#include "comm.cuh"
 
 namespace b2ot {
 
@@ -558,7 +559,12 @@ struct FinParams {
   const void* src;      // nsrc rows of column sums (stride src_ld)
   long long src_ld;
   int nsrc;
-  const void* extra_flag;  // optional: T value != 0 means "some rank produced a non-finite u"
+  const void* extra_flag;  // optional: T value(s) != 0 mean "some rank produced a non-finite u"
+  long long extra_flag_ld; // ... flag_n values, extra_flag_ld elements apart
+  int extra_flag_n;
+  int use_comm;            // 1: `src` are the peer-exchange slots of sequence `seq`: wait for all ranks first
+  unsigned long long seq;
+  CommView comm;
   const void* b;
   const void* logb;
   void* vring;
@@ -580,6 +586,10 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
   SolveState* st = p.st;
   if (st->status != ST_RUNNING) return;
   const int tid = threadIdx.x;
+  if (p.use_comm && !comm_wait(p.comm, p.seq)) {  // fused "take" of the NVLink exchange
+    if (tid == 0) st->status = ST_COMM_TIMEOUT;
+    return;
+  }
   const int sel_v = st->sel_v;
   const int nxt = (sel_v + 1) % 3;
   const T* vcur = reinterpret_cast<const T*>(p.vring) + (long long)sel_v * p.mp;
@@ -595,7 +605,7 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
   int flags = 0;
   for (long long j = (long long)blockIdx.x * 256 + tid; j < p.m; j += (long long)gridDim.x * 256) {
     T c = (T)0;
-    for (int q = 0; q < p.nsrc; ++q) c += src[(long long)q * p.src_ld + j];
+    for (int q = 0; q < p.nsrc; ++q) c += __ldcg(&src[(long long)q * p.src_ld + j]);
     const T bj = b[j];
     const T vj = vcur[j];
     T vn;
@@ -646,7 +656,10 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
   const int nflags = atomicOr(&st->next_flags, 0);
   const int nexact = atomicOr(&st->need_exact, 0);
   int uflag = atomicOr(&st->uflag, 0);
-  if (p.extra_flag != nullptr && *reinterpret_cast<const T*>(p.extra_flag) != (T)0) uflag = 1;
+  if (p.extra_flag != nullptr) {
+    for (int q = 0; q < p.extra_flag_n; ++q)
+      if (__ldcg(reinterpret_cast<const T*>(p.extra_flag) + (long long)q * p.extra_flag_ld) != (T)0) uflag = 1;
+  }
   const int ii = st->iter;
   if (p.init) {
     st->sel_v = nxt;

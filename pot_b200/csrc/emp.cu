@@ -5,6 +5,7 @@
 #include <new>
 
 #include "../../include/b2ot.h"
+#include "comm_host.h"
 #include "emp_kernels.cuh"
 #include "host_util.h"
 
@@ -25,6 +26,7 @@ struct b2ot_emp {
   int nsplitA, nsplitB, fin_blocks_f, fin_blocks_g;
   b2ot_allreduce_fn ar;
   void* ar_ctx;
+  b2ot_comm* comm;  // NVLink peer-memory exchange (takes precedence over the hook)
   EmpState* h_state;
 };
 
@@ -119,6 +121,7 @@ int launch_lse_pass(const b2ot_emp* h, bool passA) {
 }
 
 int call_allreduce(const b2ot_emp* h, void* buf, long long count, int dtype, int op) {
+  if (h->comm) return comm_allreduce(h->comm, buf, count, dtype, op, &h->st->status, h->stream);
   const int rc = h->ar(buf, count, dtype, op, (void*)h->stream, h->ar_ctx);
   B2OT_REQUIRE(rc == 0, "all-reduce hook failed with code %d", rc);
   return 0;
@@ -148,10 +151,11 @@ int launch_fin_f(const b2ot_emp* h) {
   p.len = h->n;
   p.logw = h->loga;
   p.w = h->a;
-  p.err_xchg = h->ar ? h->err_xchg : nullptr;
+  const bool multi = h->ar != nullptr || h->comm != nullptr;
+  p.err_xchg = multi ? h->err_xchg : nullptr;
   emp_fin_f_kernel<T><<<h->fin_blocks_f, 256, 0, h->stream>>>(p);
   B2OT_CHECK_LAUNCH();
-  if (h->ar) {
+  if (multi) {
     int rc = call_allreduce(h, h->err_xchg, 1, B2OT_F64, B2OT_OP_SUM);
     if (rc) return rc;
     emp_decide_kernel<<<1, 1, 0, h->stream>>>(h->st, h->err_xchg, h->err_hist, h->max_iter, h->stop_thr);
@@ -169,7 +173,7 @@ int launch_fin_g(const b2ot_emp* h) {
   p.nsplit = h->nsplitB;
   p.len = h->m;
   p.logw = h->logb;
-  if (!h->ar) {
+  if (!h->ar && !h->comm) {
     p.stage = 0;
     emp_fin_g_kernel<T><<<h->fin_blocks_g, 256, 0, h->stream>>>(p);
     B2OT_CHECK_LAUNCH();
@@ -293,6 +297,17 @@ extern "C" int b2ot_emp_set_allreduce(b2ot_emp* h, b2ot_allreduce_fn fn, void* c
   B2OT_REQUIRE(h != nullptr, "b2ot_emp_set_allreduce: null handle");
   h->ar = fn;
   h->ar_ctx = ctx;
+  return 0;
+}
+
+extern "C" int b2ot_emp_set_comm(b2ot_emp* h, b2ot_comm* comm) {
+  B2OT_REQUIRE(h != nullptr, "b2ot_emp_set_comm: null handle");
+  if (comm != nullptr) {
+    const size_t need = (size_t)h->m * esize(h->dtype);
+    B2OT_REQUIRE(comm->view.slot_bytes >= need, "b2ot_emp_set_comm: exchange slots hold %llu bytes, %zu needed",
+                 comm->view.slot_bytes, need);
+  }
+  h->comm = comm;
   return 0;
 }
 

@@ -118,7 +118,7 @@ class EmpiricalSolver:
     """One online-cost solve (or one block of source points of a sharded solve) on the current device."""
 
     def __init__(self, X_s, X_t, a, b, reg, metric="sqeuclidean", max_iter=10000, stop_thr=1e-9, variant="auto",
-                 group=None):
+                 group=None, exchange="peer"):
         self.lib = _lib.load()
         self.X_s, self.X_t = X_s, X_t
         self.n, self.m, self.d = X_s.shape[0], X_t.shape[0], X_s.shape[1]
@@ -139,8 +139,17 @@ class EmpiricalSolver:
                 _dense.stream_ptr(self.device)), "b2ot_emp_create")
         self.h = h
         self._cb = None
+        self.comm = None
         if group is not None:
-            self._install_allreduce(group)
+            if exchange == "peer":
+                from .comm import get_comm
+
+                self.comm = get_comm(group, self.device, (self.m + 1) * 8)
+                _lib.check(self.lib.b2ot_emp_set_comm(self.h, self.comm.h), "b2ot_emp_set_comm")
+            elif exchange == "nccl":
+                self._install_allreduce(group)
+            else:
+                raise ValueError(f"unknown exchange {exchange!r} (peer | nccl)")
 
     def _install_allreduce(self, group):
         import torch.distributed as dist_
@@ -184,6 +193,8 @@ class EmpiricalSolver:
         with torch.cuda.device(self.device):
             _lib.check(self.lib.b2ot_emp_solve(self.h, f0.data_ptr(), g0.data_ptr(), int(poll_every), C.byref(st),
                                                C.byref(ni), C.byref(ne)), "b2ot_emp_solve")
+        if st.value == _lib.ST_COMM_TIMEOUT:
+            raise _lib.B2otError("sharded solve: a peer rank never published its exchange flag (timeout)")
         return st.value, ni.value, ne.value
 
     def export(self):

@@ -24,7 +24,7 @@ def _as_host_tensor(x, dtype=None):
 
 
 def sinkhorn_from_host(a, b, M, reg, method="sinkhorn", numItermax=1000, stopThr=1e-9, device=None, group=None,
-                       n_total=None, chunk_rows=None, warmstart=None):
+                       n_total=None, chunk_rows=None, warmstart=None, exchange="peer"):
     """Solve from host buffers.  a: (n_local,), b: (m,), M: (n_local, m) CPU tensors / numpy arrays (pinned memory
     makes the upload asynchronous).  Returns a dict of HOST tensors {"u", "v", "err", "niter", "status"} plus
     {"h2d_bytes", "d2h_bytes"}.  With `group`, M/a are this rank's row block (see pot_b200.sharded)."""
@@ -79,7 +79,7 @@ def sinkhorn_from_host(a, b, M, reg, method="sinkhorn", numItermax=1000, stopThr
                 v0 = _as_host_tensor(warmstart[1], dt).to(dev)
             av, logb = torch.log(a_d), torch.log(b_d)
         solver = _dense.DenseSolver(mode, K, av, b_d, logb, max_iter=int(numItermax), check_every=10,
-                                    stop_thr=float(stopThr), group=group)
+                                    stop_thr=float(stopThr), group=group, exchange=exchange)
         status, niter, _ = solver.solve(u0, v0, poll_every=POLL_EVERY)
         u, v, errs = solver.export()
         solver.close()

@@ -2,8 +2,10 @@
 
 Rank r owns a contiguous block of rows of M (and of a, u); b, v and the column sums are replicated.
 Per iteration the ranks exchange exactly one vector: the m column sums K^T u (scaling domain) or the
-row-frame column marginals (log domain), plus one flag slot for the numerical guard, summed with one
-all-reduce (torch.distributed / NCCL over NVLink) between the sweep kernel and the finalize kernel.
+row-frame column marginals (log domain), plus one flag slot for the numerical guard.  Default exchange
+("peer"): each rank stores its vector into every peer's NVLink-mapped buffer from the reduce kernel and the
+finalize kernel sums the slots after polling the flags (pot_b200/comm.py, csrc/comm.cuh); exchange="nccl" is
+the baseline with one torch.distributed all-reduce between the sweep and the finalize kernel.
 Every rank evaluates the stop test on identical data, so all ranks stop at the same iteration without
 any further communication.
 
@@ -18,7 +20,7 @@ import torch
 from . import _dense, _lib
 from .bregman import _NOCONV, POLL_EVERY, _require_cuda_matrix, _rowmajor
 
-__all__ = ["shard_rows", "sinkhorn_knopp_sharded", "sinkhorn_log_sharded"]
+__all__ = ["shard_rows", "sinkhorn_knopp_sharded", "sinkhorn_log_sharded", "empirical_sinkhorn_sharded"]
 
 
 def shard_rows(n, world_size, rank):
@@ -36,7 +38,8 @@ def _total_rows(n_local, device, group):
     return int(t.item())
 
 
-def _solve_sharded(mode, a_local, b, M_local, reg, numItermax, stopThr, warmstart, group, n_total, variant):
+def _solve_sharded(mode, a_local, b, M_local, reg, numItermax, stopThr, warmstart, group, n_total, variant,
+                   exchange="peer"):
     M_local = _require_cuda_matrix(M_local, "M_local")
     n_loc, m = M_local.shape
     dt, dev = M_local.dtype, M_local.device
@@ -66,7 +69,7 @@ def _solve_sharded(mode, a_local, b, M_local, reg, numItermax, stopThr, warmstar
                 u0, v0 = warmstart[0].to(dt).contiguous(), warmstart[1].to(dt).contiguous()
             av, logb = torch.log(a_local), torch.log(b)
         solver = _dense.DenseSolver(mode, Kt, av, b, logb, max_iter=numItermax, check_every=10, stop_thr=stopThr,
-                                    variant=variant, group=group)
+                                    variant=variant, group=group, exchange=exchange)
         status, niter, _ = solver.solve(u0, v0, poll_every=POLL_EVERY)
         u, v, errs = solver.export()
         solver.close()
@@ -79,7 +82,7 @@ def sinkhorn_knopp_sharded(a_local, b, M_local, reg, numItermax=1000, stopThr=1e
     (or None with return_plan=False) and, with log=True, {"err", "niter", "u": local rows, "v": replicated}."""
     K, u, v, errs, niter, status = _solve_sharded("knopp", a_local, b, M_local, reg, int(numItermax),
                                                   float(stopThr), warmstart, group, n_total,
-                                                  kwargs.get("b2ot_variant", "auto"))
+                                                  kwargs.get("b2ot_variant", "auto"), kwargs.get("exchange", "peer"))
     if status == _lib.ST_NUMERR:
         warnings.warn("Warning: numerical errors at iteration %d" % niter)
     elif status == _lib.ST_MAXITER and warn:
@@ -96,7 +99,7 @@ def sinkhorn_log_sharded(a_local, b, M_local, reg, numItermax=1000, stopThr=1e-9
     """Log-domain Sinkhorn on a row-sharded problem (see sinkhorn_knopp_sharded)."""
     Mr, u, v, errs, niter, status = _solve_sharded("log", a_local, b, M_local, reg, int(numItermax),
                                                    float(stopThr), warmstart, group, n_total,
-                                                   kwargs.get("b2ot_variant", "auto"))
+                                                   kwargs.get("b2ot_variant", "auto"), kwargs.get("exchange", "peer"))
     if status == _lib.ST_MAXITER and warn:
         warnings.warn(_NOCONV)
     G = _dense.plan("log", Mr, u, v) if return_plan else None
@@ -104,3 +107,36 @@ def sinkhorn_log_sharded(a_local, b, M_local, reg, numItermax=1000, stopThr=1e-9
         return G, {"err": [torch.tensor(e, dtype=u.dtype, device=u.device) for e in errs], "niter": niter,
                    "log_u": u, "log_v": v, "u": torch.exp(u), "v": torch.exp(v)}
     return G
+
+
+def empirical_sinkhorn_sharded(X_s_local, X_t, reg, a_local=None, b=None, metric="sqeuclidean", numIterMax=10000,
+                               stopThr=1e-9, log=False, warn=True, warmstart=None, group=None, n_total=None, **kwargs):
+    """Online-cost (lazy) empirical Sinkhorn with the SOURCE points sharded across ranks: X_s_local / a_local /
+    f are this rank's block, X_t / b / g are replicated.  The f update is local; the g update combines the ranks'
+    column log-sum-exp partials (one max + one sum exchange of m values per iteration), the marginal check sums one
+    double every 10th iteration.  Same semantics as ot.bregman.empirical_sinkhorn(isLazy=True)
+    (ot/bregman/_empirical.py:193-271).  Returns (f_local, g) [+ {"err", "niter", "u", "v"}]."""
+    from .empirical import EmpiricalSolver, _points
+
+    X_s_local, X_t = _points(X_s_local, "X_s_local"), _points(X_t, "X_t")
+    n_loc, m = X_s_local.shape[0], X_t.shape[0]
+    dt, dev = X_s_local.dtype, X_s_local.device
+    if n_total is None:
+        n_total = _total_rows(n_loc, dev, group)
+    a_local = torch.full((n_loc,), 1.0 / n_total, dtype=dt, device=dev) if a_local is None else a_local.to(dt)
+    b = torch.full((m,), 1.0 / m, dtype=dt, device=dev) if b is None else b.to(dt)
+    if warmstart is None:
+        f0, g0 = torch.zeros(n_loc, dtype=dt, device=dev), torch.zeros(m, dtype=dt, device=dev)
+    else:
+        f0, g0 = warmstart[0].to(dt).contiguous(), warmstart[1].to(dt).contiguous()
+    solver = EmpiricalSolver(X_s_local, X_t, a_local, b, reg, metric, max_iter=int(numIterMax),
+                             stop_thr=float(stopThr), variant=kwargs.get("b2ot_variant", "auto"), group=group,
+                             exchange=kwargs.get("exchange", "peer"))
+    status, niter, _ = solver.solve(f0, g0)
+    f, g, errs = solver.export()
+    solver.close()
+    if status == _lib.ST_MAXITER and warn:
+        warnings.warn(_NOCONV)
+    if log:
+        return f, g, {"err": [torch.tensor(e, dtype=dt, device=dev) for e in errs], "niter": niter, "u": f, "v": g}
+    return f, g

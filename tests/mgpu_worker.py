@@ -1,0 +1,130 @@
+"""Worker of the multi-GPU parity tests; launched by tests/test_multigpu.py (or by hand) as
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node R --master-addr 127.0.0.1 --master-port P \
+        tests/mgpu_worker.py
+
+Every rank checks its own results and exits non-zero on a mismatch.  Checks (exchange = peer and nccl):
+  1. the stand-alone peer all-reduce against torch.distributed (sum / max, fp32 / fp64, 300 back-to-back calls);
+  2. row-sharded sinkhorn_knopp / sinkhorn_log against the CPU oracle (fp64 1e-10, fp32 1e-4) and against the
+     single-GPU solve (same niter, same err history), converged and fixed-iteration runs, ragged row split;
+  3. source-sharded empirical Sinkhorn against the oracle.
+"""
+import os
+import sys
+import warnings
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import pot_b200 as ot  # noqa: E402
+from oracle import sinkhorn_oracle as orc  # noqa: E402
+from pot_b200.comm import get_comm  # noqa: E402
+from pot_b200.sharded import (empirical_sinkhorn_sharded, shard_rows, sinkhorn_knopp_sharded,  # noqa: E402
+                              sinkhorn_log_sharded)
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    group = dist.group.WORLD
+
+    def check(cond, msg):
+        if not cond:
+            print(f"[rank {rank}] FAIL: {msg}", flush=True)
+            sys.exit(1)
+
+    # ---- 1. stand-alone peer all-reduce ----
+    comm = get_comm(group, dev, 1 << 20)
+    g = torch.Generator(device=dev).manual_seed(100 + rank)
+    for dt in (torch.float32, torch.float64):
+        for it in range(300):
+            n = 1 + (it * 37) % 5000
+            x = torch.randn(n, dtype=dt, device=dev, generator=g)
+            ref = x.clone()
+            op = "max" if it % 3 == 0 else "sum"
+            dist.all_reduce(ref, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
+            comm.all_reduce(x, op)
+            tol = 0 if op == "max" else (1e-5 if dt == torch.float32 else 1e-13)
+            check(torch.allclose(x, ref, rtol=tol, atol=tol), f"peer all-reduce {op} {dt} it {it}")
+    # results must be bit-identical on every rank
+    x = torch.randn(4097, dtype=torch.float32, device=dev, generator=g)
+    comm.all_reduce(x, "sum")
+    y = x.clone()
+    dist.broadcast(y, 0)
+    check(torch.equal(x, y), "peer all-reduce is not bit-identical across ranks")
+    if rank == 0:
+        print("peer all-reduce ok", flush=True)
+
+    # ---- 2. dense row-sharded solves ----
+    rng = np.random.RandomState(0)
+    n, m = 203, 160  # 203 rows: ragged split
+    xs, xt = rng.randn(n, 2), rng.randn(m, 2) + 1.0
+    M64 = orc.sqeuclidean(xs, xt)
+    M64 /= M64.max()
+    a64 = rng.rand(n) + 0.5
+    a64 /= a64.sum()
+    b64 = rng.rand(m) + 0.5
+    b64 /= b64.sum()
+    r0, r1 = shard_rows(n, world, rank)
+    for exchange in ("peer", "nccl"):
+        for dtype, tol in ((np.float64, 1e-10), (np.float32, 1e-4)):
+            M, a, b = M64.astype(dtype), a64.astype(dtype), b64.astype(dtype)
+            Ml, al, bd = (torch.as_tensor(M[r0:r1], device=dev), torch.as_tensor(a[r0:r1], device=dev),
+                          torch.as_tensor(b, device=dev))
+            for name, fn, ofn, key in (("knopp", sinkhorn_knopp_sharded, orc.sinkhorn_knopp, "u"),
+                                       ("log", sinkhorn_log_sharded, orc.sinkhorn_log, "log_u")):
+                for kw in (dict(numItermax=60, stopThr=0.0), dict(numItermax=2000, stopThr=1e-7 if dtype == np.float64 else 1e-5)):
+                    with warnings.catch_warnings():
+                        warnings.simplefilter("ignore")
+                        G, lg = fn(al, bd, Ml, 0.1, log=True, group=group, n_total=n, exchange=exchange, **kw)
+                        Gr, lgr = ofn(a, b, M, 0.1, log=True, **kw)
+                    check(lg["niter"] == lgr["niter"], f"{exchange} {name} {dtype.__name__} niter {lg['niter']} vs {lgr['niter']}")
+                    Gn = G.cpu().numpy().astype(np.float64)
+                    ref = Gr[r0:r1].astype(np.float64)
+                    err = np.abs(Gn - ref) / (np.abs(ref) + 1e-6 * Gr.max())
+                    check(err.max() < tol, f"{exchange} {name} {dtype.__name__} plan rel err {err.max():.3e}")
+                    check(len(lg["err"]) == len(lgr["err"]), f"{exchange} {name} err history length")
+                    # every rank holds the same replicated v and took the same decisions
+                    v = lg["v" if name == "knopp" else "log_v"].clone()
+                    v0 = v.clone()
+                    dist.broadcast(v0, 0)
+                    check(torch.equal(v, v0), f"{exchange} {name} replicated v differs across ranks")
+        if rank == 0:
+            print(f"dense sharded ok ({exchange})", flush=True)
+
+    # ---- 3. empirical, source points sharded ----
+    n, m, d = 301, 257, 5
+    xs = (rng.randn(n, d) / np.sqrt(d))
+    xt = (rng.randn(m, d) / np.sqrt(d) + 0.3)
+    r0, r1 = shard_rows(n, world, rank)
+    for exchange in ("peer", "nccl"):
+        for dtype, tol in ((np.float64, 1e-10), (np.float32, 1e-4)):
+            X, Y = xs.astype(dtype), xt.astype(dtype)
+            for kw in (dict(numIterMax=30, stopThr=-1.0), dict(numIterMax=3000, stopThr=1e-8 if dtype == np.float64 else 1e-4)):
+                with warnings.catch_warnings():
+                    warnings.simplefilter("ignore")
+                    f, gg, lg = empirical_sinkhorn_sharded(torch.as_tensor(X[r0:r1], device=dev), torch.as_tensor(Y, device=dev),
+                                                           0.5, log=True, group=group, n_total=n, exchange=exchange, **kw)
+                    fr, gr, lr = orc.empirical_sinkhorn_lazy(X, Y, 0.5, log=True, batchSize=64, **kw)
+                check(lg["niter"] == lr["niter"], f"emp {exchange} {dtype.__name__} niter {lg['niter']} vs {lr['niter']}")
+                ef = np.abs(f.cpu().numpy() - fr[r0:r1]).max() / max(1.0, np.abs(fr).max())
+                eg = np.abs(gg.cpu().numpy() - gr).max() / max(1.0, np.abs(gr).max())
+                check(ef < tol and eg < tol, f"emp {exchange} {dtype.__name__} potentials err {ef:.2e} {eg:.2e}")
+        if rank == 0:
+            print(f"empirical sharded ok ({exchange})", flush=True)
+
+    dist.barrier()
+    if rank == 0:
+        print("MGPU_OK", flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

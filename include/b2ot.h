@@ -154,7 +154,7 @@ int b2ot_batch_solve(int mode, int dtype, int64_t B, int64_t n, int64_t m, const
 #define B2OT_EMP_SIMT 1   /* register-tiled FMA sweep: any d, fp32 and fp64 */
 #define B2OT_EMP_TC 2     /* tcgen05 sweep: fp32, sqeuclidean */
 typedef struct b2ot_emp b2ot_emp;
-size_t b2ot_emp_workspace_bytes(int64_t n, int64_t m, int dtype, int max_iter);
+size_t b2ot_emp_workspace_bytes(int64_t n, int64_t m, int d, int dtype, int metric, int variant, int max_iter);
 int b2ot_emp_create(b2ot_emp** handle, int dtype, int64_t n, int64_t m, int d, const void* Xs, int64_t ldXs,
                     const void* Xt, int64_t ldXt, const void* a, const void* loga, const void* logb, double reg,
                     int metric, void* workspace, size_t workspace_bytes, int max_iter, double stop_thr, int variant,
@@ -165,6 +165,8 @@ int b2ot_emp_init(b2ot_emp* handle, const void* f0, const void* g0);
 /* enqueue n_iters iterations (row sweep, f update + pending check, column sweep, g update); no host sync */
 int b2ot_emp_iterate(b2ot_emp* handle, int n_iters);
 int b2ot_emp_poll(b2ot_emp* handle, int* status, int* iter);
+/* what the handle resolved to: B2OT_EMP_SIMT or B2OT_EMP_TC, and the reduction splits of the two sweeps */
+int b2ot_emp_info(const b2ot_emp* handle, int* variant, int* nsplit_rows, int* nsplit_cols);
 /* init + iterate until status != running, polling every `poll_every` iterations (<= 0: only at the end) */
 int b2ot_emp_solve(b2ot_emp* handle, const void* f0, const void* g0, int poll_every, int* status, int* niter,
                    int* n_err);

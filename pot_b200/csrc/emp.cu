@@ -7,6 +7,7 @@
 #include "../../include/b2ot.h"
 #include "comm_host.h"
 #include "emp_kernels.cuh"
+#include "emp_tc_kernels.cuh"
 #include "host_util.h"
 
 using namespace b2ot;
@@ -24,6 +25,8 @@ struct b2ot_emp {
   int err_cap;
   void *fring, *g, *xx, *yy, *cbuf, *pmaxA, *psumA, *pmaxB, *psumB;
   int nsplitA, nsplitB, fin_blocks_f, fin_blocks_g;
+  int use_tc, kc;          // tensor-core sweep: packed (split + pre-swizzled) clouds
+  void *packs, *packt;
   b2ot_allreduce_fn ar;
   void* ar_ctx;
   b2ot_comm* comm;  // NVLink peer-memory exchange (takes precedence over the hook)
@@ -50,15 +53,34 @@ int pick_nsplit(long long rows, long long cols) {
   return (int)ns;
 }
 
+// tensor-core sweep applies to fp32, squared euclidean cost, d <= 64; AUTO takes it when the problem is big enough
+// for 128 x 128 tiles to make sense
+bool resolve_tc(int dtype, int d, int metric, int variant, long long n, long long m) {
+  const bool eligible = dtype == B2OT_F32 && metric == B2OT_METRIC_SQEUCLIDEAN && d <= TC_MAX_D;
+  if (variant == B2OT_EMP_TC) return eligible;
+  if (variant == B2OT_EMP_SIMT) return false;
+  return eligible && std::max(n, m) >= 256;
+}
+int pick_nsplit_tc(long long rows, long long cols) {
+  const long long row_tiles = (rows + TC_BM - 1) / TC_BM;
+  const long long col_tiles = (cols + TC_BN - 1) / TC_BN;
+  long long ns = (148 + row_tiles - 1) / row_tiles;
+  ns = std::max<long long>(1, std::min<long long>(ns, std::min<long long>(64, col_tiles)));
+  return (int)ns;
+}
+
 struct EmpWs {
-  size_t off_state, off_blk, off_err, off_xchg, off_f, off_g, off_xx, off_yy, off_c, off_pa, off_pb, total;
-  int err_cap, nsA, nsB;
+  size_t off_state, off_blk, off_err, off_xchg, off_f, off_g, off_xx, off_yy, off_c, off_pa, off_pb, off_packs,
+      off_packt, total;
+  int err_cap, nsA, nsB, use_tc, kc;
 };
-EmpWs emp_ws(long long n, long long m, int dtype, int max_iter) {
+EmpWs emp_ws(long long n, long long m, int d, int dtype, int metric, int variant, int max_iter) {
   EmpWs L;
   const size_t sz = esize(dtype);
-  L.nsA = pick_nsplit(n, m);
-  L.nsB = pick_nsplit(m, n);
+  L.use_tc = resolve_tc(dtype, d, metric, variant, n, m) ? 1 : 0;
+  L.kc = (d + TC_KCH - 1) / TC_KCH;
+  L.nsA = L.use_tc ? pick_nsplit_tc(n, m) : pick_nsplit(n, m);
+  L.nsB = L.use_tc ? pick_nsplit_tc(m, n) : pick_nsplit(m, n);
   size_t o = 0;
   L.off_state = o;  o += 256;
   L.off_blk = o;    o += 1024 * sizeof(double);
@@ -72,6 +94,9 @@ EmpWs emp_ws(long long n, long long m, int dtype, int max_iter) {
   L.off_c = o;      o = align_up(o + 3 * (size_t)m * sz, 256);
   L.off_pa = o;     o = align_up(o + 2 * (size_t)L.nsA * n * sz, 256);
   L.off_pb = o;     o = align_up(o + 2 * (size_t)L.nsB * m * sz, 256);
+  o = align_up(o, 1024);
+  L.off_packs = o;  o += L.use_tc ? tc_pack_bytes(n, L.kc) : 0;
+  L.off_packt = o;  o += L.use_tc ? tc_pack_bytes(m, L.kc) : 0;
   L.total = o;
   return L;
 }
@@ -95,8 +120,35 @@ int launch_tile(const EmpTileParams& p, cudaStream_t s) {
 }
 
 // pass A (rows = source points, reduce over targets with g) or pass B (rows = targets, reduce over sources with f)
+int launch_tc_pass(const b2ot_emp* h, bool passA) {
+  EmpTcParams p;
+  memset(&p, 0, sizeof(p));
+  if (passA) {
+    p.Apack = (const float*)h->packs;  p.nx = h->n;  p.xx = (const float*)h->xx;
+    p.Bpack = (const float*)h->packt;  p.ny = h->m;  p.yy = (const float*)h->yy;
+    p.poty = (const float*)h->g;
+    p.pmax = (float*)h->pmaxA;  p.psum = (float*)h->psumA;  p.nsplit = h->nsplitA;
+  } else {
+    p.Apack = (const float*)h->packt;  p.nx = h->m;  p.xx = (const float*)h->yy;
+    p.Bpack = (const float*)h->packs;  p.ny = h->n;  p.yy = (const float*)h->xx;
+    p.poty = (const float*)h->fring;
+    p.pot_sel = &h->st->sel_f;
+    p.pot_stride = h->n;
+    p.pmax = (float*)h->pmaxB;  p.psum = (float*)h->psumB;  p.nsplit = h->nsplitB;
+  }
+  p.kc = h->kc;
+  p.k2 = (float)(1.4426950408889634 / h->reg);
+  p.status = &h->st->status;
+  p.expect_status = ST_RUNNING;
+  dim3 grid((unsigned)((p.nx + TC_BM - 1) / TC_BM), (unsigned)p.nsplit);
+  emp_tc_lse_kernel<<<grid, TC_THREADS, tc_smem_bytes(2), h->stream>>>(p);
+  B2OT_CHECK_LAUNCH();
+  return 0;
+}
+
 template <typename T>
 int launch_lse_pass(const b2ot_emp* h, bool passA) {
+  if (h->use_tc) return launch_tc_pass(h, passA);
   EmpTileParams p;
   memset(&p, 0, sizeof(p));
   if (passA) {
@@ -222,8 +274,9 @@ int emp_tail_t(b2ot_emp* h) {
 // ------------------------------------------------------------------------------------------------
 // C ABI
 // ------------------------------------------------------------------------------------------------
-extern "C" size_t b2ot_emp_workspace_bytes(int64_t n, int64_t m, int dtype, int max_iter) {
-  return emp_ws(n, m, dtype, max_iter).total;
+extern "C" size_t b2ot_emp_workspace_bytes(int64_t n, int64_t m, int d, int dtype, int metric, int variant,
+                                           int max_iter) {
+  return emp_ws(n, m, d, dtype, metric, variant, max_iter).total;
 }
 
 extern "C" int b2ot_emp_create(b2ot_emp** handle, int dtype, int64_t n, int64_t m, int d, const void* Xs, int64_t ldXs,
@@ -239,11 +292,14 @@ extern "C" int b2ot_emp_create(b2ot_emp** handle, int dtype, int64_t n, int64_t 
   B2OT_REQUIRE(metric == B2OT_METRIC_SQEUCLIDEAN || metric == B2OT_METRIC_EUCLIDEAN, "b2ot_emp_create: bad metric %d",
                metric);
   B2OT_REQUIRE(max_iter >= 1, "b2ot_emp_create: max_iter must be >= 1");
-  const EmpWs L = emp_ws(n, m, dtype, max_iter);
+  B2OT_REQUIRE(variant >= B2OT_EMP_AUTO && variant <= B2OT_EMP_TC, "b2ot_emp_create: bad variant %d", variant);
+  const EmpWs L = emp_ws(n, m, d, dtype, metric, variant, max_iter);
+  B2OT_REQUIRE(variant != B2OT_EMP_TC || L.use_tc,
+               "b2ot_emp_create: the tensor-core sweep needs fp32, sqeuclidean and d <= %d (got dtype %d, metric %d, d %d)",
+               TC_MAX_D, dtype, metric, d);
   B2OT_REQUIRE(workspace_bytes >= L.total, "b2ot_emp_create: workspace too small (%zu < %zu)", workspace_bytes,
                L.total);
   B2OT_REQUIRE(((uintptr_t)workspace) % 256 == 0, "b2ot_emp_create: workspace must be 256-byte aligned");
-  (void)variant;
   b2ot_emp* h = new (std::nothrow) b2ot_emp();
   B2OT_REQUIRE(h != nullptr, "b2ot_emp_create: out of host memory");
   memset(h, 0, sizeof(*h));
@@ -281,6 +337,14 @@ extern "C" int b2ot_emp_create(b2ot_emp** handle, int dtype, int64_t n, int64_t 
   h->psumA = ws + L.off_pa + (size_t)L.nsA * n * sz;
   h->pmaxB = ws + L.off_pb;
   h->psumB = ws + L.off_pb + (size_t)L.nsB * m * sz;
+  h->use_tc = L.use_tc;
+  h->kc = L.kc;
+  h->packs = ws + L.off_packs;
+  h->packt = ws + L.off_packt;
+  if (h->use_tc) {
+    B2OT_CUDA(cudaFuncSetAttribute(emp_tc_lse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)tc_smem_bytes(2)));
+  }
   h->fin_blocks_f = (int)std::max<long long>(1, std::min<long long>((n + 255) / 256, 1024));
   h->fin_blocks_g = (int)std::max<long long>(1, std::min<long long>((m + 255) / 256, 1024));
   (void)sm_count;
@@ -327,7 +391,18 @@ extern "C" int b2ot_emp_init(b2ot_emp* h, const void* f0, const void* g0) {
   if (h->dtype == B2OT_F32) {
     int rc = launch_sqnorm<float>(h->Xs, h->n, h->d, h->ldxs, h->xx, h->stream);
     if (rc) return rc;
-    return launch_sqnorm<float>(h->Xt, h->m, h->d, h->ldxt, h->yy, h->stream);
+    rc = launch_sqnorm<float>(h->Xt, h->m, h->d, h->ldxt, h->yy, h->stream);
+    if (rc || !h->use_tc) return rc;
+    // tensor-core sweep: split (hi, lo) + pre-swizzle both clouds once per solve
+    const long long us = (h->n + TC_BM - 1) / TC_BM * TC_BM * h->kc * 8;
+    const long long ut = (h->m + TC_BM - 1) / TC_BM * TC_BM * h->kc * 8;
+    emp_tc_pack_kernel<<<(unsigned)((us + 255) / 256), 256, 0, h->stream>>>((const float*)h->Xs, h->n, h->d, h->ldxs,
+                                                                           h->kc, (float*)h->packs);
+    B2OT_CHECK_LAUNCH();
+    emp_tc_pack_kernel<<<(unsigned)((ut + 255) / 256), 256, 0, h->stream>>>((const float*)h->Xt, h->m, h->d, h->ldxt,
+                                                                           h->kc, (float*)h->packt);
+    B2OT_CHECK_LAUNCH();
+    return 0;
   }
   int rc = launch_sqnorm<double>(h->Xs, h->n, h->d, h->ldxs, h->xx, h->stream);
   if (rc) return rc;
@@ -337,6 +412,14 @@ extern "C" int b2ot_emp_init(b2ot_emp* h, const void* f0, const void* g0) {
 extern "C" int b2ot_emp_iterate(b2ot_emp* h, int n_iters) {
   B2OT_REQUIRE(h != nullptr, "b2ot_emp_iterate: null handle");
   return h->dtype == B2OT_F32 ? emp_iterate_t<float>(h, n_iters) : emp_iterate_t<double>(h, n_iters);
+}
+
+extern "C" int b2ot_emp_info(const b2ot_emp* h, int* variant, int* nsplit_rows, int* nsplit_cols) {
+  B2OT_REQUIRE(h != nullptr, "b2ot_emp_info: null handle");
+  if (variant) *variant = h->use_tc ? B2OT_EMP_TC : B2OT_EMP_SIMT;
+  if (nsplit_rows) *nsplit_rows = h->nsplitA;
+  if (nsplit_cols) *nsplit_cols = h->nsplitB;
+  return 0;
 }
 
 extern "C" int b2ot_emp_poll(b2ot_emp* h, int* status, int* iter) {

@@ -1,0 +1,336 @@
+// Online-cost Sinkhorn sweep on the 5th-generation tensor cores (tcgen05 / TMEM), sm_100a, fp32 inputs.
+//
+// One half-iteration of the empirical solver is  out_i = LSE_j( pot_j - C_ij / reg )  with
+// C_ij = max(|x_i|^2 + |y_j|^2 - 2 x_i.y_j, 0).  The cross term is a GEMM (n x m x d); here it runs as
+// 128 x 128 output tiles of tcgen05.mma kind::tf32 with the accumulator in tensor memory:
+//
+//   * 3xTF32: every fp32 operand is split once per solve into hi = tf32(x) and lo = tf32(x - hi); a tile is
+//     D = Ahi.Bhi + Ahi.Blo + Alo.Bhi (fp32 accumulate), which keeps the dot product at fp32-level accuracy
+//     (dropped term lo.lo ~ 2^-22).  The split operands are stored PRE-SWIZZLED in the canonical K-major
+//     SWIZZLE_128B shared-memory layout, tile by tile, so that a plain 1-D TMA bulk copy (cp.async.bulk) lands
+//     a tile in shared memory exactly as the UMMA descriptors expect it - no tensor maps needed.
+//   * warp roles: warp 0 = producer (bulk copies: the row tile once, column tiles through a 2-stage ring),
+//     warp 1 = MMA issuer (one elected lane; 12 or 24 MMAs of 128x128x8 per tile; tcgen05.commit releases the
+//     smem stage and publishes the accumulator), warps 2-5 = epilogue (tcgen05.ld 32 lanes x 32 columns; one
+//     thread owns one row of the tile: cost, clamp, scale, online (max, sum 2^x) entirely in registers).
+//   * 4 accumulator stages (4 x 128 TMEM columns = all 512) decouple the MMA stream from the epilogue.
+// The n x m cost matrix never exists; HBM sees only the packed point clouds (L2 resident) and the vectors.
+// Bound: tensor pipe (3 x 2 n m d flop) with MUFU (n m ex2) and the FMA pipe (~7 instr / element) co-limiting.
+#pragma once
+
+#include "common.cuh"
+
+namespace b2ot {
+
+constexpr int TC_BM = 128;        // rows of an output tile (TMEM lanes)
+constexpr int TC_BN = 128;        // columns of an output tile
+constexpr int TC_KCH = 32;        // K elements per swizzle chunk (32 x 4 B = 128 B rows)
+constexpr int TC_SUB = 16384;     // bytes of one (chunk, hi|lo) sub-tile: 128 rows x 128 B
+constexpr int TC_NB = 2;          // shared-memory stages of the column operand
+constexpr int TC_NACC = 4;        // accumulator stages in tensor memory
+constexpr int TC_THREADS = 192;   // producer warp, MMA warp, 4 epilogue warps
+constexpr int TC_MAX_D = 64;
+
+__host__ __device__ inline size_t tc_tile_bytes(int kc) { return (size_t)kc * 2 * TC_SUB; }
+__host__ __device__ inline size_t tc_pack_bytes(long long rows, int kc) {
+  return (size_t)((rows + TC_BM - 1) / TC_BM) * tc_tile_bytes(kc);
+}
+inline size_t tc_smem_bytes(int kc) {
+  return 1024 /*alignment slack*/ + (size_t)(1 + TC_NB) * tc_tile_bytes(kc) + (size_t)TC_NACC * 2 * TC_BN * sizeof(float);
+}
+
+__device__ __forceinline__ float to_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+
+// Split + pre-swizzle: packed[tile][chunk c][hi|lo][group g of 8 rows][row r][16-byte unit (j ^ r)][4 floats].
+// One thread per (row, 16-byte unit).
+__global__ void __launch_bounds__(256) emp_tc_pack_kernel(const float* __restrict__ X, long long n, int d, long long ld,
+                                                          int kc, float* __restrict__ packed) {
+  const long long rows_pad = (n + TC_BM - 1) / TC_BM * TC_BM;
+  const int units = kc * 8;  // 16-byte units per row
+  const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= rows_pad * units) return;
+  const long long row = idx / units;
+  const int u = (int)(idx % units);
+  const int c = u >> 3, j = u & 7;
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (row < n) {
+    const int k0 = c * TC_KCH + j * 4;
+    const float* src = X + row * ld + k0;
+    if (k0 + 0 < d) v.x = src[0];
+    if (k0 + 1 < d) v.y = src[1];
+    if (k0 + 2 < d) v.z = src[2];
+    if (k0 + 3 < d) v.w = src[3];
+  }
+  float4 hi, lo;
+  hi.x = to_tf32(v.x);  lo.x = to_tf32(v.x - hi.x);
+  hi.y = to_tf32(v.y);  lo.y = to_tf32(v.y - hi.y);
+  hi.z = to_tf32(v.z);  lo.z = to_tf32(v.z - hi.z);
+  hi.w = to_tf32(v.w);  lo.w = to_tf32(v.w - hi.w);
+  const long long tile = row / TC_BM;
+  const int rt = (int)(row % TC_BM);
+  const int g = rt >> 3, r = rt & 7;
+  char* base = reinterpret_cast<char*>(packed) + tile * tc_tile_bytes(kc) + (size_t)(c * 2) * TC_SUB + g * 1024 + r * 128 +
+               ((j ^ r) << 4);
+  *reinterpret_cast<float4*>(base) = hi;
+  *reinterpret_cast<float4*>(base + TC_SUB) = lo;
+}
+
+// ---- tcgen05 PTX wrappers ----
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_holder, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_holder)), "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on an mbarrier when all MMAs issued so far by this thread have completed
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// K-major, SWIZZLE_128B operand descriptor: 8-row groups 1024 B apart
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+  return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+constexpr uint32_t TC_IDESC = (1u << 4) /*D = f32*/ | (2u << 7) /*A = tf32*/ | (2u << 10) /*B = tf32*/ |
+                              ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+
+#define B2OT_TMEM_LD32(taddr, v)                                                                                       \
+  asm volatile(                                                                                                        \
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "                                                                        \
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "                                        \
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"                        \
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),    \
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),         \
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),        \
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])                      \
+      : "r"(taddr)                                                                                                     \
+      : "memory")
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// mbarrier wait with a watchdog: a pipeline bug must end in a trap (launch error), never in a hung GPU
+__device__ __forceinline__ void mbar_wait_guard(uint64_t* bar, uint32_t parity) {
+  unsigned long long t0 = 0;
+  for (uint32_t spins = 0;; ++spins) {
+    if (mbar_try_wait(bar, parity)) return;
+    if ((spins & 0xFFFu) == 0xFFFu) {
+      unsigned long long now;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 4000000000ull) __trap();
+    }
+  }
+}
+
+struct EmpTcParams {
+  const float* Apack;   // row operand, packed tiles
+  const float* Bpack;   // column operand, packed tiles
+  const float* xx;      // |x_i|^2 (nx)
+  const float* yy;      // |y_j|^2 (ny)
+  const float* poty;    // potential along the reduced axis (ny)
+  const int* pot_sel;   // optional ring slot selector (see EmpTileParams)
+  long long pot_stride;
+  float* pmax;          // [nsplit][nx]
+  float* psum;
+  long long nx, ny;
+  int kc;               // K chunks of 32 (1 or 2)
+  int nsplit;
+  float k2;             // log2(e) / reg
+  const int* status;
+  int expect_status;
+};
+
+__global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcParams p) {
+  extern __shared__ unsigned char tc_smem_raw[];
+  __shared__ __align__(8) uint64_t a_full;
+  __shared__ __align__(8) uint64_t b_full[TC_NB], b_empty[TC_NB];
+  __shared__ __align__(8) uint64_t acc_full[TC_NACC], acc_empty[TC_NACC];
+  __shared__ uint32_t tmem_holder;
+
+  if (p.status != nullptr && *p.status != p.expect_status) return;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const size_t TB = tc_tile_bytes(p.kc);
+  // 1024-byte aligned operand area (SWIZZLE_128B atoms repeat every 1024 B)
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(tc_smem_raw) + 1023) & ~(uintptr_t)1023);
+  unsigned char* As = smem;
+  unsigned char* Bs = smem + TB;
+  float* colvec = reinterpret_cast<float*>(smem + (1 + TC_NB) * TB);  // [NACC][2][TC_BN]: pot * log2e, |y|^2
+
+  // column tiles of this block
+  const long long ctiles = (p.ny + TC_BN - 1) / TC_BN;
+  const long long per = (ctiles + p.nsplit - 1) / p.nsplit;
+  const long long ct0 = (long long)blockIdx.y * per;
+  const long long ct1 = (ct0 + per < ctiles) ? ct0 + per : ctiles;
+  const long long ntiles = ct1 > ct0 ? ct1 - ct0 : 0;
+  const long long row_tile = blockIdx.x;
+
+  if (tid == 0) {
+    mbar_init(&a_full, 1);
+    for (int s = 0; s < TC_NB; ++s) {
+      mbar_init(&b_full[s], 1);
+      mbar_init(&b_empty[s], 1);
+    }
+    for (int s = 0; s < TC_NACC; ++s) {
+      mbar_init(&acc_full[s], 1);
+      mbar_init(&acc_empty[s], 128);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(&tmem_holder, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_holder;
+
+  if (warp == 0) {
+    // ===== producer: bulk copies of pre-swizzled tiles =====
+    if (lane == 0 && ntiles > 0) {
+      const unsigned char* Ag = reinterpret_cast<const unsigned char*>(p.Apack) + (size_t)row_tile * TB;
+      mbar_arrive_expect_tx(&a_full, (uint32_t)TB);
+      for (size_t o = 0; o < TB; o += TC_SUB) bulk_g2s(As + o, Ag + o, TC_SUB, &a_full);
+      for (long long t = 0; t < ntiles; ++t) {
+        const int s = (int)(t % TC_NB);
+        const uint32_t ph = (uint32_t)((t / TC_NB) & 1);
+        mbar_wait_guard(&b_empty[s], ph ^ 1u);
+        const unsigned char* Bg = reinterpret_cast<const unsigned char*>(p.Bpack) + (size_t)(ct0 + t) * TB;
+        mbar_arrive_expect_tx(&b_full[s], (uint32_t)TB);
+        for (size_t o = 0; o < TB; o += TC_SUB) bulk_g2s(Bs + (size_t)s * TB + o, Bg + o, TC_SUB, &b_full[s]);
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (ntiles > 0) {
+      mbar_wait_guard(&a_full, 0);
+      const uint32_t a_addr = smem_u32(As);
+      for (long long t = 0; t < ntiles; ++t) {
+        const int s = (int)(t % TC_NB);
+        const uint32_t bph = (uint32_t)((t / TC_NB) & 1);
+        const int as = (int)(t % TC_NACC);
+        const uint32_t aph = (uint32_t)((t / TC_NACC) & 1);
+        mbar_wait_guard(&acc_empty[as], aph ^ 1u);
+        mbar_wait_guard(&b_full[s], bph);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t b_addr = smem_u32(Bs + (size_t)s * TB);
+          const uint32_t d_tmem = tmem_base + (uint32_t)(as * TC_BN);
+          uint32_t acc = 0;
+          for (int c = 0; c < p.kc; ++c) {
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+              const uint32_t off_hi = (uint32_t)((c * 2) * TC_SUB + ks * 32);
+              const uint32_t off_lo = off_hi + TC_SUB;
+              const uint64_t ah = umma_desc_sw128(a_addr + off_hi), al = umma_desc_sw128(a_addr + off_lo);
+              const uint64_t bh = umma_desc_sw128(b_addr + off_hi), bl = umma_desc_sw128(b_addr + off_lo);
+              umma_tf32(d_tmem, al, bh, TC_IDESC, acc);  // small terms first
+              umma_tf32(d_tmem, ah, bl, TC_IDESC, 1u);
+              umma_tf32(d_tmem, ah, bh, TC_IDESC, 1u);
+              acc = 1u;
+            }
+          }
+          umma_commit(&b_empty[s]);     // smem stage free once these MMAs have read it
+          umma_commit(&acc_full[as]);   // accumulator complete
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ===== epilogue: one thread = one row of the tile =====
+    const int q = warp & 3;                  // TMEM lane quarter this warp may access
+    const int et = tid - 64;                 // 0..127 among the epilogue threads
+    const long long row = row_tile * TC_BM + q * 32 + lane;
+    const float xi = (row < p.nx) ? p.xx[row] : 0.f;
+    const float* potg = p.poty;
+    if (p.pot_sel != nullptr) potg += (long long)(*p.pot_sel) * p.pot_stride;
+    const float LOG2E = 1.4426950408889634f;
+    const float nk2 = -p.k2;
+    float m_run = -CUDART_INF_F, s_run = 0.f;
+    for (long long t = 0; t < ntiles; ++t) {
+      const int as = (int)(t % TC_NACC);
+      const uint32_t aph = (uint32_t)((t / TC_NACC) & 1);
+      float* cg = colvec + (size_t)as * 2 * TC_BN;
+      float* cy = cg + TC_BN;
+      {
+        const long long j = (ct0 + t) * TC_BN + et;
+        const bool ok = j < p.ny;
+        cg[et] = ok ? potg[j] * LOG2E : -CUDART_INF_F;
+        cy[et] = ok ? p.yy[j] : 0.f;
+      }
+      named_bar_sync(1, 128);
+      mbar_wait_guard(&acc_full[as], aph);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * TC_BN);
+#pragma unroll 1
+      for (int ch = 0; ch < TC_BN / 32; ++ch) {
+        uint32_t v[32];
+        B2OT_TMEM_LD32(taddr + (uint32_t)(ch * 32), v);
+        tmem_ld_wait();
+        float tv[32];
+        float cmax = -CUDART_INF_F;
+#pragma unroll
+        for (int g4 = 0; g4 < 8; ++g4) {
+          const float4 gq = *reinterpret_cast<const float4*>(cg + ch * 32 + g4 * 4);
+          const float4 yq = *reinterpret_cast<const float4*>(cy + ch * 32 + g4 * 4);
+          const float gg[4] = {gq.x, gq.y, gq.z, gq.w};
+          const float yv[4] = {yq.x, yq.y, yq.z, yq.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float dot = __uint_as_float(v[g4 * 4 + e]);
+            const float c = fmaxf(fmaf(-2.f, dot, xi + yv[e]), 0.f);  // clamp: ot/utils.py:299
+            const float tt = fmaf(nk2, c, gg[e]);                      // (pot_j - C_ij / reg) * log2(e)
+            tv[g4 * 4 + e] = tt;
+            cmax = fmaxf(cmax, tt);
+          }
+        }
+        const float m_new = fmaxf(m_run, cmax);
+        const float mref = (m_new == -CUDART_INF_F) ? 0.f : m_new;
+        float s0 = s_run * ex2_approx(m_run - mref), s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+        for (int e = 0; e < 32; e += 4) {
+          s0 += ex2_approx(tv[e] - mref);
+          s1 += ex2_approx(tv[e + 1] - mref);
+          s2 += ex2_approx(tv[e + 2] - mref);
+          s3 += ex2_approx(tv[e + 3] - mref);
+        }
+        s_run = (s0 + s1) + (s2 + s3);
+        m_run = m_new;
+      }
+      tc_fence_before();
+      mbar_arrive(&acc_empty[as]);
+    }
+    if (row < p.nx) {
+      const float LN2 = 0.6931471805599453f;
+      p.pmax[(long long)blockIdx.y * p.nx + row] = m_run * LN2;   // back to natural-log units
+      p.psum[(long long)blockIdx.y * p.nx + row] = s_run;
+    }
+  }
+
+  // ---- teardown ----
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace b2ot

@@ -127,9 +127,10 @@ class EmpiricalSolver:
         self.loga, self.logb = torch.log(a).contiguous(), torch.log(b).contiguous()
         self.max_iter = int(max_iter)
         code = _dense.dtype_code(self.dtype)
-        nbytes = self.lib.b2ot_emp_workspace_bytes(self.n, self.m, code, self.max_iter)
-        self.ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
         var = {"auto": _lib.EMP_AUTO, "simt": _lib.EMP_SIMT, "tc": _lib.EMP_TC}[variant]
+        nbytes = self.lib.b2ot_emp_workspace_bytes(self.n, self.m, self.d, code, _metric_code(metric), var,
+                                                   self.max_iter)
+        self.ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
         h = C.c_void_p()
         with torch.cuda.device(self.device):
             _lib.check(self.lib.b2ot_emp_create(
@@ -171,6 +172,12 @@ class EmpiricalSolver:
 
         self._cb = _lib.ALLREDUCE_FN(hook)
         _lib.check(self.lib.b2ot_emp_set_allreduce(self.h, self._cb, None), "b2ot_emp_set_allreduce")
+
+    def info(self):
+        v, a, b = C.c_int(), C.c_int(), C.c_int()
+        _lib.check(self.lib.b2ot_emp_info(self.h, C.byref(v), C.byref(a), C.byref(b)), "b2ot_emp_info")
+        return {"variant": {_lib.EMP_SIMT: "simt", _lib.EMP_TC: "tc"}[v.value], "nsplit_rows": a.value,
+                "nsplit_cols": b.value}
 
     def init(self, f0, g0):
         self._f0, self._g0 = f0, g0

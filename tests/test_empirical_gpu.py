@@ -192,3 +192,61 @@ def test_lazy_equals_dense_log_solver():
     np.testing.assert_allclose(P.sum(1).cpu().numpy(), G.sum(1).cpu().numpy(), atol=1e-5)
     np.testing.assert_allclose(P.sum(0).cpu().numpy(), G.sum(0).cpu().numpy(), atol=1e-5)
     np.testing.assert_allclose(P.cpu().numpy(), G.cpu().numpy(), atol=1e-5)
+
+
+# ------------------------------------------------------------------------------------------------
+# tensor-core sweep (tcgen05, 3xTF32): fp32, sqeuclidean, d <= 64
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("case", [c for c in EMP if "_f32_" in c])
+def test_tc_golden(golden, case):
+    xs, xt, a, b = (golden(case, k) for k in ("xs", "xt", "a", "b"))
+    reg, its = float(golden(case, "reg")), int(golden(case, "its"))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        f, g, lg = ot.empirical_sinkhorn(dev(xs), dev(xt), reg, dev(a), dev(b), numIterMax=its, stopThr=-1, isLazy=True,
+                                         log=True, b2ot_variant="tc")
+    logclose(f, golden(case, "f"), 1e-4, "f (tc)")
+    logclose(g, golden(case, "g"), 1e-4, "g (tc)")
+    assert lg["niter"] == its - 1
+    errs_close(lg["err"], golden(case, "err"), "f32")
+
+
+@pytest.mark.parametrize("shape", [(1, 9, 2), (130, 127, 3), (200, 333, 16), (513, 190, 64), (257, 1030, 33), (1500, 900, 64)])
+def test_tc_vs_oracle(shape):
+    """The tcgen05 sweep against the fp64 oracle: ragged tiles, 1 and 2 K-chunks, reduction splits, weights,
+    warm start.  Also the auto variant and the register-tiled sweep must agree with it."""
+    n, m, d = shape
+    rng = np.random.RandomState(11 * n + m)
+    xs = (rng.randn(n, d) / np.sqrt(d)).astype(np.float32)
+    xt = (rng.randn(m, d) / np.sqrt(d) + 0.3).astype(np.float32)
+    a = rng.rand(n) + 0.2
+    b = rng.rand(m) + 0.2
+    a, b = (a / a.sum()).astype(np.float32), (b / b.sum()).astype(np.float32)
+    ws = (rng.randn(n).astype(np.float32) * 0.1, rng.randn(m).astype(np.float32) * 0.1)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        fr, gr, lr = orc.empirical_sinkhorn_lazy(xs.astype(np.float64), xt.astype(np.float64), 0.5, a.astype(np.float64),
+                                                 b.astype(np.float64), numIterMax=20, stopThr=-1, batchSize=256, log=True,
+                                                 warmstart=(ws[0].astype(np.float64), ws[1].astype(np.float64)))
+        out = {}
+        for variant in ("tc", "simt", "auto"):
+            f, g, lg = ot.empirical_sinkhorn(dev(xs), dev(xt), 0.5, dev(a), dev(b), numIterMax=20, stopThr=-1,
+                                             isLazy=True, log=True, warmstart=(dev(ws[0]), dev(ws[1])),
+                                             b2ot_variant=variant)
+            logclose(f, fr, 1e-4, f"f ({variant})")
+            logclose(g, gr, 1e-4, f"g ({variant})")
+            assert lg["niter"] == 19 and len(lg["err"]) == 2
+            out[variant] = (f, g)
+    # the two sweeps differ only by round-off (3xTF32 keeps the dot product at fp32 level)
+    assert float(torch.abs(out["tc"][0] - out["simt"][0]).max()) < 2e-5 * max(1.0, float(np.abs(fr).max()))
+
+
+def test_tc_rejects_ineligible():
+    rng = np.random.RandomState(0)
+    xs, xt = dev(rng.randn(20, 70).astype(np.float32)), dev(rng.randn(30, 70).astype(np.float32))
+    with pytest.raises(_lib.B2otError, match="tensor-core sweep needs"):
+        ot.empirical_sinkhorn(xs, xt, 1.0, isLazy=True, numIterMax=5, b2ot_variant="tc")
+    with pytest.raises(_lib.B2otError, match="tensor-core sweep needs"):
+        ot.empirical_sinkhorn(xs[:, :8].double(), xt[:, :8].double(), 1.0, isLazy=True, numIterMax=5, b2ot_variant="tc")
+    f, g = ot.empirical_sinkhorn(xs, xt, 1.0, isLazy=True, numIterMax=5, warn=False)  # auto -> register-tiled sweep
+    assert torch.isfinite(f).all()

@@ -226,31 +226,12 @@ def ours(args):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    # ---- e2e: whole solve from pinned host memory ----
-    e2e = None
+    # pinned host copy of M for the end-to-end leg (made before M is turned into K in place)
+    M_host = None
     if not args.no_e2e:
         M_host = torch.empty((nloc, m), dtype=torch.float32, pin_memory=True)
         M_host.copy_(Mdev)
-        a_host = torch.full((nloc,), 1.0 / n, dtype=torch.float32).pin_memory()
-        b_host = torch.full((m,), 1.0 / m, dtype=torch.float32).pin_memory()
         torch.cuda.synchronize(dev)
-        sinkhorn_from_host(a_host, b_host, M_host, REG, numItermax=min(W, 5), stopThr=0.0, device=dev, group=group,
-                           n_total=n, exchange=args.exchange)  # warm-up solve (allocator, NCCL channels, kernel images)
-        barrier()
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ev0.record()
-        res = sinkhorn_from_host(a_host, b_host, M_host, REG, numItermax=K_steps, stopThr=0.0, device=dev,
-                                 group=group, n_total=n, exchange=args.exchange)
-        ev1.record()
-        barrier()
-        t_e2e = max_over_ranks(ev0.elapsed_time(ev1) * 1e-3)
-        assert res["niter"] == K_steps - 1, res["niter"]
-        e2e = {"value": K_steps / t_e2e, "unit": "it/s",
-               "h2d_bytes_per_step": int(res["h2d_bytes"] * world / K_steps),
-               "d2h_bytes_per_step": int(res["d2h_bytes"] * world / K_steps),
-               "solve_seconds": t_e2e, "iterations_per_solve": K_steps,
-               "note": "one solve of `steps` iterations from pinned host M; bytes = whole-job bytes of the solve / steps"}
-        del M_host
 
     # ---- device-resident iterations/s ----
     _lib.check(lib.b2ot_kexp(Mdev.data_ptr(), Mdev.data_ptr(), nloc, m, Mdev.stride(0), Mdev.stride(0), REG,
@@ -285,6 +266,8 @@ def ours(args):
     finite = bool(torch.isfinite(u).all().item() and torch.isfinite(v).all().item())
     info = solver.info()
     solver.close()
+    del solver, Kmat, Mdev
+    torch.cuda.empty_cache()
     alg_bytes = 4.0 * nloc * m + 4.0 * (2 * nloc + 3 * m)
     peak, peak_src = peaks()
     achieved = alg_bytes / (sweep_ms * 1e-3) / 1e9
@@ -294,6 +277,30 @@ def ours(args):
             traffic = json.load(f).get(f"knopp_f32_{nloc}x{m}")
     except Exception:
         pass
+
+    # ---- e2e: whole solve from pinned host memory ----
+    e2e = None
+    if not args.no_e2e:
+        a_host = torch.full((nloc,), 1.0 / n, dtype=torch.float32).pin_memory()
+        b_host = torch.full((m,), 1.0 / m, dtype=torch.float32).pin_memory()
+        torch.cuda.synchronize(dev)
+        sinkhorn_from_host(a_host, b_host, M_host, REG, numItermax=min(W, 5), stopThr=0.0, device=dev, group=group,
+                           n_total=n, exchange=args.exchange)  # warm-up solve (allocator, NCCL channels, kernel images)
+        barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        res = sinkhorn_from_host(a_host, b_host, M_host, REG, numItermax=K_steps, stopThr=0.0, device=dev,
+                                 group=group, n_total=n, exchange=args.exchange)
+        ev1.record()
+        barrier()
+        t_e2e = max_over_ranks(ev0.elapsed_time(ev1) * 1e-3)
+        assert res["niter"] == K_steps - 1, res["niter"]
+        e2e = {"value": K_steps / t_e2e, "unit": "it/s",
+               "h2d_bytes_per_step": int(res["h2d_bytes"] * world / K_steps),
+               "d2h_bytes_per_step": int(res["d2h_bytes"] * world / K_steps),
+               "solve_seconds": t_e2e, "iterations_per_solve": K_steps,
+               "note": "one solve of `steps` iterations from pinned host M; bytes = whole-job bytes of the solve / steps"}
+        del M_host
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:

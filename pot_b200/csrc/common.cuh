@@ -78,6 +78,38 @@ __device__ __forceinline__ double max_t(double a, double b) { return fmax(a, b);
 __device__ __forceinline__ bool finite_t(float x) { return isfinite(x); }
 __device__ __forceinline__ bool finite_t(double x) { return isfinite(x); }
 
+// ---- packed fp32x2 arithmetic (sm_100: FADD2 / FFMA2, one issue slot for two lanes of work) ----
+__device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(unsigned long long v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+// (x0, x1) += (y0, y1)
+__device__ __forceinline__ void add2(float& x0, float& x1, float y0, float y1) {
+  unsigned long long r;
+  asm("add.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pack2(x0, x1)), "l"(pack2(y0, y1)));
+  unpack2(r, x0, x1);
+}
+// (d0, d1) = (a0, a1) * (b0, b1) + (c0, c1)
+__device__ __forceinline__ void fma2(float& d0, float& d1, float a0, float a1, float b0, float b1, float c0, float c1) {
+  unsigned long long r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(pack2(a0, a1)), "l"(pack2(b0, b1)), "l"(pack2(c0, c1)));
+  unpack2(r, d0, d1);
+}
+__device__ __forceinline__ float max3(float a, float b, float c) {
+  float r;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
+}
+__device__ __forceinline__ float ex2_ftz(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 // ---- element access on the 16-byte vector types ----
 __device__ __forceinline__ float& elem(float4& v, int i) { return (&v.x)[i]; }
 __device__ __forceinline__ double& elem(double2& v, int i) { return (&v.x)[i]; }

@@ -196,6 +196,9 @@ __global__ void __launch_bounds__(NCW * 32, OCC) fused_sweep_kernel(const SweepP
     // ---- phase A: this warp's partial row reductions over its columns ----
     T pay[NQ];
     T wref[R];  // LOG: this warp's exp reference per row
+    T wcorr[R]; // LOG fp32: first-order correction of the rounded reference (1 elsewhere)
+#pragma unroll
+    for (int r = 0; r < R; ++r) wcorr[r] = (T)1;
     if (MODE == MODE_KNOPP) {
 #pragma unroll
       for (int r = 0; r < R; ++r) {
@@ -215,6 +218,74 @@ __global__ void __launch_bounds__(NCW * 32, OCC) fused_sweep_kernel(const SweepP
       for (int o = 16; o > 0; o >>= 1) {
 #pragma unroll
         for (int r = 0; r < R; ++r) pay[r] += __shfl_xor_sync(0xffffffffu, pay[r], o);
+      }
+    } else if constexpr (sizeof(T) == 4) {
+      // fp32 log-domain row pass on packed fp32x2 arithmetic: x = Mr + v (FADD2), row maximum on four
+      // independent FMNMX3 chains, then e = 2^(x log2e - ref log2e) as one FFMA2 + MUFU.EX2 per element.
+      T mx[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        float m0 = neg_inf<float>(), m1 = m0, m2 = m0, m3 = m0;
+#pragma unroll
+        for (int k = 0; k < VPT; k += 2) {
+          float4& q0 = reinterpret_cast<float4&>(kreg[r][k]);
+          float4& q1 = reinterpret_cast<float4&>(kreg[r][k + (VPT > 1 ? 1 : 0)]);
+          const float4& w0 = reinterpret_cast<const float4&>(vreg[k]);
+          const float4& w1 = reinterpret_cast<const float4&>(vreg[k + (VPT > 1 ? 1 : 0)]);
+          add2(q0.x, q0.y, w0.x, w0.y);
+          add2(q0.z, q0.w, w0.z, w0.w);
+          if (VPT > 1) {
+            add2(q1.x, q1.y, w1.x, w1.y);
+            add2(q1.z, q1.w, w1.z, w1.w);
+            m0 = max3(m0, q0.x, q1.x);
+            m1 = max3(m1, q0.y, q1.y);
+            m2 = max3(m2, q0.z, q1.z);
+            m3 = max3(m3, q0.w, q1.w);
+          } else {
+            m0 = fmaxf(m0, q0.x);
+            m1 = fmaxf(m1, q0.y);
+            m2 = fmaxf(m2, q0.z);
+            m3 = fmaxf(m3, q0.w);
+          }
+        }
+        mx[r] = fmaxf(max3(m0, m1, m2), m3);
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) mx[r] = max_t(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], o));
+      }
+      constexpr float L2E = 1.4426950408889634f;
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const float ref = (mx[r] == neg_inf<float>()) ? 0.f : (float)mx[r];
+        const float nref = -ref * L2E;
+        // the rounding of ref * log2e is a common factor 2^lo of the whole row: divide it back out of the sum here
+        // and out of the row-frame factor f_i below (wcorr)
+        const float lo = fmaf(ref, L2E, nref);  // exact product minus its rounding
+        wcorr[r] = (T)(1.f - lo * 0.6931471805599453f);
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+        for (int k = 0; k < VPT; ++k) {
+          float4& q = reinterpret_cast<float4&>(kreg[r][k]);
+          float t0, t1, t2, t3;
+          fma2(t0, t1, q.x, q.y, L2E, L2E, nref, nref);
+          fma2(t2, t3, q.z, q.w, L2E, L2E, nref, nref);
+          q.x = ex2_ftz(t0);
+          q.y = ex2_ftz(t1);
+          q.z = ex2_ftz(t2);
+          q.w = ex2_ftz(t3);
+          add2(s0, s1, q.x, q.y);
+          add2(s2, s3, q.z, q.w);
+        }
+        wref[r] = (T)ref;
+        pay[2 * r] = mx[r];
+        pay[2 * r + 1] = (T)(((s0 + s1) + (s2 + s3)) * (float)wcorr[r]);
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) pay[2 * r + 1] += __shfl_xor_sync(0xffffffffu, pay[2 * r + 1], o);
       }
     } else {
       T mx[R];
@@ -340,18 +411,32 @@ __global__ void __launch_bounds__(NCW * 32, OCC) fused_sweep_kernel(const SweepP
 #pragma unroll
       for (int r = 0; r < R; ++r) {
         const T u = areg[r] - (M[r] + log_t(Ssum[r]));
-        urow[r] = (r < rv) ? exp_t(wref[r] + u) : (T)0;
+        urow[r] = (r < rv) ? exp_t(wref[r] + u) * wcorr[r] : (T)0;
         if (crank == 0 && tid == r && r < rv) unew[row0 + r] = u;
       }
     }
 
     // ---- phase B: the resident tile feeds the column accumulators ----
+    if constexpr (sizeof(T) == 4 && MODE == MODE_LOG) {
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
+      for (int r = 0; r < R; ++r) {
+        const float ur = (float)urow[r];
 #pragma unroll
-      for (int k = 0; k < VPT; ++k) {
+        for (int k = 0; k < VPT; ++k) {
+          const float4& q = reinterpret_cast<const float4&>(kreg[r][k]);
+          float4& ac = reinterpret_cast<float4&>(acc[k]);
+          fma2(ac.x, ac.y, q.x, q.y, ur, ur, ac.x, ac.y);
+          fma2(ac.z, ac.w, q.z, q.w, ur, ur, ac.z, ac.w);
+        }
+      }
+    } else {
 #pragma unroll
-        for (int i = 0; i < VEC; ++i) elem(acc[k], i) = fma(elem(kreg[r][k], i), urow[r], elem(acc[k], i));
+      for (int r = 0; r < R; ++r) {
+#pragma unroll
+        for (int k = 0; k < VPT; ++k) {
+#pragma unroll
+          for (int i = 0; i < VEC; ++i) elem(acc[k], i) = fma(elem(kreg[r][k], i), urow[r], elem(acc[k], i));
+        }
       }
     }
 

@@ -62,11 +62,25 @@ bool resolve_tc(int dtype, int d, int metric, int variant, long long n, long lon
   return eligible && std::max(n, m) >= 256;
 }
 int pick_nsplit_tc(long long rows, long long cols) {
+  // CTAs = row tiles x splits of the reduced axis, one CTA per SM at a time: take the split whose last wave is
+  // fullest (ties: fewer splits), keeping at least 8 column tiles per CTA so the row operand load stays amortised
   const long long row_tiles = (rows + TC_BM - 1) / TC_BM;
   const long long col_tiles = (cols + TC_BN - 1) / TC_BN;
-  long long ns = (148 + row_tiles - 1) / row_tiles;
-  ns = std::max<long long>(1, std::min<long long>(ns, std::min<long long>(64, col_tiles)));
-  return (int)ns;
+  const long long sms = sm_count();
+  const long long ns_max = std::max<long long>(1, std::min<long long>(64, col_tiles / 8));
+  long long best = 1;
+  double best_eff = -1.0;
+  for (long long ns = 1; ns <= ns_max; ++ns) {
+    const long long per = (col_tiles + ns - 1) / ns;          // column tiles per CTA (the longest one)
+    const long long ctas = row_tiles * ns;
+    const long long waves = (ctas + sms - 1) / sms;
+    const double eff = (double)(row_tiles * col_tiles) / (double)(waves * sms * per);
+    if (eff > best_eff + 1e-3) {
+      best_eff = eff;
+      best = ns;
+    }
+  }
+  return (int)best;
 }
 
 struct EmpWs {

@@ -11,8 +11,11 @@
 //     a tile in shared memory exactly as the UMMA descriptors expect it - no tensor maps needed.
 //   * warp roles: warp 0 = producer (bulk copies: the row tile once, column tiles through a 2-stage ring),
 //     warp 1 = MMA issuer (one elected lane; 12 or 24 MMAs of 128x128x8 per tile; tcgen05.commit releases the
-//     smem stage and publishes the accumulator), warps 2-5 = epilogue (tcgen05.ld 32 lanes x 32 columns; one
-//     thread owns one row of the tile: cost, clamp, scale, online (max, sum 2^x) entirely in registers).
+//     smem stage and publishes the accumulator), warps 2-9 = epilogue: two warpgroups take alternate column tiles
+//     (two warps per SM sub-partition, so one warp's MUFU phase overlaps the other's FMA phase); one thread owns
+//     one row of the tile: tcgen05.ld 32 lanes x 32 columns (double-buffered), cost, clamp, scale, online
+//     (max, sum 2^x) entirely in registers on packed fp32x2 arithmetic (FADD2 / FFMA2 / FMNMX3, ~5 issue slots
+//     per element); the per-column vectors are prefetched one tile ahead.
 //   * 4 accumulator stages (4 x 128 TMEM columns = all 512) decouple the MMA stream from the epilogue.
 // The n x m cost matrix never exists; HBM sees only the packed point clouds (L2 resident) and the vectors.
 // Bound: tensor pipe (3 x 2 n m d flop) with MUFU (n m ex2) and the FMA pipe (~7 instr / element) co-limiting.
@@ -28,7 +31,8 @@ constexpr int TC_KCH = 32;        // K elements per swizzle chunk (32 x 4 B = 12
 constexpr int TC_SUB = 16384;     // bytes of one (chunk, hi|lo) sub-tile: 128 rows x 128 B
 constexpr int TC_NB = 2;          // shared-memory stages of the column operand
 constexpr int TC_NACC = 4;        // accumulator stages in tensor memory
-constexpr int TC_THREADS = 192;   // producer warp, MMA warp, 4 epilogue warps
+constexpr int TC_EPI_WARPS = 8;    // two epilogue warpgroups, alternating column tiles
+constexpr int TC_THREADS = 64 + 32 * TC_EPI_WARPS;  // producer warp, MMA warp, epilogue warps
 constexpr int TC_MAX_D = 64;
 
 __host__ __device__ inline size_t tc_tile_bytes(int kc) { return (size_t)kc * 2 * TC_SUB; }
@@ -36,7 +40,8 @@ __host__ __device__ inline size_t tc_pack_bytes(long long rows, int kc) {
   return (size_t)((rows + TC_BM - 1) / TC_BM) * tc_tile_bytes(kc);
 }
 inline size_t tc_smem_bytes(int kc) {
-  return 1024 /*alignment slack*/ + (size_t)(1 + TC_NB) * tc_tile_bytes(kc) + (size_t)TC_NACC * 2 * TC_BN * sizeof(float);
+  return 1024 /*alignment slack*/ + (size_t)(1 + TC_NB) * tc_tile_bytes(kc) + (size_t)TC_NACC * 2 * TC_BN * sizeof(float) +
+         (size_t)2 * TC_BM * sizeof(float) /*warpgroup merge*/;
 }
 
 __device__ __forceinline__ float to_tf32(float x) {
@@ -120,6 +125,17 @@ constexpr uint32_t TC_IDESC = (1u << 4) /*D = f32*/ | (2u << 7) /*A = tf32*/ | (
         "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])                      \
       : "r"(taddr)                                                                                                     \
       : "memory")
+// wait for the outstanding tcgen05.ld of this thread; the registers are threaded through as in/out operands so that
+// the compiler cannot schedule a use of them above the wait
+#define B2OT_TMEM_WAIT32(v)                                                                                            \
+  asm volatile("tcgen05.wait::ld.sync.aligned;"                                                                        \
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),       \
+                 "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]), \
+                 "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]),            \
+                 "+r"(v[23]), "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]),            \
+                 "+r"(v[30]), "+r"(v[31])                                                                              \
+               :                                                                                                       \
+               : "memory")
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
@@ -254,73 +270,118 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
       }
     }
   } else {
-    // ===== epilogue: one thread = one row of the tile =====
-    const int q = warp & 3;                  // TMEM lane quarter this warp may access
-    const int et = tid - 64;                 // 0..127 among the epilogue threads
-    const long long row = row_tile * TC_BM + q * 32 + lane;
+    // ===== epilogue: two warpgroups take alternate column tiles; one thread = one row of a tile =====
+    const int ew = warp - 2;               // 0..7
+    const int wg = ew >> 2;                // warpgroup 0 / 1
+    const int q = warp & 3;                // TMEM lane quarter this warp may access
+    const int et = (ew & 3) * 32 + lane;   // column of the tile this thread stages into shared memory
+    const int rloc = q * 32 + lane;        // row of the tile this thread owns
+    const long long row = row_tile * TC_BM + rloc;
     const float xi = (row < p.nx) ? p.xx[row] : 0.f;
     const float* potg = p.poty;
     if (p.pot_sel != nullptr) potg += (long long)(*p.pot_sel) * p.pot_stride;
     const float LOG2E = 1.4426950408889634f;
-    const float nk2 = -p.k2;
+    const float k2 = p.k2, k22 = 2.f * p.k2;
+    const float nxk = -k2 * xi;
     float m_run = -CUDART_INF_F, s_run = 0.f;
-    for (long long t = 0; t < ntiles; ++t) {
+    // column vectors of a tile are fetched one tile ahead into registers (global-load latency hidden behind a
+    // whole tile of work) and staged into shared memory as  G_j = pot_j log2e  and  B_j = G_j - k2 |y_j|^2
+    float pg = -CUDART_INF_F, py = 0.f;
+    auto fetch = [&](long long t) {
+      const long long j = (ct0 + t) * TC_BN + et;
+      const bool ok = (t < ntiles) && (j < p.ny);
+      pg = ok ? potg[j] * LOG2E : -CUDART_INF_F;
+      py = ok ? p.yy[j] : 0.f;
+    };
+    fetch(wg);
+    for (long long t = wg; t < ntiles; t += 2) {
       const int as = (int)(t % TC_NACC);
       const uint32_t aph = (uint32_t)((t / TC_NACC) & 1);
-      float* cg = colvec + (size_t)as * 2 * TC_BN;
-      float* cy = cg + TC_BN;
-      {
-        const long long j = (ct0 + t) * TC_BN + et;
-        const bool ok = j < p.ny;
-        cg[et] = ok ? potg[j] * LOG2E : -CUDART_INF_F;
-        cy[et] = ok ? p.yy[j] : 0.f;
-      }
-      named_bar_sync(1, 128);
+      float* cB = colvec + (size_t)as * 2 * TC_BN;
+      float* cG = cB + TC_BN;
+      cG[et] = pg;
+      cB[et] = fmaf(-k2, py, pg);
+      fetch(t + 2);
+      named_bar_sync(1 + wg, 128);
       mbar_wait_guard(&acc_full[as], aph);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * TC_BN);
-#pragma unroll 1
-      for (int ch = 0; ch < TC_BN / 32; ++ch) {
-        uint32_t v[32];
-        B2OT_TMEM_LD32(taddr + (uint32_t)(ch * 32), v);
-        tmem_ld_wait();
+      // one 32-column chunk: (pot_j - C_ij / reg) log2e = min(2 k2 x.y + B_j - k2 |x|^2, G_j)  [clamp C >= 0,
+      // ot/utils.py:299], then the online (max, sum 2^x) update; packed fp32x2 arithmetic throughout
+      auto chunk = [&](const uint32_t (&v)[32], int ch) {
         float tv[32];
-        float cmax = -CUDART_INF_F;
+        float c0 = -CUDART_INF_F, c1 = -CUDART_INF_F;
 #pragma unroll
         for (int g4 = 0; g4 < 8; ++g4) {
-          const float4 gq = *reinterpret_cast<const float4*>(cg + ch * 32 + g4 * 4);
-          const float4 yq = *reinterpret_cast<const float4*>(cy + ch * 32 + g4 * 4);
-          const float gg[4] = {gq.x, gq.y, gq.z, gq.w};
-          const float yv[4] = {yq.x, yq.y, yq.z, yq.w};
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const float dot = __uint_as_float(v[g4 * 4 + e]);
-            const float c = fmaxf(fmaf(-2.f, dot, xi + yv[e]), 0.f);  // clamp: ot/utils.py:299
-            const float tt = fmaf(nk2, c, gg[e]);                      // (pot_j - C_ij / reg) * log2(e)
-            tv[g4 * 4 + e] = tt;
-            cmax = fmaxf(cmax, tt);
-          }
+          const float4 bq = *reinterpret_cast<const float4*>(cB + ch * 32 + g4 * 4);
+          const float4 gq = *reinterpret_cast<const float4*>(cG + ch * 32 + g4 * 4);
+          float z0 = bq.x, z1 = bq.y, z2 = bq.z, z3 = bq.w;
+          add2(z0, z1, nxk, nxk);
+          add2(z2, z3, nxk, nxk);
+          float r0, r1, r2, r3;
+          fma2(r0, r1, __uint_as_float(v[g4 * 4 + 0]), __uint_as_float(v[g4 * 4 + 1]), k22, k22, z0, z1);
+          fma2(r2, r3, __uint_as_float(v[g4 * 4 + 2]), __uint_as_float(v[g4 * 4 + 3]), k22, k22, z2, z3);
+          r0 = fminf(r0, gq.x);
+          r1 = fminf(r1, gq.y);
+          r2 = fminf(r2, gq.z);
+          r3 = fminf(r3, gq.w);
+          tv[g4 * 4 + 0] = r0;
+          tv[g4 * 4 + 1] = r1;
+          tv[g4 * 4 + 2] = r2;
+          tv[g4 * 4 + 3] = r3;
+          c0 = max3(c0, r0, r1);
+          c1 = max3(c1, r2, r3);
         }
-        const float m_new = fmaxf(m_run, cmax);
+        const float m_new = max3(m_run, c0, c1);
         const float mref = (m_new == -CUDART_INF_F) ? 0.f : m_new;
-        float s0 = s_run * ex2_approx(m_run - mref), s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        const float nm = -mref;
+        float s0 = s_run * ex2_ftz(m_run - mref), s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
         for (int e = 0; e < 32; e += 4) {
-          s0 += ex2_approx(tv[e] - mref);
-          s1 += ex2_approx(tv[e + 1] - mref);
-          s2 += ex2_approx(tv[e + 2] - mref);
-          s3 += ex2_approx(tv[e + 3] - mref);
+          float a0 = tv[e], a1 = tv[e + 1], a2 = tv[e + 2], a3 = tv[e + 3];
+          add2(a0, a1, nm, nm);
+          add2(a2, a3, nm, nm);
+          a0 = ex2_ftz(a0);
+          a1 = ex2_ftz(a1);
+          a2 = ex2_ftz(a2);
+          a3 = ex2_ftz(a3);
+          add2(s0, s1, a0, a1);
+          add2(s2, s3, a2, a3);
         }
         s_run = (s0 + s1) + (s2 + s3);
         m_run = m_new;
-      }
+      };
+      uint32_t v0[32], v1[32];
+      B2OT_TMEM_LD32(taddr, v0);
+      B2OT_TMEM_WAIT32(v0);
+      B2OT_TMEM_LD32(taddr + 32u, v1);
+      chunk(v0, 0);
+      B2OT_TMEM_WAIT32(v1);
+      B2OT_TMEM_LD32(taddr + 64u, v0);
+      chunk(v1, 1);
+      B2OT_TMEM_WAIT32(v0);
+      B2OT_TMEM_LD32(taddr + 96u, v1);
+      chunk(v0, 2);
+      B2OT_TMEM_WAIT32(v1);
       tc_fence_before();
-      mbar_arrive(&acc_empty[as]);
+      mbar_arrive(&acc_empty[as]);  // accumulator stage drained: the MMA warp may overwrite it
+      chunk(v1, 3);
     }
-    if (row < p.nx) {
+    // merge the two warpgroups' running (max, sum) of each row
+    float* mrg = colvec + (size_t)TC_NACC * 2 * TC_BN;
+    if (wg == 1) {
+      mrg[rloc] = m_run;
+      mrg[TC_BM + rloc] = s_run;
+    }
+    named_bar_sync(3, 32 * TC_EPI_WARPS);
+    if (wg == 0 && row < p.nx) {
+      const float m2 = mrg[rloc], s2 = mrg[TC_BM + rloc];
+      const float M = fmaxf(m_run, m2);
+      const float mref = (M == -CUDART_INF_F) ? 0.f : M;
+      const float s = s_run * ex2_ftz(m_run - mref) + s2 * ex2_ftz(m2 - mref);
       const float LN2 = 0.6931471805599453f;
-      p.pmax[(long long)blockIdx.y * p.nx + row] = m_run * LN2;   // back to natural-log units
-      p.psum[(long long)blockIdx.y * p.nx + row] = s_run;
+      p.pmax[(long long)blockIdx.y * p.nx + row] = M * LN2;   // back to natural-log units
+      p.psum[(long long)blockIdx.y * p.nx + row] = s;
     }
   }
 

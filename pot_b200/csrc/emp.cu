@@ -26,6 +26,8 @@ struct b2ot_emp {
   void *fring, *g, *xx, *yy, *cbuf, *pmaxA, *psumA, *pmaxB, *psumB;
   int nsplitA, nsplitB, fin_blocks_f, fin_blocks_g;
   int use_tc, kc;          // tensor-core sweep: packed (split + pre-swizzled) clouds
+  int tc_kind;             // 0 = 3xTF32, 1 = 3xFP16 (scaled split)
+  float* tc_scales;        // 3xFP16: [s_x, s_y, 1 / (s_x s_y)] followed by the two abs-max words (device)
   void *packs, *packt;
   b2ot_allreduce_fn ar;
   void* ar_ctx;
@@ -62,21 +64,21 @@ bool resolve_tc(int dtype, int d, int metric, int variant, long long n, long lon
   return eligible && std::max(n, m) >= 256;
 }
 int pick_nsplit_tc(long long rows, long long cols) {
-  // CTAs = row tiles x splits of the reduced axis, one CTA per SM at a time: take the split whose last wave is
-  // fullest (ties: fewer splits), keeping at least 8 column tiles per CTA so the row operand load stays amortised
+  // CTAs = row tiles x splits of the reduced axis, one CTA per SM at a time: minimise waves x (tiles per CTA + fill /
+  // drain), keeping at least 8 column tiles per CTA so the row operand load stays amortised
   const long long row_tiles = (rows + TC_BM - 1) / TC_BM;
   const long long col_tiles = (cols + TC_BN - 1) / TC_BN;
   const long long sms = sm_count();
   const long long ns_max = std::max<long long>(1, std::min<long long>(64, col_tiles / 8));
   long long best = 1;
-  double best_eff = -1.0;
+  double best_cost = 1e300;
   for (long long ns = 1; ns <= ns_max; ++ns) {
     const long long per = (col_tiles + ns - 1) / ns;          // column tiles per CTA (the longest one)
     const long long ctas = row_tiles * ns;
     const long long waves = (ctas + sms - 1) / sms;
-    const double eff = (double)(row_tiles * col_tiles) / (double)(waves * sms * per);
-    if (eff > best_eff + 1e-3) {
-      best_eff = eff;
+    const double cost = (double)waves * (double)(per + 2);    // + ~2 tile times of pipeline fill / drain per CTA
+    if (cost < best_cost * 0.999) {
+      best_cost = cost;
       best = ns;
     }
   }
@@ -151,12 +153,36 @@ int launch_tc_pass(const b2ot_emp* h, bool passA) {
     p.pmax = (float*)h->pmaxB;  p.psum = (float*)h->psumB;  p.nsplit = h->nsplitB;
   }
   p.kc = h->kc;
+  p.kind = h->tc_kind;
+  p.dotscale = h->tc_kind ? h->tc_scales + 2 : nullptr;
   p.k2 = (float)(1.4426950408889634 / h->reg);
   p.status = &h->st->status;
   p.expect_status = ST_RUNNING;
-  dim3 grid((unsigned)((p.nx + TC_BM - 1) / TC_BM), (unsigned)p.nsplit);
-  emp_tc_lse_kernel<<<grid, TC_THREADS, tc_smem_bytes(2), h->stream>>>(p);
-  B2OT_CHECK_LAUNCH();
+  if (const char* e = getenv("B2OT_EMP_DBG")) p.dbg = atoi(e);
+  if (const char* e = getenv("B2OT_EMP_TRACE")) p.trace = (long long*)strtoull(e, nullptr, 0);  // device address
+
+  // cluster along the row tiles (multicast of the column operand); B2OT_EMP_CLUSTER = 1, 2 or 4
+  int cs = 1;
+  if (const char* e = getenv("B2OT_EMP_CLUSTER")) {
+    const int v = atoi(e);
+    if (v == 1 || v == 2 || v == 4) cs = v;
+  }
+  const long long row_tiles = (p.nx + TC_BM - 1) / TC_BM;
+  if (row_tiles < cs) cs = 1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)((row_tiles + cs - 1) / cs * cs), (unsigned)p.nsplit);
+  cfg.blockDim = dim3(TC_THREADS);
+  cfg.dynamicSmemBytes = tc_smem_bytes(2);
+  cfg.stream = h->stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)cs;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B2OT_CUDA(cudaLaunchKernelEx(&cfg, emp_tc_lse_kernel, p));
+  count_launch();
   return 0;
 }
 
@@ -352,7 +378,10 @@ extern "C" int b2ot_emp_create(b2ot_emp** handle, int dtype, int64_t n, int64_t 
   h->pmaxB = ws + L.off_pb;
   h->psumB = ws + L.off_pb + (size_t)L.nsB * m * sz;
   h->use_tc = L.use_tc;
-  h->kc = L.kc;
+  h->tc_kind = 1;
+  if (const char* e = getenv("B2OT_EMP_KIND")) h->tc_kind = (strcmp(e, "tf32") == 0) ? 0 : 1;
+  h->kc = h->tc_kind ? (d + 63) / 64 : L.kc;   // the workspace is sized for the (larger) TF32 packing
+  h->tc_scales = (float*)((char*)(ws + L.off_xchg) + 64);
   h->packs = ws + L.off_packs;
   h->packt = ws + L.off_packt;
   if (h->use_tc) {
@@ -410,11 +439,31 @@ extern "C" int b2ot_emp_init(b2ot_emp* h, const void* f0, const void* g0) {
     // tensor-core sweep: split (hi, lo) + pre-swizzle both clouds once per solve
     const long long us = (h->n + TC_BM - 1) / TC_BM * TC_BM * h->kc * 8;
     const long long ut = (h->m + TC_BM - 1) / TC_BM * TC_BM * h->kc * 8;
-    emp_tc_pack_kernel<<<(unsigned)((us + 255) / 256), 256, 0, h->stream>>>((const float*)h->Xs, h->n, h->d, h->ldxs,
-                                                                           h->kc, (float*)h->packs);
+    if (h->tc_kind == 0) {
+      emp_tc_pack_kernel<<<(unsigned)((us + 255) / 256), 256, 0, h->stream>>>((const float*)h->Xs, h->n, h->d, h->ldxs,
+                                                                             h->kc, (float*)h->packs);
+      B2OT_CHECK_LAUNCH();
+      emp_tc_pack_kernel<<<(unsigned)((ut + 255) / 256), 256, 0, h->stream>>>((const float*)h->Xt, h->m, h->d, h->ldxt,
+                                                                             h->kc, (float*)h->packt);
+      B2OT_CHECK_LAUNCH();
+      return 0;
+    }
+    // 3xFP16: one power-of-two scale per cloud from its largest |coordinate|, then the scaled split
+    unsigned int* maxbits = (unsigned int*)(h->tc_scales + 4);
+    B2OT_CUDA(cudaMemsetAsync(maxbits, 0, 2 * sizeof(unsigned int), h->stream));
+    const unsigned gs = (unsigned)std::min<long long>((h->n * h->d + 255) / 256, 1184);
+    const unsigned gt = (unsigned)std::min<long long>((h->m * h->d + 255) / 256, 1184);
+    emp_absmax_kernel<<<gs, 256, 0, h->stream>>>((const float*)h->Xs, h->n, h->d, h->ldxs, maxbits);
     B2OT_CHECK_LAUNCH();
-    emp_tc_pack_kernel<<<(unsigned)((ut + 255) / 256), 256, 0, h->stream>>>((const float*)h->Xt, h->m, h->d, h->ldxt,
-                                                                           h->kc, (float*)h->packt);
+    emp_absmax_kernel<<<gt, 256, 0, h->stream>>>((const float*)h->Xt, h->m, h->d, h->ldxt, maxbits + 1);
+    B2OT_CHECK_LAUNCH();
+    emp_tc_scale_kernel<<<1, 32, 0, h->stream>>>(maxbits, h->tc_scales);
+    B2OT_CHECK_LAUNCH();
+    emp_tc_pack_f16_kernel<<<(unsigned)((us + 255) / 256), 256, 0, h->stream>>>(
+        (const float*)h->Xs, h->n, h->d, h->ldxs, h->kc, h->tc_scales, (unsigned char*)h->packs);
+    B2OT_CHECK_LAUNCH();
+    emp_tc_pack_f16_kernel<<<(unsigned)((ut + 255) / 256), 256, 0, h->stream>>>(
+        (const float*)h->Xt, h->m, h->d, h->ldxt, h->kc, h->tc_scales + 1, (unsigned char*)h->packt);
     B2OT_CHECK_LAUNCH();
     return 0;
   }

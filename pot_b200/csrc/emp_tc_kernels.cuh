@@ -9,7 +9,8 @@
 //     (dropped term lo.lo ~ 2^-22).  The split operands are stored PRE-SWIZZLED in the canonical K-major
 //     SWIZZLE_128B shared-memory layout, tile by tile, so that a plain 1-D TMA bulk copy (cp.async.bulk) lands
 //     a tile in shared memory exactly as the UMMA descriptors expect it - no tensor maps needed.
-//   * warp roles: warp 0 = producer (bulk copies: the row tile once, column tiles through a 2-stage ring),
+//   * warp roles: warp 0 = producer (bulk copies: the row tile once, the column operand through a 4-stage ring of
+//     32 KB K chunks, so loads run 3 chunks = 1.5 tiles ahead of the MMAs),
 //     warp 1 = MMA issuer (one elected lane; 12 or 24 MMAs of 128x128x8 per tile; tcgen05.commit releases the
 //     smem stage and publishes the accumulator), warps 2-9 = epilogue: two warpgroups take alternate column tiles
 //     (two warps per SM sub-partition, so one warp's MUFU phase overlaps the other's FMA phase); one thread owns
@@ -21,6 +22,8 @@
 // Bound: tensor pipe (3 x 2 n m d flop) with MUFU (n m ex2) and the FMA pipe (~7 instr / element) co-limiting.
 #pragma once
 
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace b2ot {
@@ -29,10 +32,12 @@ constexpr int TC_BM = 128;        // rows of an output tile (TMEM lanes)
 constexpr int TC_BN = 128;        // columns of an output tile
 constexpr int TC_KCH = 32;        // K elements per swizzle chunk (32 x 4 B = 128 B rows)
 constexpr int TC_SUB = 16384;     // bytes of one (chunk, hi|lo) sub-tile: 128 rows x 128 B
-constexpr int TC_NB = 2;          // shared-memory stages of the column operand
+constexpr int TC_NB = 4;          // shared-memory stages of the column operand, one K chunk (hi + lo) each
+constexpr int TC_STAGE = 2 * TC_SUB;  // bytes of a stage
 constexpr int TC_NACC = 4;        // accumulator stages in tensor memory
 constexpr int TC_EPI_WARPS = 8;    // two epilogue warpgroups, alternating column tiles
-constexpr int TC_THREADS = 64 + 32 * TC_EPI_WARPS;  // producer warp, MMA warp, epilogue warps
+constexpr int TC_MMA2_WARP = 2 + TC_EPI_WARPS;      // second MMA-issuing warp (odd tiles)
+constexpr int TC_THREADS = 96 + 32 * TC_EPI_WARPS;  // producer warp, MMA warp, epilogue warps, second MMA warp
 constexpr int TC_MAX_D = 64;
 
 __host__ __device__ inline size_t tc_tile_bytes(int kc) { return (size_t)kc * 2 * TC_SUB; }
@@ -40,7 +45,7 @@ __host__ __device__ inline size_t tc_pack_bytes(long long rows, int kc) {
   return (size_t)((rows + TC_BM - 1) / TC_BM) * tc_tile_bytes(kc);
 }
 inline size_t tc_smem_bytes(int kc) {
-  return 1024 /*alignment slack*/ + (size_t)(1 + TC_NB) * tc_tile_bytes(kc) + (size_t)TC_NACC * 2 * TC_BN * sizeof(float) +
+  return 1024 /*alignment slack*/ + tc_tile_bytes(kc) + (size_t)TC_NB * TC_STAGE + (size_t)TC_NACC * 2 * TC_BN * sizeof(float) +
          (size_t)2 * TC_BM * sizeof(float) /*warpgroup merge*/;
 }
 
@@ -84,6 +89,66 @@ __global__ void __launch_bounds__(256) emp_tc_pack_kernel(const float* __restric
   *reinterpret_cast<float4*>(base + TC_SUB) = lo;
 }
 
+// ---- 3xFP16 operands (kind::f16): same split idea on half the bytes ----
+// x * s = hi + lo with hi = fp16(x s), lo = fp16(x s - hi): 11 + 11 significant bits, the same as the TF32 split.
+// s is ONE power of two per cloud chosen so that max |x s| lies in [2^13, 2^14): the small halves then stay normal
+// fp16 numbers unless |x| < 2^-15 max|x| (absolute error 2^-39 of the largest coordinate).  A 128-byte swizzle row
+// holds 64 fp16, so a K chunk covers 64 coordinates and one 128x128x16 MMA does twice the work of a 128x128x8 TF32
+// one for the same 8 KB of shared-memory operand traffic -- which is what bounds this kernel (UMMA operand reads +
+// TMA fills share the 128 B/clk of shared-memory bandwidth).
+__global__ void __launch_bounds__(256) emp_absmax_kernel(const float* __restrict__ X, long long n, int d, long long ld,
+                                                         unsigned int* __restrict__ out_bits) {
+  float mx = 0.f;
+  const long long total = n * d;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const float v = fabsf(X[(i / d) * ld + (i % d)]);
+    if (v < CUDART_INF_F) mx = fmaxf(mx, v);  // nan / inf coordinates poison the result anyway
+  }
+  mx = warp_max(mx);
+  if ((threadIdx.x & 31) == 0) atomicMax(out_bits, __float_as_uint(mx));
+}
+// scales[0] = s_x, scales[1] = s_y, scales[2] = 1 / (s_x s_y)   (all powers of two)
+__global__ void emp_tc_scale_kernel(const unsigned int* __restrict__ maxbits, float* __restrict__ scales) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  float s[2];
+  for (int i = 0; i < 2; ++i) {
+    const float mx = __uint_as_float(maxbits[i]);
+    int e = 0;
+    if (mx > 0.f) frexpf(mx, &e);  // mx = f 2^e, f in [0.5, 1)
+    s[i] = (mx > 0.f) ? ldexpf(1.f, 14 - e) : 1.f;
+  }
+  scales[0] = s[0];
+  scales[1] = s[1];
+  scales[2] = 1.f / (s[0] * s[1]);
+}
+// packed[tile][chunk c of 64 coordinates][hi|lo][group g of 8 rows][row r][16-byte unit (j ^ r)][8 halves]
+__global__ void __launch_bounds__(256) emp_tc_pack_f16_kernel(const float* __restrict__ X, long long n, int d, long long ld,
+                                                              int kc, const float* __restrict__ scale,
+                                                              unsigned char* __restrict__ packed) {
+  const long long rows_pad = (n + TC_BM - 1) / TC_BM * TC_BM;
+  const int units = kc * 8;
+  const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= rows_pad * units) return;
+  const long long row = idx / units;
+  const int u = (int)(idx % units);
+  const int c = u >> 3, j = u & 7;
+  const float sc = *scale;
+  __half hi[8], lo[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const int k = c * 64 + j * 8 + e;
+    const float v = (row < n && k < d) ? X[row * ld + k] * sc : 0.f;
+    hi[e] = __float2half_rn(v);
+    lo[e] = __float2half_rn(v - __half2float(hi[e]));
+  }
+  const long long tile = row / TC_BM;
+  const int rt = (int)(row % TC_BM);
+  const int g = rt >> 3, r = rt & 7;
+  unsigned char* base = packed + tile * tc_tile_bytes(kc) + (size_t)(c * 2) * TC_SUB + g * 1024 + r * 128 + ((j ^ r) << 4);
+  *reinterpret_cast<uint4*>(base) = *reinterpret_cast<const uint4*>(hi);
+  *reinterpret_cast<uint4*>(base + TC_SUB) = *reinterpret_cast<const uint4*>(lo);
+}
+
 // ---- tcgen05 PTX wrappers ----
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_holder, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_holder)), "r"(ncols)
@@ -93,24 +158,73 @@ __device__ __forceinline__ void tmem_alloc(uint32_t* smem_holder, uint32_t ncols
 __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
   asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
 }
+// one lane of the (converged) warp; the compiler recognises the elected lane and emits the uniform-datapath
+// tcgen05 instructions inside `if (elect_one())` once, instead of a per-active-thread election loop
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xFFFFFFFF;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
   asm volatile(
-      "{\n\t.reg .pred p;\n\t"
+      "{\n\t.reg .pred p, q;\n\t"
       "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      "elect.sync _|q, 0xFFFFFFFF;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "elect.sync _|q, 0xFFFFFFFF;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// NOTE: the tcgen05.mma / tcgen05.commit wrappers are WARP-level calls: every lane of the converged MMA warp executes
+// them with identical (warp-uniform) operands and one lane is elected inside the asm block.  ptxas then keeps the
+// descriptors in uniform registers and emits back-to-back UTCHMMA; issuing from `if (lane == 0)` instead costs an
+// election loop + R2UR moves per MMA (~85 clk per MMA measured, more than the 64 clk the MMA itself takes).
 // arrive on an mbarrier when all MMAs issued so far by this thread have completed
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "elect.sync _|q, 0xFFFFFFFF;\n\t"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar))
+      : "memory");
+}
+// same, signalling the barrier at this offset in every CTA of the cluster named by `mask`
+__device__ __forceinline__ void umma_commit_mc(uint64_t* bar, uint16_t mask) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "elect.sync _|q, 0xFFFFFFFF;\n\t"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}" ::"r"(
+          smem_u32(bar)),
+      "h"(mask)
+      : "memory");
+}
+// bulk copy global -> the same shared-memory offset of every CTA in `mask`; each destination CTA's mbarrier (same
+// offset) receives the byte count
+__device__ __forceinline__ void bulk_g2s_mc(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar, uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;" ::
+          "r"(smem_u32(smem_dst)),
+      "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "h"(mask)
+      : "memory");
 }
 // K-major, SWIZZLE_128B operand descriptor: 8-row groups 1024 B apart
 __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
   return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
 }
+constexpr uint32_t TC_IDESC_F16 = (1u << 4) /*D = f32, A = B = f16*/ | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
 constexpr uint32_t TC_IDESC = (1u << 4) /*D = f32*/ | (2u << 7) /*A = tf32*/ | (2u << 10) /*B = tf32*/ |
                               ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
 
@@ -157,6 +271,12 @@ __device__ __forceinline__ void mbar_wait_guard(uint64_t* bar, uint32_t parity) 
   }
 }
 
+#define B2OT_TRACE(slot, t)                                                                     \
+  do {                                                                                          \
+    if (p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && (t) < 256)                  \
+      p.trace[(t) * 8 + (slot)] = clock64();                                                    \
+  } while (0)
+
 struct EmpTcParams {
   const float* Apack;   // row operand, packed tiles
   const float* Bpack;   // column operand, packed tiles
@@ -173,6 +293,10 @@ struct EmpTcParams {
   float k2;             // log2(e) / reg
   const int* status;
   int expect_status;
+  int kind;             // 0: 3xTF32 (kind::tf32, 32 coordinates per K chunk), 1: 3xFP16 (kind::f16, 64 per chunk)
+  const float* dotscale; // 3xFP16: accumulator -> x.y factor 1 / (s_x s_y), device scalar; null = 1
+  long long* trace;     // experiment: clock64 stamps of CTA (0,0): [tile][8] (null = off)
+  int dbg;              // experiment switches (B2OT_EMP_DBG): 1 no MUFU, 2 no epilogue arithmetic, 4 no MMAs
 };
 
 __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcParams p) {
@@ -187,10 +311,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const size_t TB = tc_tile_bytes(p.kc);
   // 1024-byte aligned operand area (SWIZZLE_128B atoms repeat every 1024 B)
-  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(tc_smem_raw) + 1023) & ~(uintptr_t)1023);
+  // (offset arithmetic on the shared array itself, so the compiler keeps the shared address space: LDS, not LD)
+  unsigned char* smem = tc_smem_raw + ((1024u - (smem_u32(tc_smem_raw) & 1023u)) & 1023u);
   unsigned char* As = smem;
   unsigned char* Bs = smem + TB;
-  float* colvec = reinterpret_cast<float*>(smem + (1 + TC_NB) * TB);  // [NACC][2][TC_BN]: pot * log2e, |y|^2
+  float* colvec = reinterpret_cast<float*>(smem + TB + (size_t)TC_NB * TC_STAGE);  // [NACC][2][TC_BN]: pot * log2e, |y|^2
 
   // column tiles of this block
   const long long ctiles = (p.ny + TC_BN - 1) / TC_BN;
@@ -199,12 +324,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
   const long long ct1 = (ct0 + per < ctiles) ? ct0 + per : ctiles;
   const long long ntiles = ct1 > ct0 ? ct1 - ct0 : 0;
   const long long row_tile = blockIdx.x;
+  // cluster of CS CTAs along the row tiles: same column tiles, so each CTA fetches 1/CS of every column tile and
+  // multicasts it to all (L2 -> SM traffic of the column operand / CS)
+  const uint32_t cs = cluster_nctarank(), crank = cluster_ctarank();
+  const uint16_t cmask = (uint16_t)((1u << cs) - 1u);
+  const long long row_tiles = (p.nx + TC_BM - 1) / TC_BM;
+  const long long row_tile_ld = row_tile < row_tiles ? row_tile : row_tiles - 1;  // padding CTA of the last cluster
 
   if (tid == 0) {
     mbar_init(&a_full, 1);
     for (int s = 0; s < TC_NB; ++s) {
       mbar_init(&b_full[s], 1);
-      mbar_init(&b_empty[s], 1);
+      mbar_init(&b_empty[s], cs);
     }
     for (int s = 0; s < TC_NACC; ++s) {
       mbar_init(&acc_full[s], 1);
@@ -214,59 +345,105 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
   }
   if (warp == 1) tmem_alloc(&tmem_holder, 512);
   tc_fence_before();
-  __syncthreads();
+  if (cs > 1)
+    cluster_sync_all();  // every CTA's barriers exist before a peer's multicast copy or commit can reach them
+  else
+    __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_holder;
 
   if (warp == 0) {
-    // ===== producer: bulk copies of pre-swizzled tiles =====
+    // ===== producer: bulk copies of pre-swizzled operands; the column operand moves through the ring one
+    // K chunk (hi + lo sub-tiles, 32 KB) at a time =====
     if (lane == 0 && ntiles > 0) {
-      const unsigned char* Ag = reinterpret_cast<const unsigned char*>(p.Apack) + (size_t)row_tile * TB;
+      const unsigned char* Ag = reinterpret_cast<const unsigned char*>(p.Apack) + (size_t)row_tile_ld * TB;
       mbar_arrive_expect_tx(&a_full, (uint32_t)TB);
       for (size_t o = 0; o < TB; o += TC_SUB) bulk_g2s(As + o, Ag + o, TC_SUB, &a_full);
+      long long qn = 0;  // chunk counter
       for (long long t = 0; t < ntiles; ++t) {
-        const int s = (int)(t % TC_NB);
-        const uint32_t ph = (uint32_t)((t / TC_NB) & 1);
-        mbar_wait_guard(&b_empty[s], ph ^ 1u);
         const unsigned char* Bg = reinterpret_cast<const unsigned char*>(p.Bpack) + (size_t)(ct0 + t) * TB;
-        mbar_arrive_expect_tx(&b_full[s], (uint32_t)TB);
-        for (size_t o = 0; o < TB; o += TC_SUB) bulk_g2s(Bs + (size_t)s * TB + o, Bg + o, TC_SUB, &b_full[s]);
+        for (int c = 0; c < p.kc; ++c, ++qn) {
+          const int s = (int)(qn % TC_NB);
+          const uint32_t ph = (uint32_t)((qn / TC_NB) & 1);
+          mbar_wait_guard(&b_empty[s], ph ^ 1u);
+          B2OT_TRACE(0, t);
+          if ((p.dbg & 8) && qn >= TC_NB) {  // experiment: no refills (stale operands), handshake only
+            mbar_arrive(&b_full[s]);
+            continue;
+          }
+          mbar_arrive_expect_tx(&b_full[s], (uint32_t)TC_STAGE);
+          unsigned char* dst = Bs + (size_t)s * TC_STAGE;
+          const unsigned char* src = Bg + (size_t)c * TC_STAGE;
+          if (cs == 1) {
+            bulk_g2s(dst, src, TC_SUB, &b_full[s]);
+            bulk_g2s(dst + TC_SUB, src + TC_SUB, TC_SUB, &b_full[s]);
+          } else {
+            const size_t piece = (size_t)TC_STAGE / cs, base = (size_t)crank * piece;
+            for (size_t o = 0; o < piece; o += TC_SUB) {
+              const size_t len = (piece - o < (size_t)TC_SUB) ? piece - o : (size_t)TC_SUB;
+              bulk_g2s_mc(dst + base + o, src + base + o, (uint32_t)len, &b_full[s], cmask);
+            }
+          }
+        }
       }
     }
-  } else if (warp == 1) {
-    // ===== MMA issuer =====
+  } else if (warp == 1 || warp == TC_MMA2_WARP) {
+    // ===== MMA issuers: two warps take alternate column tiles.  A tcgen05.mma issue blocks while the tensor pipe's
+    // queue is full, so one warp's barrier waits for its next tile overlap the other warp's issue stream =====
+    const int mw = (warp == 1) ? 0 : 1;
     if (ntiles > 0) {
       mbar_wait_guard(&a_full, 0);
       const uint32_t a_addr = smem_u32(As);
-      for (long long t = 0; t < ntiles; ++t) {
-        const int s = (int)(t % TC_NB);
-        const uint32_t bph = (uint32_t)((t / TC_NB) & 1);
+      // The CTA owns all 512 TMEM columns, so the allocation starts at column 0 / lane 0: using the literal 0 keeps
+      // the accumulator address in a uniform register (an address loaded from shared memory would force a
+      // per-thread register + election loop around every MMA).
+      if (tmem_base != 0u) __trap();
+      const uint32_t tmem_u = 0u;
+      for (long long t = mw; t < ntiles; t += 2) {
+        long long qn = t * p.kc;  // chunk counter of this tile's first K chunk
         const int as = (int)(t % TC_NACC);
         const uint32_t aph = (uint32_t)((t / TC_NACC) & 1);
         mbar_wait_guard(&acc_empty[as], aph ^ 1u);
-        mbar_wait_guard(&b_full[s], bph);
-        tc_fence_after();
-        if (lane == 0) {
-          const uint32_t b_addr = smem_u32(Bs + (size_t)s * TB);
-          const uint32_t d_tmem = tmem_base + (uint32_t)(as * TC_BN);
-          uint32_t acc = 0;
-          for (int c = 0; c < p.kc; ++c) {
+        if (lane == 0) B2OT_TRACE(1, t);
+        const uint32_t d_tmem = tmem_u + (uint32_t)(as * TC_BN);
+        uint32_t acc = 0;
+        for (int c = 0; c < p.kc; ++c, ++qn) {
+          const int s = (int)(qn % TC_NB);
+          const uint32_t bph = (uint32_t)((qn / TC_NB) & 1);
+          mbar_wait_guard(&b_full[s], bph);
+          tc_fence_after();
+          if (lane == 0) B2OT_TRACE(2, t);
+          __syncwarp();  // converged warp: the uniform-datapath instructions below are emitted without election loops
+          {
+            const uint32_t b_addr = smem_u32(Bs + (size_t)s * TC_STAGE);
+            const uint32_t a_chunk = a_addr + (uint32_t)(c * TC_STAGE);
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks) {
-              const uint32_t off_hi = (uint32_t)((c * 2) * TC_SUB + ks * 32);
+              const uint32_t off_hi = (uint32_t)(ks * 32);
               const uint32_t off_lo = off_hi + TC_SUB;
-              const uint64_t ah = umma_desc_sw128(a_addr + off_hi), al = umma_desc_sw128(a_addr + off_lo);
+              const uint64_t ah = umma_desc_sw128(a_chunk + off_hi), al = umma_desc_sw128(a_chunk + off_lo);
               const uint64_t bh = umma_desc_sw128(b_addr + off_hi), bl = umma_desc_sw128(b_addr + off_lo);
-              umma_tf32(d_tmem, al, bh, TC_IDESC, acc);  // small terms first
-              umma_tf32(d_tmem, ah, bl, TC_IDESC, 1u);
-              umma_tf32(d_tmem, ah, bh, TC_IDESC, 1u);
+              if (p.dbg & 4) continue;
+              if (p.kind == 0) {
+                umma_tf32(d_tmem, al, bh, TC_IDESC, acc);  // small terms first
+                umma_tf32(d_tmem, ah, bl, TC_IDESC, 1u);
+                umma_tf32(d_tmem, ah, bh, TC_IDESC, 1u);
+              } else {
+                umma_f16(d_tmem, al, bh, TC_IDESC_F16, acc);
+                umma_f16(d_tmem, ah, bl, TC_IDESC_F16, 1u);
+                umma_f16(d_tmem, ah, bh, TC_IDESC_F16, 1u);
+              }
               acc = 1u;
             }
+            if (cs == 1)
+              umma_commit(&b_empty[s]);     // smem stage free once these MMAs have read it
+            else
+              umma_commit_mc(&b_empty[s], cmask);  // ... in every CTA of the cluster (they all write into it)
+            if (c == p.kc - 1) umma_commit(&acc_full[as]);   // accumulator complete
+            if (lane == 0) B2OT_TRACE(3, t);
           }
-          umma_commit(&b_empty[s]);     // smem stage free once these MMAs have read it
-          umma_commit(&acc_full[as]);   // accumulator complete
+          __syncwarp();
         }
-        __syncwarp();
       }
     }
   } else {
@@ -281,7 +458,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
     const float* potg = p.poty;
     if (p.pot_sel != nullptr) potg += (long long)(*p.pot_sel) * p.pot_stride;
     const float LOG2E = 1.4426950408889634f;
-    const float k2 = p.k2, k22 = 2.f * p.k2;
+    const float k2 = p.k2, k22 = 2.f * p.k2 * (p.dotscale != nullptr ? *p.dotscale : 1.f);
     const float nxk = -k2 * xi;
     float m_run = -CUDART_INF_F, s_run = 0.f;
     // column vectors of a tile are fetched one tile ahead into registers (global-load latency hidden behind a
@@ -299,18 +476,25 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
       const uint32_t aph = (uint32_t)((t / TC_NACC) & 1);
       float* cB = colvec + (size_t)as * 2 * TC_BN;
       float* cG = cB + TC_BN;
+      if (et == 0) B2OT_TRACE(4, t);
       cG[et] = pg;
       cB[et] = fmaf(-k2, py, pg);
+      if (et == 0) B2OT_TRACE(5, t);
       fetch(t + 2);
       named_bar_sync(1 + wg, 128);
       mbar_wait_guard(&acc_full[as], aph);
       tc_fence_after();
+      if (et == 0) B2OT_TRACE(6, t);
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * TC_BN);
-      // one 32-column chunk: (pot_j - C_ij / reg) log2e = min(2 k2 x.y + B_j - k2 |x|^2, G_j)  [clamp C >= 0,
-      // ot/utils.py:299], then the online (max, sum 2^x) update; packed fp32x2 arithmetic throughout
-      auto chunk = [&](const uint32_t (&v)[32], int ch) {
-        float tv[32];
+      // One 32-column chunk in two phases (TMEM loads double-buffered one chunk ahead; interleaving P1 of the next
+      // chunk with P2 of this one in a three-buffer software pipeline measured slower: the two warps that share an
+      // SM sub-partition already overlap each other's phases):
+      //   P1: (pot_j - C_ij / reg) log2e = min(2 k2 x.y + B_j - k2 |x|^2, G_j)   [clamp C >= 0, ot/utils.py:299],
+      //       written back in place, and the chunk maximum;
+      //   P2: online (max, sum 2^x) update.  Packed fp32x2 arithmetic throughout.
+      auto phase1 = [&](uint32_t (&v)[32], int ch) -> float {
         float c0 = -CUDART_INF_F, c1 = -CUDART_INF_F;
+        if (p.dbg & 2) return c0;
 #pragma unroll
         for (int g4 = 0; g4 < 8; ++g4) {
           const float4 bq = *reinterpret_cast<const float4*>(cB + ch * 32 + g4 * 4);
@@ -325,47 +509,63 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
           r1 = fminf(r1, gq.y);
           r2 = fminf(r2, gq.z);
           r3 = fminf(r3, gq.w);
-          tv[g4 * 4 + 0] = r0;
-          tv[g4 * 4 + 1] = r1;
-          tv[g4 * 4 + 2] = r2;
-          tv[g4 * 4 + 3] = r3;
+          v[g4 * 4 + 0] = __float_as_uint(r0);
+          v[g4 * 4 + 1] = __float_as_uint(r1);
+          v[g4 * 4 + 2] = __float_as_uint(r2);
+          v[g4 * 4 + 3] = __float_as_uint(r3);
           c0 = max3(c0, r0, r1);
           c1 = max3(c1, r2, r3);
         }
-        const float m_new = max3(m_run, c0, c1);
+        return fmaxf(c0, c1);
+      };
+      auto phase2 = [&](const uint32_t (&v)[32], float cmax) {
+        if (p.dbg & 2) {
+          s_run += __uint_as_float(v[0]);
+          return;
+        }
+        const float m_new = fmaxf(m_run, cmax);
         const float mref = (m_new == -CUDART_INF_F) ? 0.f : m_new;
         const float nm = -mref;
         float s0 = s_run * ex2_ftz(m_run - mref), s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
         for (int e = 0; e < 32; e += 4) {
-          float a0 = tv[e], a1 = tv[e + 1], a2 = tv[e + 2], a3 = tv[e + 3];
+          float a0 = __uint_as_float(v[e]), a1 = __uint_as_float(v[e + 1]), a2 = __uint_as_float(v[e + 2]),
+                a3 = __uint_as_float(v[e + 3]);
           add2(a0, a1, nm, nm);
           add2(a2, a3, nm, nm);
-          a0 = ex2_ftz(a0);
-          a1 = ex2_ftz(a1);
-          a2 = ex2_ftz(a2);
-          a3 = ex2_ftz(a3);
+          if (!(p.dbg & 1)) {
+            a0 = ex2_ftz(a0);
+            a1 = ex2_ftz(a1);
+            a2 = ex2_ftz(a2);
+            a3 = ex2_ftz(a3);
+          }
           add2(s0, s1, a0, a1);
           add2(s2, s3, a2, a3);
         }
         s_run = (s0 + s1) + (s2 + s3);
         m_run = m_new;
       };
-      uint32_t v0[32], v1[32];
-      B2OT_TMEM_LD32(taddr, v0);
-      B2OT_TMEM_WAIT32(v0);
-      B2OT_TMEM_LD32(taddr + 32u, v1);
-      chunk(v0, 0);
-      B2OT_TMEM_WAIT32(v1);
-      B2OT_TMEM_LD32(taddr + 64u, v0);
-      chunk(v1, 1);
-      B2OT_TMEM_WAIT32(v0);
-      B2OT_TMEM_LD32(taddr + 96u, v1);
-      chunk(v0, 2);
-      B2OT_TMEM_WAIT32(v1);
+      if (p.dbg & 16) {  // experiment: no TMEM reads
+        tc_fence_before();
+        mbar_arrive(&acc_empty[as]);
+        continue;
+      }
+      uint32_t b0[32], b1[32];
+      B2OT_TMEM_LD32(taddr, b0);
+      B2OT_TMEM_WAIT32(b0);
+      B2OT_TMEM_LD32(taddr + 32u, b1);
+      phase2(b0, phase1(b0, 0));
+      B2OT_TMEM_WAIT32(b1);
+      B2OT_TMEM_LD32(taddr + 64u, b0);
+      phase2(b1, phase1(b1, 1));
+      B2OT_TMEM_WAIT32(b0);
+      B2OT_TMEM_LD32(taddr + 96u, b1);
+      phase2(b0, phase1(b0, 2));
+      B2OT_TMEM_WAIT32(b1);
       tc_fence_before();
       mbar_arrive(&acc_empty[as]);  // accumulator stage drained: the MMA warp may overwrite it
-      chunk(v1, 3);
+      phase2(b1, phase1(b1, 3));
+      if (et == 0) B2OT_TRACE(7, t);
     }
     // merge the two warpgroups' running (max, sum) of each row
     float* mrg = colvec + (size_t)TC_NACC * 2 * TC_BN;
@@ -387,7 +587,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
 
   // ---- teardown ----
   tc_fence_before();
-  __syncthreads();
+  if (cs > 1)
+    cluster_sync_all();  // no CTA leaves while a peer can still multicast into its shared memory
+  else
+    __syncthreads();
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);

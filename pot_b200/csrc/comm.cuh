@@ -79,6 +79,8 @@ template <typename T>
 __global__ void __launch_bounds__(256) comm_put_kernel(const CommView c, const T* __restrict__ src, long long ld, int nsrc,
                                                        long long count, const int* flag_src, const int* status,
                                                        int expect_status, unsigned long long seq) {
+  griddep_wait();
+  griddep_launch_dependents();
   __shared__ int s_last;
   if (status != nullptr && *status != expect_status) return;
   const int par = (int)(seq & 1ull);

@@ -268,6 +268,12 @@ __device__ __forceinline__ void bulk_g2s_hint(void* smem_dst, const void* gsrc, 
       : "memory");
 }
 
+// ---- programmatic dependent launch (no-ops when the kernel was launched without the attribute) ----
+// wait: the preceding kernel of the stream has completed and its memory is visible
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// the next kernel of the stream may start launching (it still blocks in its own griddep_wait)
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }

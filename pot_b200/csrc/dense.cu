@@ -236,13 +236,15 @@ static int launch_fused(b2ot_dense* h) {
   cfg.blockDim = dim3(NW * 32, 1, 1);
   cfg.dynamicSmemBytes = h->dyn_smem;
   cfg.stream = h->stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = (unsigned)h->cs;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = 2;
   B2OT_CUDA(cudaLaunchKernelEx(&cfg, fused_sweep_kernel<T, VPT, MODE, NW, OCC>, p));
   count_launch();
   return 0;
@@ -520,9 +522,10 @@ static int launch_finalize(const b2ot_dense* h, int nsrc, int init) {
     b2ot_comm* c = h->comm;
     const unsigned long long seq = ++c->seq;
     const unsigned g = (unsigned)std::min<long long>((h->m + 1 + 255) / 256, 296);
-    comm_put_kernel<T><<<g, 256, 0, h->stream>>>(c->view, (const T*)h->partials, h->mp, nsrc, h->m, &h->st->uflag,
-                                                 &h->st->status, ST_RUNNING, seq);
-    B2OT_CHECK_LAUNCH();
+    B2OT_CUDA(launch_pdl(comm_put_kernel<T>, dim3(g), dim3(256), 0, h->stream, c->view, (const T*)h->partials,
+                         (long long)h->mp, nsrc, (long long)h->m, (const int*)&h->st->uflag,
+                         (const int*)&h->st->status, (int)ST_RUNNING, seq));
+    count_launch();
     p.src = c->view.data[c->view.rank] + (size_t)((seq & 1ull) * c->view.nranks) * c->view.slot_bytes;
     p.src_ld = (long long)(c->view.slot_bytes / sizeof(T));
     p.nsrc = c->view.nranks;
@@ -564,10 +567,10 @@ static int launch_finalize(const b2ot_dense* h, int nsrc, int init) {
   p.stop_thr = h->stop_thr;
   p.init = init;
   if (h->mode == B2OT_MODE_KNOPP)
-    finalize_kernel<T, MODE_KNOPP><<<h->fin_blocks, 256, 0, h->stream>>>(p);
+    B2OT_CUDA(launch_pdl(finalize_kernel<T, MODE_KNOPP>, dim3(h->fin_blocks), dim3(256), 0, h->stream, p));
   else
-    finalize_kernel<T, MODE_LOG><<<h->fin_blocks, 256, 0, h->stream>>>(p);
-  B2OT_CHECK_LAUNCH();
+    B2OT_CUDA(launch_pdl(finalize_kernel<T, MODE_LOG>, dim3(h->fin_blocks), dim3(256), 0, h->stream, p));
+  count_launch();
   return 0;
 }
 

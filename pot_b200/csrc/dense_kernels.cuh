@@ -72,10 +72,6 @@ __global__ void __launch_bounds__(NCW * 32, OCC) fused_sweep_kernel(const SweepP
   extern __shared__ __align__(128) unsigned char dyn_smem[];
   T* const stage_base = reinterpret_cast<T*>(dyn_smem);
 
-  if (p.st->status != ST_RUNNING) return;  // sticky stop: uniform over the grid
-  const int sel_u = p.st->sel_u;
-  const int sel_v = p.st->sel_v;
-
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
   const int lane = tid & 31;
@@ -126,6 +122,21 @@ __global__ void __launch_bounds__(NCW * 32, OCC) fused_sweep_kernel(const SweepP
   }
   __syncthreads();
   cluster_sync_all();  // every CTA's barriers exist before any remote put
+
+  // Programmatic dependent launch: everything above (barrier setup, the first S row groups of K already in flight)
+  // overlaps the tail of the previous kernel of the stream (the finalize of the previous iteration); K does not
+  // depend on it.  The solver state and v do: wait for them here.
+  griddep_launch_dependents();
+  griddep_wait();
+  if (p.st->status != ST_RUNNING) {  // sticky stop (uniform over the grid): drain the copies in flight and leave
+    for (int s = 0; s < S; ++s) {
+      const long long g = cid + (long long)s * ncl;
+      if (g < NG) mbar_wait(&full_bar[s], 0);
+    }
+    return;
+  }
+  const int sel_u = p.st->sel_u;
+  const int sel_v = p.st->sel_v;
 
   const T* vcur = reinterpret_cast<const T*>(p.vring) + (long long)sel_v * p.mp + col0;
   T* unew = reinterpret_cast<T*>(p.uring) + (long long)(sel_u ^ 1) * p.n;
@@ -669,6 +680,8 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
   __shared__ int sflags;
   __shared__ int s_last;
   SolveState* st = p.st;
+  griddep_wait();               // column partials of the sweep (or the peer put) are complete and visible
+  griddep_launch_dependents();  // let the next sweep start its prologue (barriers, first K tiles) under this kernel
   if (st->status != ST_RUNNING) return;
   const int tid = threadIdx.x;
   if (p.use_comm && !comm_wait(p.comm, p.seq)) {  // fused "take" of the NVLink exchange

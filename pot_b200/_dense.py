@@ -109,6 +109,9 @@ class DenseSolver:
         names = ("variant", "cluster_size", "n_clusters", "stages", "vecs_per_thread")
         out = dict(zip(names, (x.value for x in v)))
         out["variant"] = {1: "fused", 2: "split"}.get(out["variant"], "?")
+        if out["vecs_per_thread"] >= 100:  # fp32 log domain: two independent half-CTAs (dense_logpp_kernels.cuh)
+            out["vecs_per_thread"] -= 100
+            out["schedule"] = "ping-pong"
         return out
 
     def init(self, u0, v0):

@@ -9,6 +9,7 @@
 #include "../../include/b2ot.h"
 #include "comm_host.h"
 #include "dense_kernels.cuh"
+#include "dense_logpp_kernels.cuh"
 #include "host_util.h"
 
 using namespace b2ot;
@@ -45,6 +46,7 @@ struct b2ot_dense {
   void *uring, *vring, *cbuf, *partials;
   // fused sweep configuration
   int cs, ncl, stages, vpt, nw, occ, W, use_hint;
+  int pp_vpt;  // > 0: fp32 log-domain sweeps run the ping-pong kernel with this many vectors per thread
   size_t dyn_smem;
   // split sweep / column-only pass configuration
   int nsplit, nsplit_lse;
@@ -250,6 +252,93 @@ static int launch_fused(b2ot_dense* h) {
   return 0;
 }
 
+// ---- ping-pong log-domain sweep (fp32): configuration and launch ----
+template <int VPT>
+static int config_pp(b2ot_dense* h) {
+  int stages = PP_SMAX;
+  while (stages > 2 && pp_smem_bytes(VPT, stages) > (size_t)(228 * 1024 - 4096)) --stages;
+  const char* env = getenv("B2OT_PP_STAGES");
+  if (env && atoi(env) >= 2 && atoi(env) <= stages) stages = atoi(env);
+  h->stages = stages;
+  h->dyn_smem = pp_smem_bytes(VPT, stages);
+  auto kern = log_pp_sweep_kernel<VPT>;
+  B2OT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->dyn_smem));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)h->cs, 1, 1);
+  cfg.blockDim = dim3(PP_NH * PP_NTH, 1, 1);
+  cfg.dynamicSmemBytes = h->dyn_smem;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)h->cs;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int maxcl = 0;
+  B2OT_CUDA(cudaOccupancyMaxActiveClusters(&maxcl, kern, &cfg));
+  B2OT_REQUIRE(maxcl >= 1, "ping-pong sweep: no cluster of size %d fits on this device", h->cs);
+  long long ncl = std::min<long long>(maxcl, std::max<long long>((h->n + PP_NH - 1) / PP_NH, 1));
+  const char* envc = getenv("B2OT_CLUSTERS");
+  if (envc && atoi(envc) >= 1) ncl = std::min<long long>(ncl, atoi(envc));
+  if (ncl > NPMAX) ncl = NPMAX;
+  h->ncl = (int)ncl;
+  return 0;
+}
+template <int VPT>
+static int launch_pp(b2ot_dense* h) {
+  SweepParams p;
+  p.K = h->K;
+  p.ld = h->ld;
+  p.n = h->n;
+  p.m = h->m;
+  p.mp = h->mp;
+  p.a = h->a;
+  p.uring = h->uring;
+  p.vring = h->vring;
+  p.partials = h->partials;
+  p.st = h->st;
+  p.W = h->W;
+  p.stages = h->stages;
+  p.use_hint = h->use_hint;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(h->ncl * h->cs), 1, 1);
+  cfg.blockDim = dim3(PP_NH * PP_NTH, 1, 1);
+  cfg.dynamicSmemBytes = h->dyn_smem;
+  cfg.stream = h->stream;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)h->cs;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 2;
+  B2OT_CUDA(cudaLaunchKernelEx(&cfg, log_pp_sweep_kernel<VPT>, p));
+  count_launch();
+  return 0;
+}
+static int dispatch_config_pp(b2ot_dense* h) {
+  switch (h->pp_vpt) {
+    case 4: return config_pp<4>(h);
+    case 8: return config_pp<8>(h);
+    case 16: return config_pp<16>(h);
+    default: break;
+  }
+  set_error("internal: bad ping-pong dispatch (vpt=%d)", h->pp_vpt);
+  return -1;
+}
+static int dispatch_launch_pp(b2ot_dense* h) {
+  switch (h->pp_vpt) {
+    case 4: return launch_pp<4>(h);
+    case 8: return launch_pp<8>(h);
+    case 16: return launch_pp<16>(h);
+    default: break;
+  }
+  set_error("internal: bad ping-pong dispatch (vpt=%d)", h->pp_vpt);
+  return -1;
+}
+
 #define B2OT_FUSED_CASES(FN, h, T, MODE)                          \
   if ((h)->nw == 8 && (h)->occ == 1) {                             \
     switch ((h)->vpt) {                                            \
@@ -290,8 +379,14 @@ static int launch_fused(b2ot_dense* h) {
     return -1;                                                                       \
   } while (0)
 
-static int dispatch_config_fused(b2ot_dense* h) { B2OT_DISPATCH_FUSED(config_fused, h); }
-static int dispatch_launch_fused(b2ot_dense* h) { B2OT_DISPATCH_FUSED(launch_fused, h); }
+static int dispatch_config_fused(b2ot_dense* h) {
+  if (h->pp_vpt > 0) return dispatch_config_pp(h);
+  B2OT_DISPATCH_FUSED(config_fused, h);
+}
+static int dispatch_launch_fused(b2ot_dense* h) {
+  if (h->pp_vpt > 0) return dispatch_launch_pp(h);
+  B2OT_DISPATCH_FUSED(launch_fused, h);
+}
 
 // Decide whether the fused sweep applies and pick (cluster size, vectors per thread, slice width).
 static bool plan_fused(b2ot_dense* h) {
@@ -338,6 +433,14 @@ static bool plan_fused(b2ot_dense* h) {
   h->use_hint = ((double)h->n * (double)h->ld * (double)sz > 80.0 * 1024 * 1024) ? 1 : 0;
   const char* envh = getenv("B2OT_L2_HINT");
   if (envh) h->use_hint = atoi(envh) ? 1 : 0;
+  // fp32 log domain: ping-pong schedule (two independent half-CTAs) when the slice is wide enough (B2OT_LOGPP=0: off)
+  h->pp_vpt = 0;
+  const char* envp = getenv("B2OT_LOGPP");
+  const bool pp_on = !(envp && envp[0] == '0');
+  if (pp_on && h->mode == B2OT_MODE_LOG && h->dtype == B2OT_F32 && h->nw == 8 && h->occ == 1 && h->W >= 1024 &&
+      h->W <= pp_wcap(16)) {
+    h->pp_vpt = h->W <= pp_wcap(4) ? 4 : (h->W <= pp_wcap(8) ? 8 : 16);
+  }
   return true;
 }
 
@@ -451,7 +554,8 @@ extern "C" int b2ot_dense_info(const b2ot_dense* h, int* variant, int* cluster_s
   if (cluster_size) *cluster_size = h->variant == B2OT_VARIANT_FUSED ? h->cs : 0;
   if (n_clusters) *n_clusters = h->variant == B2OT_VARIANT_FUSED ? h->ncl : h->nsplit;
   if (stages) *stages = h->variant == B2OT_VARIANT_FUSED ? h->stages : 0;
-  if (vecs_per_thread) *vecs_per_thread = h->variant == B2OT_VARIANT_FUSED ? h->vpt : 0;
+  // ping-pong log-domain sweep: reported as 100 + vectors per thread of a half-CTA
+  if (vecs_per_thread) *vecs_per_thread = h->variant == B2OT_VARIANT_FUSED ? (h->pp_vpt > 0 ? 100 + h->pp_vpt : h->vpt) : 0;
   return 0;
 }
 

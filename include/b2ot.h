@@ -112,6 +112,33 @@ size_t b2ot_dense_loss_scratch_bytes(int64_t n, int64_t m);
 int b2ot_dense_loss(int mode, int dtype, const void* K, const void* M, const void* u, const void* v, int64_t n,
                     int64_t m, int64_t ldK, int64_t ldM, double* loss_dev, void* scratch_dev, void* stream);
 
+/* ---- plan / objective epilogue: plan, value_linear, entropy / KL term and row marginal in ONE pass ----
+ * Replaces the post-solve temporaries of ot.solve (ot/solvers.py:476-483: value_linear = sum M * plan,
+ * value = value_linear + reg * sum plan log(plan + 1e-16)  or  + reg * kl_div(plan, a b^T), ot/backend.py:1542-1546)
+ * and of sinkhorn_knopp_unbalanced's log (ot/unbalanced/_sinkhorn.py:785-797: cost, kl_div(plan, c), plan 1).
+ *
+ *   K (n x m) : Gibbs kernel (KNOPP) / scaled cost (LOG) the solve ran on, or NULL to rebuild it from the cost:
+ *               LOG K = -M/reg (ot/bregman/_sinkhorn.py:860); KNOPP K = exp(M/(-reg)) (:621), times q_ij when
+ *               B2OT_VALUE_KMULQ is set (ot/unbalanced/_sinkhorn.py:736-740) -- then M is read once, plan written once;
+ *   Cref      : optional n x m reference matrix q of the KL term; NULL: q_ij = a_i b_j (needs a, b);
+ *   plan_out  : n x m or NULL (values only);  rowsum_out : n values (plan 1) or NULL;
+ *   terms     : OR of B2OT_VALUE_*;  values_dev: 3 doubles {sum M*P, sum P log(P + 1e-16), sum P log(P/q + 1e-16)}
+ *               (terms not requested are written as 0);  scratch_dev >= b2ot_dense_plan_value_scratch_bytes(n, m). */
+#define B2OT_VALUE_LINEAR 1
+#define B2OT_VALUE_ENTROPY 2
+#define B2OT_VALUE_KL 4
+#define B2OT_VALUE_KMULQ 8
+size_t b2ot_dense_plan_value_scratch_bytes(int64_t n, int64_t m);
+int b2ot_dense_plan_value(int mode, int dtype, const void* K, const void* M, const void* Cref, double reg,
+                          const void* u, const void* v, const void* a, const void* b, void* plan_out,
+                          void* rowsum_out, int64_t n, int64_t m, int64_t ldK, int64_t ldM, int64_t ldC,
+                          int64_t ldOut, int terms, double* values_dev, void* scratch_dev, void* stream);
+/* column marginal out_j = sum_i P_ij (nx.sum(plan, 0), ot/unbalanced/_sinkhorn.py:795); deterministic;
+ * scratch_dev >= b2ot_colsum_scratch_bytes(n, m) */
+size_t b2ot_colsum_scratch_bytes(int64_t n, int64_t m);
+int b2ot_colsum(int dtype, const void* P, int64_t n, int64_t m, int64_t ld, void* out, void* scratch_dev,
+                void* stream);
+
 /* ---- batched Sinkhorn (ot.batch): B independent n x m problems, each solved on chip ----
  * Replaces bregman_projection_batch (ot/batch/_utils.py:46-162; mode KNOPP, potentials = scalings f, g),
  * bregman_log_projection_batch (ot/batch/_utils.py:165-290; mode LOG, potentials = log-scalings u, v) and

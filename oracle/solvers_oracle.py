@@ -1,0 +1,221 @@
+"""CPU oracle for the callers right after the Sinkhorn hot path (TEST INFRASTRUCTURE ONLY).
+
+numpy restatement of the reference's `ot.solve` / `ot.solve_sample` Sinkhorn branches, the lazy
+`empirical_sinkhorn2` loss, `empirical_sinkhorn_divergence` and `sinkhorn_knopp_unbalanced` (SURVEY.md
+section 8f, ranks 1-3).  Only ``tests/`` may import it; nothing under ``pot_b200/`` does.
+
+Parity status: PINNED.  ``tests/golden/make_golden_solvers.py`` ran the unmodified reference (imported from
+/root/reference in the build container) on seeded inputs and committed its outputs as
+``tests/golden/golden_solvers.npz``; ``tests/test_oracle_solvers.py`` checks every function below against them.
+
+Each function cites the reference file:line (relative to /root/reference) it restates.
+"""
+
+import warnings
+
+import numpy as np
+
+from . import sinkhorn_oracle as so
+
+__all__ = ["solve", "solve_sample_lazy", "empirical_sinkhorn2_lazy", "empirical_sinkhorn_divergence_lazy",
+           "sinkhorn_knopp_unbalanced", "solve_unbalanced"]
+
+
+def _kl_div(p, q, eps=1e-16):
+    """nx.kl_div with mass=False (ot/backend.py:1542-1546)."""
+    return np.sum(p * np.log(p / q + eps))
+
+
+def solve(M, a=None, b=None, reg=None, reg_type="KL", max_iter=None, tol=None, grad="autodiff"):
+    """Balanced entropic branch of ot.solve (ot/solvers.py:300-304, :429-494).
+
+    Returns a dict with plan, potentials (log-scalings), value_linear, value and the envelope gradients
+    (dM, da, db) = (plan, reg (f - mean f), reg (g - mean g)) that grad="envelope" attaches (:485-494).
+    grad="last_step": max_iter - 1 iterations, then one step in which BOTH updates start from the loop's
+    potentials (:463-474).
+    """
+    M = np.asarray(M)
+    n, m = M.shape
+    if a is None:
+        a = (np.ones(n) / n).astype(M.dtype)
+    if b is None:
+        b = (np.ones(m) / m).astype(M.dtype)
+    rt = reg_type.lower()
+    if rt not in ("entropy", "kl"):
+        raise NotImplementedError('Not implemented reg_type="{}"'.format(reg_type))
+    if max_iter is None:
+        max_iter = 1000
+    if tol is None:
+        tol = 1e-9
+    if grad == "last_step":
+        if max_iter == 0:
+            raise ValueError("The maximum number of iterations must be greater than 0 when using grad=last_step.")
+        max_iter = max_iter - 1
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        plan, log = so.sinkhorn_log(a, b, M, reg, numItermax=max_iter, stopThr=tol, log=True)
+    f, g = log["log_u"], log["log_v"]
+    if max_iter == 0:  # the reference loop body never runs: potentials stay at zero
+        f, g = np.zeros(n, dtype=M.dtype), np.zeros(m, dtype=M.dtype)
+    if grad == "last_step":
+        from scipy.special import logsumexp
+
+        loga, logb = np.log(a), np.log(b)
+        v = logb - logsumexp(-M / reg + f[:, None], 0)
+        u = loga - logsumexp(-M / reg + g[None, :], 1)
+        plan = np.exp(-M / reg + u[:, None] + v[None, :])
+        f, g = u, v
+    value_linear = np.sum(M * plan)
+    if rt == "entropy":
+        value = value_linear + reg * np.sum(plan * np.log(plan + 1e-16))
+    else:
+        value = value_linear + reg * _kl_div(plan, a[:, None] * b[None, :])
+    return {"plan": plan, "potentials": (f, g), "value_linear": value_linear, "value": value,
+            "grad_M": plan, "grad_a": reg * (f - f.mean()), "grad_b": reg * (g - g.mean())}
+
+
+def empirical_sinkhorn2_lazy(X_s, X_t, reg, a=None, b=None, numIterMax=10000, stopThr=1e-9, batchSize=100,
+                             log=False, warn=True, warmstart=None):
+    """Lazy branch of empirical_sinkhorn2 (ot/bregman/_empirical.py:413-483): solve, then
+    loss = sum over source blocks of sum(M_block * exp(f_i + g_j - M_block / reg)) (:466-478)."""
+    X_s, X_t = np.asarray(X_s), np.asarray(X_t)
+    ns, nt = X_s.shape[0], X_t.shape[0]
+    if a is None:
+        a = (np.ones((ns,)) / ns).astype(X_s.dtype)
+    if b is None:
+        b = (np.ones((nt,)) / nt).astype(X_s.dtype)
+    f, g, hist = so.empirical_sinkhorn_lazy(X_s, X_t, reg, a, b, numIterMax=numIterMax, stopThr=stopThr,
+                                            batchSize=batchSize, log=True, warn=warn, warmstart=warmstart)
+    bs = batchSize if isinstance(batchSize, int) else batchSize[0]
+    loss = 0
+    for i in range(0, ns, bs):
+        Mb = so.sqeuclidean(X_s[i:i + bs, :], X_t).astype(a.dtype, copy=False)
+        loss += np.sum(Mb * np.exp(f[i:i + bs, None] + g[None, :] - Mb / reg))
+    return (loss, hist) if log else loss
+
+
+def empirical_sinkhorn_divergence_lazy(X_s, X_t, reg, a=None, b=None, numIterMax=10000, stopThr=1e-9, warn=True,
+                                       warmstart=None, batchSize=100):
+    """empirical_sinkhorn_divergence with isLazy=True (ot/bregman/_empirical.py:640-763):
+    max(0, W_ab - (W_aa + W_bb) / 2); warm starts (u, u) and (v, v) for the symmetric terms (:646-648)."""
+    if warmstart is None:
+        ws_a = ws_b = None
+    else:
+        u, v = warmstart
+        ws_a, ws_b = (u, u), (v, v)
+    kw = dict(numIterMax=numIterMax, stopThr=stopThr, batchSize=batchSize, warn=warn)
+    l_ab = empirical_sinkhorn2_lazy(X_s, X_t, reg, a, b, warmstart=warmstart, **kw)
+    l_a = empirical_sinkhorn2_lazy(X_s, X_s, reg, a, a, warmstart=ws_a, **kw)
+    l_b = empirical_sinkhorn2_lazy(X_t, X_t, reg, b, b, warmstart=ws_b, **kw)
+    return np.maximum(0, l_ab - 0.5 * (l_a + l_b)), (l_ab, l_a, l_b)
+
+
+def solve_sample_lazy(X_a, X_b, a=None, b=None, reg=None, max_iter=None, tol=None, batch_size=None):
+    """Lazy regularised branch of ot.solve_sample (ot/solvers.py:1977-2002): defaults 1000 / 1e-9 / 100;
+    value_linear from empirical_sinkhorn2, potentials = (log["u"], log["v"]) = (f, g)."""
+    if max_iter is None:
+        max_iter = 1000
+    if tol is None:
+        tol = 1e-9
+    if batch_size is None:
+        batch_size = 100
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        value_linear, log = empirical_sinkhorn2_lazy(X_a, X_b, reg, a, b, numIterMax=max_iter, stopThr=tol,
+                                                     batchSize=batch_size, log=True)
+    return {"value_linear": value_linear, "potentials": (log["u"], log["v"]), "niter": log["niter"]}
+
+
+def sinkhorn_knopp_unbalanced(a, b, M, reg, reg_m, reg_type="kl", c=None, warmstart=None, numItermax=1000,
+                              stopThr=1e-6, log=False):
+    """Scaling-domain unbalanced Sinkhorn (ot/unbalanced/_sinkhorn.py:690-804).
+
+    K = exp(-M/reg) * c with c = a b^T by default, the one matrix for reg_type "entropy" (:727-740; no c factor for
+    2-D b); per iteration u = (a / Kv)^fi_1, v = (b / K^T u)^fi_2 (:749-758); guard -> previous (u, v) and stop
+    (:760-772); err = (|u - uprev|_inf / max(|u|_inf, |uprev|_inf, 1) + same for v) / 2 every iteration, `<` stop
+    test (:774-787); log: err, logu = log(u + 1e-300), logv, cost, total_cost (:789-814)."""
+    a, b, M = (np.asarray(x) for x in (a, b, M))
+    dim_a, dim_b = M.shape
+    if len(a) == 0:
+        a = (np.ones(dim_a) / dim_a).astype(M.dtype)
+    if len(b) == 0:
+        b = (np.ones(dim_b) / dim_b).astype(M.dtype)
+    n_hists = b.shape[1] if b.ndim > 1 else 0
+    if isinstance(reg_m, (tuple, list)):
+        reg_m1, reg_m2 = (reg_m[0], reg_m[0]) if len(reg_m) == 1 else (reg_m[0], reg_m[1])
+    else:
+        reg_m1 = reg_m2 = reg_m
+    hist = {"err": []}
+    if warmstart is None:
+        if n_hists:
+            u = np.ones((dim_a, 1), dtype=M.dtype)
+            v = np.ones((dim_b, n_hists), dtype=M.dtype)
+            a = a.reshape(dim_a, 1)
+        else:
+            u = np.ones(dim_a, dtype=M.dtype)
+            v = np.ones(dim_b, dtype=M.dtype)
+    else:
+        u, v = np.exp(warmstart[0]), np.exp(warmstart[1])
+    if reg_type.lower() == "entropy":
+        c = np.ones((dim_a, dim_b), dtype=M.dtype)
+    if n_hists:
+        K = np.exp(-M / reg)
+    else:
+        c = a[:, None] * b[None, :] if c is None else c
+        K = np.exp(-M / reg) * c
+    fi_1 = reg_m1 / (reg_m1 + reg) if reg_m1 != float("inf") else 1
+    fi_2 = reg_m2 / (reg_m2 + reg) if reg_m2 != float("inf") else 1
+    for i in range(numItermax):
+        uprev, vprev = u, v
+        Kv = np.dot(K, v)
+        u = (a / Kv) ** fi_1
+        Ktu = np.dot(K.T, u)
+        v = (b / Ktu) ** fi_2
+        if (np.any(Ktu == 0.0) or np.any(np.isnan(u)) or np.any(np.isnan(v)) or np.any(np.isinf(u))
+                or np.any(np.isinf(v))):
+            warnings.warn("Numerical errors at iteration %s" % i)
+            u, v = uprev, vprev
+            break
+        err_u = np.max(np.abs(u - uprev)) / max(np.max(np.abs(u)), np.max(np.abs(uprev)), 1.0)
+        err_v = np.max(np.abs(v - vprev)) / max(np.max(np.abs(v)), np.max(np.abs(vprev)), 1.0)
+        err = 0.5 * (err_u + err_v)
+        hist["err"].append(err)
+        if err < stopThr:
+            break
+    hist["logu"] = np.log(u + 1e-300)
+    hist["logv"] = np.log(v + 1e-300)
+    if n_hists:
+        res = np.einsum("ik,ij,jk,ij->k", u, K, v, M)
+        return (res, hist) if log else res
+    plan = u[:, None] * K * v[None, :]
+    if log:
+        linear_cost = np.sum(plan * M)
+        hist["cost"] = linear_cost
+        total = linear_cost + reg * _kl_div(plan, c)
+        if reg_m1 != float("inf"):
+            total = total + reg_m1 * _kl_div(np.sum(plan, 1), a)
+        if reg_m2 != float("inf"):
+            total = total + reg_m2 * _kl_div(np.sum(plan, 0), b)
+        hist["total_cost"] = total
+        return plan, hist
+    return plan
+
+
+def solve_unbalanced(M, a=None, b=None, reg=None, unbalanced=None, max_iter=None, tol=None):
+    """Unbalanced KL branch of ot.solve (ot/solvers.py:300-306, :524-556): defaults 1000 / 1e-9,
+    c = a b^T, value_linear = log["cost"], value = log["total_cost"], potentials = (logu, logv)."""
+    M = np.asarray(M)
+    n, m = M.shape
+    if a is None:
+        a = (np.ones(n) / n).astype(M.dtype)
+    if b is None:
+        b = (np.ones(m) / m).astype(M.dtype)
+    c = a[:, None] * b[None, :]
+    if max_iter is None:
+        max_iter = 1000
+    if tol is None:
+        tol = 1e-9
+    plan, log = sinkhorn_knopp_unbalanced(a, b, M, reg, unbalanced, reg_type="kl", c=c, numItermax=max_iter,
+                                          stopThr=tol, log=True)
+    return {"plan": plan, "potentials": (log["logu"], log["logv"]), "value_linear": log["cost"],
+            "value": log["total_cost"], "err": log["err"]}

@@ -195,3 +195,52 @@ def loss(mode, K, M, u, v):
                                        K.shape[1], K.stride(0), M.stride(0), out.data_ptr(), scratch.data_ptr(),
                                        stream_ptr(K.device)), "b2ot_dense_loss")
     return out
+
+
+def plan_value(mode, u, v, *, K=None, M=None, reg=0.0, a=None, b=None, c=None, terms=(), want_plan=True,
+               want_rowsum=False, kmulq=False):
+    """Plan + objective terms + row marginal in one pass (b2ot_dense_plan_value).
+
+    K None: the Gibbs kernel / scaled cost is rebuilt from the cost M with `reg` (M read once, plan written once).
+    terms : subset of {"linear", "entropy", "kl"}.
+    Returns (plan or None, values (3,) float64 device tensor [sum M*P, sum P log(P+1e-16), sum P log(P/q+1e-16)],
+    rowsum or None).
+    """
+    lib = _lib.load()
+    ref = K if K is not None else M
+    n, m = ref.shape
+    code = dtype_code(ref.dtype)
+    bits = 0
+    for t in terms:
+        bits |= {"linear": _lib.VALUE_LINEAR, "entropy": _lib.VALUE_ENTROPY, "kl": _lib.VALUE_KL}[t]
+    if kmulq:
+        bits |= _lib.VALUE_KMULQ
+    out = torch.empty((n, m), dtype=ref.dtype, device=ref.device) if want_plan else None
+    rows = torch.empty(n, dtype=ref.dtype, device=ref.device) if want_rowsum else None
+    vals = torch.empty(3, dtype=torch.float64, device=ref.device)
+    scratch = torch.empty(lib.b2ot_dense_plan_value_scratch_bytes(n, m), dtype=torch.uint8, device=ref.device)
+
+    def ptr(t):
+        return t.data_ptr() if t is not None else None
+
+    def ld(t):
+        return t.stride(0) if t is not None else 0
+
+    with torch.cuda.device(ref.device):
+        _lib.check(lib.b2ot_dense_plan_value(
+            _lib.MODE_KNOPP if mode == "knopp" else _lib.MODE_LOG, code, ptr(K), ptr(M), ptr(c), float(reg),
+            u.data_ptr(), v.data_ptr(), ptr(a), ptr(b), ptr(out), ptr(rows), n, m, ld(K), ld(M), ld(c), ld(out),
+            bits, vals.data_ptr(), scratch.data_ptr(), stream_ptr(ref.device)), "b2ot_dense_plan_value")
+    return out, vals, rows
+
+
+def colsum(P):
+    """Column marginal P^T 1 (b2ot_colsum), deterministic."""
+    lib = _lib.load()
+    n, m = P.shape
+    out = torch.empty(m, dtype=P.dtype, device=P.device)
+    scratch = torch.empty(lib.b2ot_colsum_scratch_bytes(n, m), dtype=torch.uint8, device=P.device)
+    with torch.cuda.device(P.device):
+        _lib.check(lib.b2ot_colsum(dtype_code(P.dtype), P.data_ptr(), n, m, P.stride(0), out.data_ptr(),
+                                   scratch.data_ptr(), stream_ptr(P.device)), "b2ot_colsum")
+    return out

@@ -16,6 +16,7 @@ ST_RUNNING, ST_CONVERGED, ST_NUMERR, ST_MAXITER = 0, 1, 2, 3
 VARIANT_AUTO, VARIANT_FUSED, VARIANT_SPLIT = 0, 1, 2
 OP_SUM, OP_MAX = 0, 1
 BATCH_FORCE_EXACT = 1
+VALUE_LINEAR, VALUE_ENTROPY, VALUE_KL, VALUE_KMULQ = 1, 2, 4, 8
 
 ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_void_p)
 
@@ -49,6 +50,14 @@ PROTOTYPES = {
     "b2ot_dense_loss_scratch_bytes": (C.c_size_t, [C.c_int64, C.c_int64]),
     "b2ot_dense_loss": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                   C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b2ot_dense_plan_value_scratch_bytes": (C.c_size_t, [C.c_int64, C.c_int64]),
+    "b2ot_dense_plan_value": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_void_p,
+                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                        C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int, C.c_void_p,
+                                        C.c_void_p, C.c_void_p]),
+    "b2ot_colsum_scratch_bytes": (C.c_size_t, [C.c_int64, C.c_int64]),
+    "b2ot_colsum": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
+                              C.c_void_p]),
     "b2ot_batch_workspace_bytes": (C.c_size_t, [C.c_int64]),
     "b2ot_batch_config": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_int64, C.POINTER(C.c_int), C.POINTER(C.c_int),
                                     C.POINTER(C.c_int)]),

@@ -1,0 +1,97 @@
+// C ABI of the plan / objective epilogue (see include/b2ot.h, value_kernels.cuh).
+#include <algorithm>
+#include <cstdint>
+
+#include "../../include/b2ot.h"
+#include "host_util.h"
+#include "value_kernels.cuh"
+
+using namespace b2ot;
+
+static const int kPvBlocks = 148 * 8;
+static const int kColSplit = 32;
+
+extern "C" size_t b2ot_dense_plan_value_scratch_bytes(int64_t, int64_t) { return 3 * kPvBlocks * sizeof(double); }
+
+template <typename T, int MODE>
+static int launch_plan_value(const PlanValueParams& p, bool vect, double* values, cudaStream_t s) {
+  if (vect)
+    plan_value_kernel<T, MODE, true><<<p.nblk, 256, 0, s>>>(p);
+  else
+    plan_value_kernel<T, MODE, false><<<p.nblk, 256, 0, s>>>(p);
+  B2OT_CHECK_LAUNCH();
+  plan_value_reduce_kernel<<<3, 256, 0, s>>>(p.blk, p.nblk, values);
+  B2OT_CHECK_LAUNCH();
+  return 0;
+}
+
+static inline bool aligned16(const void* q) { return q == nullptr || ((uintptr_t)q % 16) == 0; }
+
+extern "C" int b2ot_dense_plan_value(int mode, int dtype, const void* K, const void* M, const void* Cref, double reg,
+                                     const void* u, const void* v, const void* a, const void* b, void* plan_out,
+                                     void* rowsum_out, int64_t n, int64_t m, int64_t ldK, int64_t ldM, int64_t ldC,
+                                     int64_t ldOut, int terms, double* values_dev, void* scratch_dev, void* stream) {
+  B2OT_REQUIRE(mode == B2OT_MODE_KNOPP || mode == B2OT_MODE_LOG, "b2ot_dense_plan_value: bad mode %d", mode);
+  B2OT_REQUIRE(dtype == B2OT_F32 || dtype == B2OT_F64, "b2ot_dense_plan_value: bad dtype %d", dtype);
+  B2OT_REQUIRE(n >= 1 && m >= 1, "b2ot_dense_plan_value: bad shape n=%lld m=%lld", (long long)n, (long long)m);
+  B2OT_REQUIRE(u && v && values_dev && scratch_dev, "b2ot_dense_plan_value: null device pointer");
+  B2OT_REQUIRE(K != nullptr || M != nullptr, "b2ot_dense_plan_value: need K or the cost M");
+  B2OT_REQUIRE(!(terms & B2OT_VALUE_LINEAR) || M != nullptr, "b2ot_dense_plan_value: the linear term needs M");
+  B2OT_REQUIRE(K != nullptr || reg > 0.0, "b2ot_dense_plan_value: rebuilding K from the cost needs reg > 0");
+  const bool need_q = (terms & B2OT_VALUE_KL) || ((terms & B2OT_VALUE_KMULQ) && K == nullptr);
+  B2OT_REQUIRE(!need_q || Cref != nullptr || (a != nullptr && b != nullptr),
+               "b2ot_dense_plan_value: the KL reference needs c or (a, b)");
+  PlanValueParams p;
+  p.K = K;
+  p.M = M;
+  p.C = Cref;
+  p.u = u;
+  p.v = v;
+  p.a = a;
+  p.b = b;
+  p.out = plan_out;
+  p.rowsum = rowsum_out;
+  p.n = n;
+  p.m = m;
+  p.ldK = ldK;
+  p.ldM = ldM;
+  p.ldC = ldC;
+  p.ldO = ldOut;
+  p.reg = reg;
+  p.terms = terms;
+  p.nblk = (int)std::min<long long>(n, kPvBlocks);
+  p.blk = (double*)scratch_dev;
+  const int vec = dtype == B2OT_F64 ? 2 : 4;
+  const bool vect = m % vec == 0 && (K == nullptr || ldK % vec == 0) && (M == nullptr || ldM % vec == 0) &&
+                    (Cref == nullptr || ldC % vec == 0) && (plan_out == nullptr || ldOut % vec == 0) &&
+                    aligned16(K) && aligned16(M) && aligned16(Cref) && aligned16(plan_out) && aligned16(v) &&
+                    aligned16(b);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (dtype == B2OT_F32)
+    return mode == B2OT_MODE_KNOPP ? launch_plan_value<float, MODE_KNOPP>(p, vect, values_dev, s)
+                                   : launch_plan_value<float, MODE_LOG>(p, vect, values_dev, s);
+  return mode == B2OT_MODE_KNOPP ? launch_plan_value<double, MODE_KNOPP>(p, vect, values_dev, s)
+                                 : launch_plan_value<double, MODE_LOG>(p, vect, values_dev, s);
+}
+
+extern "C" size_t b2ot_colsum_scratch_bytes(int64_t, int64_t m) { return (size_t)kColSplit * (size_t)m * sizeof(double); }
+
+extern "C" int b2ot_colsum(int dtype, const void* P, int64_t n, int64_t m, int64_t ld, void* out, void* scratch_dev,
+                           void* stream) {
+  B2OT_REQUIRE(dtype == B2OT_F32 || dtype == B2OT_F64, "b2ot_colsum: bad dtype %d", dtype);
+  B2OT_REQUIRE(P && out && scratch_dev && n >= 1 && m >= 1 && ld >= m, "b2ot_colsum: bad arguments");
+  const int S = (int)std::min<long long>(n, kColSplit);
+  dim3 grid((unsigned)((m + 255) / 256), (unsigned)S);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (dtype == B2OT_F32) {
+    colsum_kernel<float><<<grid, 256, 0, s>>>((const float*)P, n, m, ld, (double*)scratch_dev);
+    B2OT_CHECK_LAUNCH();
+    colsum_reduce_kernel<float><<<grid.x, 256, 0, s>>>((const double*)scratch_dev, m, S, (float*)out);
+  } else {
+    colsum_kernel<double><<<grid, 256, 0, s>>>((const double*)P, n, m, ld, (double*)scratch_dev);
+    B2OT_CHECK_LAUNCH();
+    colsum_reduce_kernel<double><<<grid.x, 256, 0, s>>>((const double*)scratch_dev, m, S, (double*)out);
+  }
+  B2OT_CHECK_LAUNCH();
+  return 0;
+}

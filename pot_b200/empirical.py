@@ -6,6 +6,7 @@ Mirrors (same names, argument meaning, return values, warnings and errors):
     ot.bregman.empirical_sinkhorn              ot/bregman/_empirical.py:74-302
     ot.bregman.empirical_sinkhorn2             ot/bregman/_empirical.py:305-517
     ot.bregman.get_sinkhorn_lazytensor         ot/bregman/_empirical.py:26-71
+    ot.bregman.empirical_sinkhorn_divergence   ot/bregman/_empirical.py:520-763
 
 `isLazy=True` runs the online-cost log-domain solver of libb2ot.so: every half-iteration is one sweep that
 forms the cost tile from the point clouds in registers (-2 x.y^T + |x|^2 + |y|^2, clamped at 0), adds the
@@ -23,7 +24,8 @@ from . import _dense, _lib
 from .bregman import _NOCONV, sinkhorn, sinkhorn2
 from .utils import LazyTensor
 
-__all__ = ["dist", "empirical_sinkhorn", "empirical_sinkhorn2", "get_sinkhorn_lazytensor", "EmpiricalSolver"]
+__all__ = ["dist", "empirical_sinkhorn", "empirical_sinkhorn2", "empirical_sinkhorn_divergence",
+           "get_sinkhorn_lazytensor", "EmpiricalSolver"]
 
 POLL_EVERY = 50
 _METRICS = {"sqeuclidean": _lib.METRIC_SQEUCLIDEAN, "euclidean": _lib.METRIC_EUCLIDEAN}
@@ -318,3 +320,30 @@ def empirical_sinkhorn2(X_s, X_t, reg, a=None, b=None, metric="sqeuclidean", num
     M = dist(X_s, X_t, metric=metric)
     return sinkhorn2(a, b, M, reg, numItermax=numIterMax, stopThr=stopThr, verbose=verbose, log=log, warn=warn,
                      warmstart=warmstart, **kwargs)
+
+
+def empirical_sinkhorn_divergence(X_s, X_t, reg, a=None, b=None, metric="sqeuclidean", numIterMax=10000,
+                                  stopThr=1e-9, verbose=False, log=False, warn=True, warmstart=None, **kwargs):
+    """Drop-in for ot.bregman.empirical_sinkhorn_divergence (ot/bregman/_empirical.py:520-763).
+
+    S = max(0, W(X_s, X_t) - (W(X_s, X_s) + W(X_t, X_t)) / 2), three `empirical_sinkhorn2` solves; `isLazy=True`
+    (through **kwargs, as in the reference) keeps all three on the online-cost kernels.
+    """
+    if warmstart is None:
+        warmstart_a, warmstart_b = None, None
+    else:
+        u, v = warmstart
+        warmstart_a, warmstart_b = (u, u), (v, v)  # :646-648
+    common = dict(metric=metric, numIterMax=numIterMax, stopThr=stopThr, verbose=verbose, log=log, warn=warn)
+    r_ab = empirical_sinkhorn2(X_s, X_t, reg, a, b, warmstart=warmstart, **common, **kwargs)
+    r_a = empirical_sinkhorn2(X_s, X_s, reg, a, a, warmstart=warmstart_a, **common, **kwargs)
+    r_b = empirical_sinkhorn2(X_t, X_t, reg, b, b, warmstart=warmstart_b, **common, **kwargs)
+    if log:
+        (l_ab, log_ab), (l_a, log_a), (l_b, log_b) = r_ab, r_a, r_b
+    else:
+        l_ab, l_a, l_b = r_ab, r_a, r_b
+    div = torch.clamp(l_ab - 0.5 * (l_a + l_b), min=0)
+    if log:
+        return div, {"sinkhorn_loss_ab": l_ab, "sinkhorn_loss_a": l_a, "sinkhorn_loss_b": l_b,
+                     "log_sinkhorn_ab": log_ab, "log_sinkhorn_a": log_a, "log_sinkhorn_b": log_b}
+    return div

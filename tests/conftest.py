@@ -50,3 +50,9 @@ def golden():
 @pytest.fixture(scope="session")
 def golden_c1():
     return np.load(os.path.join(GOLDEN_DIR, "golden_c1.npz"), allow_pickle=False)
+
+
+@pytest.fixture(scope="session")
+def gs():
+    """Golden vectors of the callers after the path (ot.solve, unbalanced, divergence): golden_solvers.npz."""
+    return Golden(os.path.join(GOLDEN_DIR, "golden_solvers.npz"))

@@ -1,0 +1,220 @@
+"""GPU parity tests of ot.solve / ot.solve_sample / empirical_sinkhorn_divergence
+against the golden vectors of the reference (tests/golden/golden_solvers.npz) and the CPU oracle.
+Everything goes through libb2ot.so (C ABI) via pot_b200.
+
+Tolerances (north_star): 1e-10 relative in fp64, 1e-4 relative in fp32, fixed iteration count.
+"""
+import warnings
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+if torch.cuda.is_available():
+    import pot_b200 as ot
+from oracle import solvers_oracle as sorc
+
+DEV = "cuda:0"
+SOLVE_CASES = [f"solve_{t}_{s}" for t in ("f64", "f32") for s in ("40x52", "128x96")]
+
+
+def tol_of(case):
+    return 1e-10 if "f64" in case else 1e-4
+
+
+def to_dev(*xs):
+    return [torch.as_tensor(np.ascontiguousarray(x), device=DEV) for x in xs]
+
+
+def npf(x):
+    return x.detach().cpu().numpy().astype(np.float64)
+
+
+def assert_plan(G, Gref, tol):
+    G, Gref = npf(G), np.asarray(Gref, dtype=np.float64)
+    err = np.abs(G - Gref) / (np.abs(Gref) + 1e-6 * Gref.max())
+    assert err.max() < tol, f"plan rel err {err.max():.3e} >= {tol}"
+
+
+def assert_vec(x, ref, tol):
+    x, ref = npf(x), np.asarray(ref, dtype=np.float64)
+    err = np.abs(x - ref).max() / max(1.0, np.abs(ref).max())
+    assert err < tol, f"vector err {err:.3e} >= {tol}"
+
+
+def assert_scalar(x, ref, tol, scale=None):
+    x, ref = float(x), float(ref)
+    s = abs(ref) if scale is None else scale
+    assert abs(x - ref) <= tol * s, f"scalar {x} vs {ref} (tol {tol}, scale {s})"
+
+
+@pytest.mark.parametrize("case", SOLVE_CASES)
+@pytest.mark.parametrize("rt", ["KL", "entropy"])
+def test_solve_balanced_golden(gs, case, rt):
+    M, a, b = to_dev(gs(case, "M"), gs(case, "a"), gs(case, "b"))
+    reg, its, tol = float(gs(case, "reg")), int(gs(case, "its")), tol_of(case)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        r = ot.solve(M, a, b, reg=reg, reg_type=rt, max_iter=its, tol=0)
+    c = f"{case}/{rt}"
+    assert r.plan.dtype == M.dtype and r.plan.device == M.device
+    assert_plan(r.plan, gs(c, "plan"), tol)
+    assert_vec(r.potentials[0], gs(c, "f"), tol)
+    assert_vec(r.potentials[1], gs(c, "g"), tol)
+    lin = float(gs(c, "value_linear"))
+    assert_scalar(r.value_linear, lin, tol)
+    # the regularisation term is O(reg * log n) next to value_linear: compare on that scale
+    assert_scalar(r.value, gs(c, "value"), tol, scale=max(abs(lin), abs(float(gs(c, "value")))))
+    assert r.value.dtype == M.dtype
+
+
+@pytest.mark.parametrize("case", SOLVE_CASES)
+@pytest.mark.parametrize("rt", ["KL", "entropy"])
+def test_solve_envelope_gradients(gs, case, rt):
+    M, a, b = to_dev(gs(case, "M"), gs(case, "a"), gs(case, "b"))
+    for t in (M, a, b):
+        t.requires_grad_(True)
+    reg, its, tol = float(gs(case, "reg")), int(gs(case, "its")), tol_of(case)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        r = ot.solve(M, a, b, reg=reg, reg_type=rt, max_iter=its, tol=0, grad="envelope")
+    r.value.backward()
+    c = f"{case}/{rt}_envelope"
+    assert M.grad.shape == M.shape and a.grad.shape == a.shape and b.grad.shape == b.shape
+    assert_plan(M.grad, gs(c, "gM"), tol)
+    assert_vec(a.grad, gs(c, "ga"), tol)
+    assert_vec(b.grad, gs(c, "gb"), tol)
+    # detach: no graph
+    r = ot.solve(M, a, b, reg=reg, reg_type=rt, max_iter=its, tol=0, grad="detach")
+    with pytest.raises(RuntimeError):
+        r.value.backward()
+
+
+@pytest.mark.parametrize("case", SOLVE_CASES[:1] + SOLVE_CASES[2:3])
+def test_solve_autodiff_substitutes_envelope(gs, case):
+    M, a, b = to_dev(gs(case, "M"), gs(case, "a"), gs(case, "b"))
+    M.requires_grad_(True)
+    reg, its, tol = float(gs(case, "reg")), int(gs(case, "its")), tol_of(case)
+    with pytest.warns(UserWarning, match="forward-only"):
+        r = ot.solve(M, a, b, reg=reg, max_iter=its, tol=0)
+    r.value.backward()
+    assert_plan(M.grad, gs(f"{case}/KL_envelope", "gM"), tol)
+    assert a.grad is None
+
+
+@pytest.mark.parametrize("case", SOLVE_CASES)
+@pytest.mark.parametrize("rt", ["KL", "entropy"])
+def test_solve_last_step(gs, case, rt):
+    M, a, b = to_dev(gs(case, "M"), gs(case, "a"), gs(case, "b"))
+    reg, its, tol = float(gs(case, "reg")), int(gs(case, "its")), tol_of(case)
+    c = f"{case}/{rt}_last_step"
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        r = ot.solve(M, a, b, reg=reg, reg_type=rt, max_iter=its, tol=0, grad="last_step")
+        assert_plan(r.plan, gs(c, "plan"), tol)
+        assert_vec(r.potentials[0], gs(c, "f"), tol)
+        lin = float(gs(c, "value_linear"))
+        assert_scalar(r.value, gs(c, "value"), tol, scale=max(abs(lin), abs(float(gs(c, "value")))))
+        # differentiable variant: same numbers, gradients flow through the last step only
+        for t in (M, a, b):
+            t.requires_grad_(True)
+        r = ot.solve(M, a, b, reg=reg, reg_type=rt, max_iter=its, tol=0, grad="last_step")
+    assert_plan(r.plan, gs(c, "plan"), tol)
+    assert_scalar(r.value, gs(c, "value"), tol, scale=max(abs(lin), abs(float(gs(c, "value")))))
+    r.value.backward()
+    assert M.grad.shape == M.shape and torch.isfinite(M.grad).all()
+    assert a.grad.shape == a.shape and b.grad.shape == b.shape
+    with pytest.raises(ValueError):
+        ot.solve(M, a, b, grad="last_step", max_iter=0, reg=reg)
+
+
+@pytest.mark.parametrize("case", SOLVE_CASES)
+def test_solve_default_weights_converged(gs, case):
+    (M,) = to_dev(gs(case, "M"))
+    reg = float(gs(case, "reg"))
+    r = ot.solve(M, reg=reg, tol=1e-9 if "f64" in case else 1e-6, max_iter=3000)
+    c = f"{case}/default"
+    t = 1e-7 if "f64" in case else 1e-4  # converged runs: the stop iteration may differ by one check
+    assert_plan(r.plan, gs(c, "plan"), t)
+    assert_scalar(r.value_linear, gs(c, "value_linear"), t)
+    ma, mb = r.marginals
+    assert_vec(ma, np.full(M.shape[0], 1.0 / M.shape[0]), 1e-5)
+    assert_vec(mb, np.full(M.shape[1], 1.0 / M.shape[1]), 1e-5)
+    r.sparse_plan, r.status, r.potentials  # attributes the reference test touches (test_solvers.py:125-128)
+
+
+def test_solve_errors():
+    M = torch.rand(8, 6, device=DEV, dtype=torch.float64)
+    with pytest.raises(NotImplementedError):
+        ot.solve(M, reg=1, reg_type="cryptic divergence")  # test_solvers.py:143-144
+    with pytest.raises(NotImplementedError):
+        ot.solve(M, reg=1, unbalanced=1, unbalanced_type="cryptic divergence")  # :139-140
+    with pytest.raises(NotImplementedError):
+        ot.solve(M)  # exact OT: outside the path
+    with pytest.raises((TypeError, ValueError)):
+        ot.solve(M.cpu(), reg=1.0)
+    with pytest.raises(TypeError):
+        ot.solve(M.cpu().numpy(), reg=1.0)
+
+
+@pytest.mark.parametrize("n,m,dtype", [(1024, 2048, torch.float32), (777, 1031, torch.float32),
+                                       (512, 640, torch.float64), (301, 1001, torch.float64)])
+@pytest.mark.parametrize("rt", ["KL", "entropy"])
+def test_solve_vs_oracle_larger(n, m, dtype, rt):
+    """Aligned (vector path) and ragged (scalar path) shapes against the oracle on seeded inputs."""
+    rng = np.random.RandomState(n + m)
+    npd = np.float32 if dtype == torch.float32 else np.float64
+    xs, xt = rng.randn(n, 2), rng.randn(m, 2) + 1.0
+    M = ((xs ** 2).sum(1)[:, None] + (xt ** 2).sum(1)[None, :] - 2 * xs @ xt.T).clip(0)
+    M = (M / M.max()).astype(npd)
+    a = rng.rand(n) + 0.1
+    b = rng.rand(m) + 0.1
+    a, b = (a / a.sum()).astype(npd), (b / b.sum()).astype(npd)
+    ref = sorc.solve(M, a, b, reg=0.1, reg_type=rt, max_iter=30, tol=0)
+    Mt, at, bt = to_dev(M, a, b)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        r = ot.solve(Mt, at, bt, reg=0.1, reg_type=rt, max_iter=30, tol=0)
+    tol = 1e-10 if dtype == torch.float64 else 1e-4
+    assert_plan(r.plan, ref["plan"], tol)
+    assert_scalar(r.value_linear, ref["value_linear"], tol)
+    assert_scalar(r.value, ref["value"], tol, scale=max(abs(ref["value"]), abs(ref["value_linear"])))
+
+
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+def test_empirical_divergence_and_solve_sample(gs, tag):
+    base = f"emp2_{tag}"
+    xs, xt, a, b = to_dev(*(gs(base, k) for k in ("xs", "xt", "a", "b")))
+    reg, its = float(gs(base, "reg")), int(gs(base, "its"))
+    tol = 1e-10 if tag == "f64" else 1e-4
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        D, lg = ot.bregman.empirical_sinkhorn_divergence(xs, xt, reg, a, b, numIterMax=its, stopThr=-1, isLazy=True,
+                                                         batchSize=32, log=True)
+        scale = abs(float(gs(base + "/div", "l_ab")))
+        assert_scalar(lg["sinkhorn_loss_ab"], gs(base + "/div", "l_ab"), tol)
+        assert_scalar(lg["sinkhorn_loss_a"], gs(base + "/div", "l_a"), tol)
+        assert_scalar(lg["sinkhorn_loss_b"], gs(base + "/div", "l_b"), tol)
+        assert_scalar(D, gs(base + "/div", "div"), tol, scale=scale)
+        D2 = ot.bregman.empirical_sinkhorn_divergence(xs, xt, reg, a, b, numIterMax=its, stopThr=-1, isLazy=True)
+        assert_scalar(D2, gs(base + "/div", "div"), tol, scale=scale)
+        # solve_sample, lazy
+        r = ot.solve_sample(xs, xt, a, b, reg=reg, lazy=True, max_iter=its, tol=-1, batch_size=32)
+        c = base + "/solve_sample"
+        assert r.plan is None and r.value is None
+        assert_scalar(r.value_linear, gs(c, "value_linear"), tol)
+        assert_vec(r.potentials[0], gs(c, "f"), tol)
+        assert_vec(r.potentials[1], gs(c, "g"), tol)
+        assert_plan(r.lazy_plan[3:9, 5:12], gs(c, "block"), tol)
+        # solve_sample, dense
+        r = ot.solve_sample(xs, xt, a, b, reg=reg, max_iter=its, tol=0)
+        c = base + "/solve_sample_dense"
+        assert_plan(r.plan, gs(c, "plan"), tol)
+        assert_scalar(r.value_linear, gs(c, "value_linear"), tol)
+        assert_scalar(r.value, gs(c, "value"), tol, scale=max(abs(float(gs(c, "value"))), abs(float(gs(c, "value_linear")))))
+    with pytest.raises(NotImplementedError):
+        ot.solve_sample(xs, xt, lazy=True)
+    with pytest.raises(NotImplementedError):
+        ot.solve_sample(xs, xt, reg=1.0, method="lowrank")

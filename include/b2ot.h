@@ -80,6 +80,13 @@ size_t b2ot_dense_workspace_bytes(int64_t n, int64_t m, int dtype, int max_iter,
 int b2ot_dense_create(b2ot_dense** handle, int mode, int dtype, int64_t n, int64_t m, int64_t ld, const void* K,
                       const void* a, const void* b, const void* logb, void* workspace, size_t workspace_bytes,
                       int max_iter, int check_every, double stop_thr, int variant, void* stream);
+/* switch a KNOPP handle (created with check_every = 1) to the UNBALANCED scaling iteration of
+ * ot.unbalanced.sinkhorn_knopp_unbalanced (ot/unbalanced/_sinkhorn.py:749-787): per iteration
+ * u = (a / K v)^fi_1 (inside the one fused sweep), v = (b / K^T u)^fi_2, fi = reg_m / (reg_m + reg) (:743-744);
+ * K is the caller's exp(-M/reg) * c (:736-740).  Guard: K^T u == 0 or nan / inf in u, v -> previous (u, v), status
+ * NUMERR (:760-772).  Error every iteration: (|u-uprev|_inf / max(|u|_inf, |uprev|_inf, 1) + same for v) / 2, stop
+ * when err < stop_thr (:774-787).  b2ot_dense_init then only loads (u0, v0).  Single device only. */
+int b2ot_dense_set_unbalanced(b2ot_dense* handle, double fi_1, double fi_2);
 int b2ot_dense_set_allreduce(b2ot_dense* handle, b2ot_allreduce_fn fn, void* ctx);
 /* enqueue: load the initial scalings (u0: n, v0: m; log-scalings in LOG mode) and run the
  * column-only pass that seeds the first v update (:629 / :881 of the reference loop) */

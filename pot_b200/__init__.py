@@ -14,10 +14,11 @@ from . import _lib
 
 _lib.load()  # fail loudly when the CUDA library is missing
 
-from . import batch, bregman, empirical, host, sharded, solvers, utils  # noqa: E402
+from . import batch, bregman, empirical, host, sharded, solvers, unbalanced, utils  # noqa: E402
 from .batch import solve_batch  # noqa: E402
 from .empirical import dist, empirical_sinkhorn, empirical_sinkhorn2, empirical_sinkhorn_divergence  # noqa: E402
 from .solvers import solve, solve_sample  # noqa: E402
+from .unbalanced import sinkhorn_unbalanced  # noqa: E402
 from .utils import LazyTensor, OTResult  # noqa: E402
 
 # the reference exposes the empirical solvers under ot.bregman as well
@@ -30,4 +31,4 @@ from .bregman import sinkhorn, sinkhorn2, sinkhorn_knopp, sinkhorn_log  # noqa: 
 __version__ = "0.1.0"
 __all__ = ["batch", "bregman", "empirical", "host", "sharded", "utils", "sinkhorn", "sinkhorn2", "sinkhorn_knopp",
            "sinkhorn_log", "solve_batch", "dist", "empirical_sinkhorn", "empirical_sinkhorn2",
-           "empirical_sinkhorn_divergence", "solve", "solve_sample", "solvers", "LazyTensor", "OTResult"]
+           "empirical_sinkhorn_divergence", "solve", "solve_sample", "solvers", "unbalanced", "sinkhorn_unbalanced", "LazyTensor", "OTResult"]

@@ -73,6 +73,10 @@ __device__ __forceinline__ float exp_elem(float d) {
 __device__ __forceinline__ double exp_elem(double d) { return exp(d); }
 __device__ __forceinline__ float log_t(float x) { return logf(x); }
 __device__ __forceinline__ double log_t(double x) { return log(x); }
+__device__ __forceinline__ float pow_t(float x, float y) { return powf(x, y); }
+__device__ __forceinline__ double pow_t(double x, double y) { return pow(x, y); }
+__device__ __forceinline__ float abs_t(float x) { return fabsf(x); }
+__device__ __forceinline__ double abs_t(double x) { return fabs(x); }
 __device__ __forceinline__ float max_t(float a, float b) { return fmaxf(a, b); }
 __device__ __forceinline__ double max_t(double a, double b) { return fmax(a, b); }
 __device__ __forceinline__ bool finite_t(float x) { return isfinite(x); }

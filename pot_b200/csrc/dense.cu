@@ -55,6 +55,8 @@ struct b2ot_dense {
   void* ar_ctx;
   b2ot_comm* comm;  // NVLink peer-memory exchange (takes precedence over the hook)
   SolveState* h_state;  // pinned host mirror for polls
+  int unbal;            // 1: unbalanced scaling iteration u = (a/Kv)^fi1, v = (b/K^T u)^fi2 (b2ot_dense_set_unbalanced)
+  double fi1, fi2;
 };
 
 static inline size_t esize(int dtype) { return dtype == B2OT_F64 ? 8 : 4; }
@@ -233,6 +235,7 @@ static int launch_fused(b2ot_dense* h) {
   p.W = h->W;
   p.stages = h->stages;
   p.use_hint = h->use_hint;
+  p.fi = h->unbal ? h->fi1 : 1.0;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(h->ncl * h->cs), 1, 1);
   cfg.blockDim = dim3(NW * 32, 1, 1);
@@ -300,6 +303,7 @@ static int launch_pp(b2ot_dense* h) {
   p.W = h->W;
   p.stages = h->stages;
   p.use_hint = h->use_hint;
+  p.fi = 1.0;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(h->ncl * h->cs), 1, 1);
   cfg.blockDim = dim3(PP_NH * PP_NTH, 1, 1);
@@ -529,8 +533,23 @@ extern "C" int b2ot_dense_create(b2ot_dense** handle, int mode, int dtype, int64
   return 0;
 }
 
+extern "C" int b2ot_dense_set_unbalanced(b2ot_dense* h, double fi_1, double fi_2) {
+  B2OT_REQUIRE(h != nullptr, "b2ot_dense_set_unbalanced: null handle");
+  B2OT_REQUIRE(h->mode == B2OT_MODE_KNOPP, "b2ot_dense_set_unbalanced: the handle must be in the scaling domain (KNOPP)");
+  B2OT_REQUIRE(h->check_every == 1, "b2ot_dense_set_unbalanced: the unbalanced error is evaluated every iteration; "
+                                    "create the handle with check_every = 1 (got %d)", h->check_every);
+  B2OT_REQUIRE(h->ar == nullptr && h->comm == nullptr, "b2ot_dense_set_unbalanced: row-sharded runs are not supported");
+  B2OT_REQUIRE(fi_1 > 0.0 && fi_1 <= 1.0 && fi_2 > 0.0 && fi_2 <= 1.0,
+               "b2ot_dense_set_unbalanced: exponents must be in (0, 1], got %g %g", fi_1, fi_2);
+  h->unbal = 1;
+  h->fi1 = fi_1;
+  h->fi2 = fi_2;
+  return 0;
+}
+
 extern "C" int b2ot_dense_set_allreduce(b2ot_dense* h, b2ot_allreduce_fn fn, void* ctx) {
   B2OT_REQUIRE(h != nullptr, "b2ot_dense_set_allreduce: null handle");
+  B2OT_REQUIRE(!h->unbal, "b2ot_dense_set_allreduce: the unbalanced iteration runs on a single device");
   h->ar = fn;
   h->ar_ctx = ctx;
   return 0;
@@ -538,6 +557,7 @@ extern "C" int b2ot_dense_set_allreduce(b2ot_dense* h, b2ot_allreduce_fn fn, voi
 
 extern "C" int b2ot_dense_set_comm(b2ot_dense* h, b2ot_comm* comm) {
   B2OT_REQUIRE(h != nullptr, "b2ot_dense_set_comm: null handle");
+  B2OT_REQUIRE(!h->unbal, "b2ot_dense_set_comm: the unbalanced iteration runs on a single device");
   if (comm != nullptr) {
     const size_t need = (size_t)(h->m + 1) * esize(h->dtype);
     B2OT_REQUIRE(comm->view.slot_bytes >= need, "b2ot_dense_set_comm: exchange slots hold %llu bytes, %zu needed",
@@ -582,6 +602,7 @@ static SplitParams split_params(const b2ot_dense* h, int u_slot_xor, int nsplit,
   p.u_slot_xor = u_slot_xor;
   p.nsplit = nsplit;
   p.expect_status = expect_status;
+  p.fi = h->unbal ? h->fi1 : 1.0;
   return p;
 }
 
@@ -678,6 +699,33 @@ static int launch_finalize(const b2ot_dense* h, int nsrc, int init) {
   return 0;
 }
 
+// unbalanced iteration: v = (b / K^T u)^fi2, guard, error, stop decision (single device only)
+template <typename T>
+static int launch_finalize_unbal(const b2ot_dense* h, int nsrc) {
+  FinUnbalParams p;
+  memset(&p, 0, sizeof(p));
+  p.src = h->partials;
+  p.src_ld = h->mp;
+  p.nsrc = nsrc;
+  p.b = h->b;
+  p.vring = h->vring;
+  p.uring = h->uring;
+  p.cbuf = h->cbuf;
+  p.n = h->n;
+  p.m = h->m;
+  p.mp = h->mp;
+  p.st = h->st;
+  p.blk = h->blk_err;
+  p.err_hist = h->err_hist;
+  p.max_iter = h->max_iter;
+  p.stop_thr = h->stop_thr;
+  p.fi = h->fi2;
+  const int blocks = std::min(h->fin_blocks, 160);  // 6 x blocks doubles of block scratch (1024 available)
+  B2OT_CUDA(launch_pdl(finalize_unbal_kernel<T>, dim3(blocks), dim3(256), 0, h->stream, p));
+  count_launch();
+  return 0;
+}
+
 // exact column log-sum-exp step: v_next = logb - LSE_i(K_ij + u_i)
 template <typename T>
 static int launch_exact_cols(const b2ot_dense* h, int expect_status, int advance_iter) {
@@ -723,6 +771,7 @@ static int dense_init_t(b2ot_dense* h, const void* u0, const void* v0) {
   B2OT_CUDA(cudaMemsetAsync(h->st, 0, 256, h->stream));
   B2OT_CUDA(cudaMemcpyAsync(h->uring, u0, (size_t)h->n * sizeof(T), cudaMemcpyDeviceToDevice, h->stream));
   B2OT_CUDA(cudaMemcpyAsync(h->vring, v0, (size_t)h->m * sizeof(T), cudaMemcpyDeviceToDevice, h->stream));
+  if (h->unbal) return 0;  // u-then-v order: the first sweep starts from v0, no seeding pass
   if (h->mode == B2OT_MODE_KNOPP) {
     int rc = launch_cols<T>(h, 0);  // c0 = K^T u0
     if (rc) return rc;
@@ -746,7 +795,7 @@ static int dense_iterate_t(b2ot_dense* h, int n_iters) {
       if (rc) return rc;
       nsrc = h->nsplit;
     }
-    int rc = launch_finalize<T>(h, nsrc, 0);
+    int rc = h->unbal ? launch_finalize_unbal<T>(h, nsrc) : launch_finalize<T>(h, nsrc, 0);
     if (rc) return rc;
   }
   return 0;
@@ -782,7 +831,10 @@ extern "C" int b2ot_dense_profile(b2ot_dense* h, int n_iters, float* sweep_ms_av
     }
     if (rc) break;
     B2OT_CUDA(cudaEventRecord(ev[2 * it + 1], h->stream));
-    rc = h->dtype == B2OT_F32 ? launch_finalize<float>(h, nsrc, 0) : launch_finalize<double>(h, nsrc, 0);
+    if (h->unbal)
+      rc = h->dtype == B2OT_F32 ? launch_finalize_unbal<float>(h, nsrc) : launch_finalize_unbal<double>(h, nsrc);
+    else
+      rc = h->dtype == B2OT_F32 ? launch_finalize<float>(h, nsrc, 0) : launch_finalize<double>(h, nsrc, 0);
   }
   if (rc == 0) {
     B2OT_CUDA(cudaEventRecord(ev[2 * n_iters], h->stream));

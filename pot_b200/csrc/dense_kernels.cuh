@@ -52,6 +52,7 @@ struct SweepParams {
   int W;                // columns per CTA slice (multiple of the vector width)
   int stages;
   int use_hint;         // L2 evict-first on the K stream (K much larger than L2)
+  double fi;            // KNOPP only: u = (a / Kv)^fi (unbalanced, ot/unbalanced/_sinkhorn.py:756); 1 = balanced
 };
 
 template <typename T, int VPT, int MODE, int NCW, int OCC>
@@ -385,7 +386,8 @@ __global__ void __launch_bounds__(NCW * 32, OCC) fused_sweep_kernel(const SweepP
       }
 #pragma unroll
       for (int r = 0; r < R; ++r) {
-        const T u = areg[r] / tot[r];
+        T u = areg[r] / tot[r];
+        if (p.fi != 1.0) u = pow_t(u, (T)p.fi);
         urow[r] = (r < rv) ? u : (T)0;
         if (crank == 0 && tid == r && r < rv) {
           unew[row0 + r] = u;
@@ -482,6 +484,7 @@ struct SplitParams {
   int u_slot_xor;   // cols kernel: 0 = current u, 1 = the u just produced
   int nsplit;       // row chunks of the column kernel
   int expect_status;
+  double fi;        // KNOPP rows kernel: u = (a / Kv)^fi (unbalanced); 1 = balanced
 };
 
 template <typename T, int MODE>
@@ -506,7 +509,8 @@ __global__ void __launch_bounds__(256) rows_kernel(const SplitParams p) {
     for (; j < p.m; j += 32) s0 = fma(kr[j], v[j], s0);
     const T tot = warp_sum((s0 + s1) + (s2 + s3));
     if (lane == 0) {
-      const T u = ai / tot;
+      T u = ai / tot;
+      if (p.fi != 1.0) u = pow_t(u, (T)p.fi);
       unew[row] = u;
       if (!finite_t(u)) atomicOr(&p.st->uflag, 1);
     }
@@ -797,6 +801,141 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
   st->next_flags = 0;
   st->uflag = 0;
   st->need_exact = 0;
+  st->ticket = 0;
+  __threadfence();
+}
+
+// ------------------------------------------------------------------------------------------------
+// Finalize of the UNBALANCED scaling iteration (ot/unbalanced/_sinkhorn.py:749-787).  The fused sweep has
+// produced u = (a / Kv)^fi_1 and the column sums c = K^T u; here v = (b / c)^fi_2, the guard (c == 0,
+// nan / inf in u or v -> keep the previous (u, v) and stop, :760-772), the error
+// err = (|u - uprev|_inf / max(|u|_inf, |uprev|_inf, 1) + |v - vprev|_inf / max(|v|_inf, |vprev|_inf, 1)) / 2
+// every iteration and the `<` stop test (:774-787).  No iteration skew: sweep i + this kernel = iteration i.
+// ------------------------------------------------------------------------------------------------
+struct FinUnbalParams {
+  const void* src;      // nsrc rows of column sums (stride src_ld)
+  long long src_ld;
+  int nsrc;
+  const void* b;
+  void* vring;          // 3 x mp
+  const void* uring;    // 2 x n
+  void* cbuf;
+  long long n, m, mp;
+  SolveState* st;
+  double* blk;          // [6][gridDim.x] block maxima: du, mu, mup, dv, mv, mvp
+  double* err_hist;
+  int max_iter;
+  double stop_thr;
+  double fi;            // fi_2
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256) finalize_unbal_kernel(const FinUnbalParams p) {
+  __shared__ double sred[6][8];
+  __shared__ int sflags;
+  __shared__ int s_last;
+  SolveState* st = p.st;
+  griddep_wait();
+  griddep_launch_dependents();
+  if (st->status != ST_RUNNING) return;
+  const int tid = threadIdx.x;
+  const int sel_v = st->sel_v, sel_u = st->sel_u;
+  const int nxt = (sel_v + 1) % 3;
+  const T* vcur = reinterpret_cast<const T*>(p.vring) + (long long)sel_v * p.mp;
+  T* vnext = reinterpret_cast<T*>(p.vring) + (long long)nxt * p.mp;
+  const T* ucur = reinterpret_cast<const T*>(p.uring) + (long long)sel_u * p.n;
+  const T* unew = reinterpret_cast<const T*>(p.uring) + (long long)(sel_u ^ 1) * p.n;
+  const T* src = reinterpret_cast<const T*>(p.src);
+  const T* b = reinterpret_cast<const T*>(p.b);
+  T* cbuf = reinterpret_cast<T*>(p.cbuf);
+  if (tid == 0) sflags = 0;
+  __syncthreads();
+
+  double mx[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  int flags = 0;
+  for (long long j = (long long)blockIdx.x * 256 + tid; j < p.m; j += (long long)gridDim.x * 256) {
+    T c = (T)0;
+    for (int q = 0; q < p.nsrc; ++q) c += __ldcg(&src[(long long)q * p.src_ld + j]);
+    T vn = b[j] / c;
+    if (p.fi != 1.0) vn = pow_t(vn, (T)p.fi);
+    const T vj = vcur[j];
+    if (c == (T)0) flags |= FLAG_CZERO;
+    if (!finite_t(vn)) flags |= FLAG_VBAD;
+    mx[3] = fmax(mx[3], (double)abs_t(vn - vj));
+    mx[4] = fmax(mx[4], (double)abs_t(vn));
+    mx[5] = fmax(mx[5], (double)abs_t(vj));
+    cbuf[j] = c;
+    vnext[j] = vn;
+  }
+  for (long long i = (long long)blockIdx.x * 256 + tid; i < p.n; i += (long long)gridDim.x * 256) {
+    const T un = unew[i], uo = ucur[i];
+    mx[0] = fmax(mx[0], (double)abs_t(un - uo));
+    mx[1] = fmax(mx[1], (double)abs_t(un));
+    mx[2] = fmax(mx[2], (double)abs_t(uo));
+  }
+  if (flags) atomicOr(&sflags, flags);
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    double x = mx[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x = fmax(x, __shfl_xor_sync(0xffffffffu, x, o));
+    if ((tid & 31) == 0) sred[k][tid >> 5] = x;
+  }
+  __syncthreads();
+  if (tid < 6) {
+    double x = 0.0;
+    for (int w = 0; w < 8; ++w) x = fmax(x, sred[tid][w]);
+    p.blk[(long long)tid * gridDim.x + blockIdx.x] = x;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    if (sflags) atomicOr(&st->next_flags, sflags);
+    __threadfence();
+    const unsigned int t = atomicAdd(&st->ticket, 1u);
+    s_last = (t == gridDim.x - 1) ? 1 : 0;
+  }
+  __syncthreads();
+  if (!s_last) return;
+
+  // ---- last block: maxima over the blocks, guard, error, stop decision ----
+  __threadfence();
+  if (tid < 6 * 32) {
+    const int k = tid >> 5;
+    double x = 0.0;
+    for (unsigned int i = tid & 31; i < gridDim.x; i += 32) x = fmax(x, __ldcg(&p.blk[(long long)k * gridDim.x + i]));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x = fmax(x, __shfl_xor_sync(0xffffffffu, x, o));
+    if ((tid & 31) == 0) sred[k][0] = x;
+  }
+  __syncthreads();
+  if (tid != 0) return;
+  const int nflags = atomicOr(&st->next_flags, 0);
+  const int uflag = atomicOr(&st->uflag, 0);
+  const int ii = st->iter;
+  if (nflags != 0 || uflag != 0) {
+    st->status = ST_NUMERR;  // previous (u, v) stay current
+    st->niter = ii;
+  } else {
+    st->sel_u = sel_u ^ 1;
+    st->sel_v = nxt;
+    const double err_u = sred[0][0] / fmax(fmax(sred[1][0], sred[2][0]), 1.0);
+    const double err_v = sred[3][0] / fmax(fmax(sred[4][0], sred[5][0]), 1.0);
+    const double err = 0.5 * (err_u + err_v);
+    p.err_hist[st->n_err] = err;
+    st->n_err += 1;
+    st->last_err = err;
+    if (err < p.stop_thr) {
+      st->status = ST_CONVERGED;
+      st->niter = ii;
+    } else if (ii + 1 >= p.max_iter) {
+      st->status = ST_MAXITER;
+      st->niter = ii;
+    } else {
+      st->iter = ii + 1;
+    }
+  }
+  st->next_flags = 0;
+  st->uflag = 0;
   st->ticket = 0;
   __threadfence();
 }

@@ -218,3 +218,126 @@ def test_empirical_divergence_and_solve_sample(gs, tag):
         ot.solve_sample(xs, xt, lazy=True)
     with pytest.raises(NotImplementedError):
         ot.solve_sample(xs, xt, reg=1.0, method="lowrank")
+
+
+# ---- unbalanced scaling-domain Sinkhorn ----
+UNB_CASES = [f"unb_{t}_{s}" for t in ("f64", "f32") for s in ("33x47", "128x160")]
+UNB_VARIANTS = {"scalar": dict(reg_m=1.0), "pair": dict(reg_m=(0.5, 2.0)), "semi": dict(reg_m=(float("inf"), 1.0)),
+                "entropy": dict(reg_m=1.0, reg_type="entropy")}
+
+
+@pytest.mark.parametrize("case", UNB_CASES)
+@pytest.mark.parametrize("variant", list(UNB_VARIANTS))
+def test_unbalanced_fixed_golden(gs, case, variant):
+    M, a, b = to_dev(gs(case, "M"), gs(case, "a"), gs(case, "b"))
+    reg, its, tol = float(gs(case, "reg")), int(gs(case, "its")), tol_of(case)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        P, lg = ot.unbalanced.sinkhorn_knopp_unbalanced(a, b, M, reg, numItermax=its, stopThr=0, log=True,
+                                                        **UNB_VARIANTS[variant])
+        P2 = ot.unbalanced.sinkhorn_knopp_unbalanced(a, b, M, reg, numItermax=its, stopThr=0, **UNB_VARIANTS[variant])
+    c = f"{case}/{variant}"
+    assert P.dtype == M.dtype and P.device == M.device
+    assert_plan(P, gs(c, "plan"), tol)
+    assert_plan(P2, gs(c, "plan"), tol)
+    assert_vec(lg["logu"], gs(c, "logu"), tol)
+    assert_vec(lg["logv"], gs(c, "logv"), tol)
+    assert_scalar(lg["cost"], gs(c, "cost"), tol)
+    assert_scalar(lg["total_cost"], gs(c, "total_cost"), tol,
+                  scale=max(abs(float(gs(c, "cost"))), abs(float(gs(c, "total_cost")))))
+    eref = np.asarray(gs(c, "err"), dtype=np.float64)
+    e = np.array([float(x) for x in lg["err"]])
+    assert e.shape == eref.shape
+    floor = 1e-13 if "f64" in case else 3e-7
+    assert np.all(np.abs(e - eref) <= 1e-3 * eref + floor), (e[-3:], eref[-3:])
+
+
+@pytest.mark.parametrize("case", UNB_CASES)
+def test_unbalanced_conv_c_warm_multib(gs, case):
+    M, a, b = to_dev(gs(case, "M"), gs(case, "a"), gs(case, "b"))
+    reg, its, tol = float(gs(case, "reg")), int(gs(case, "its")), tol_of(case)
+    P, lg = ot.unbalanced.sinkhorn_knopp_unbalanced(a, b, M, reg, 1.0, numItermax=5000,
+                                                    stopThr=1e-6 if "f32" in case else 1e-9, log=True)
+    nref = int(gs(f"{case}/conv", "nerr"))
+    if "f64" in case:
+        assert len(lg["err"]) == nref
+    else:
+        assert abs(len(lg["err"]) - nref) <= max(2, nref // 20)
+    assert_plan(P, gs(f"{case}/conv", "plan"), 1e-7 if "f64" in case else 1e-4)
+    c = f"{case}/c_warm"
+    cm, wu, wv = to_dev(gs(c, "c"), gs(c, "ws_u"), gs(c, "ws_v"))
+    P, lg = ot.unbalanced.sinkhorn_knopp_unbalanced(a, b, M, reg, 1.0, c=cm, warmstart=(wu, wv), numItermax=its,
+                                                    stopThr=0, log=True)
+    assert_plan(P, gs(c, "plan"), tol)
+    assert_scalar(lg["total_cost"], gs(c, "total_cost"), tol,
+                  scale=max(abs(float(gs(c, "cost"))), abs(float(gs(c, "total_cost")))))
+    c = f"{case}/multib"
+    (b2,) = to_dev(gs(c, "b2"))
+    L, lg = ot.unbalanced.sinkhorn_knopp_unbalanced(a, b2, M, reg, 1.0, numItermax=its, stopThr=0, log=True)
+    np.testing.assert_allclose(npf(L), gs(c, "loss"), rtol=tol)
+    assert_vec(lg["logu"], gs(c, "logu"), tol)
+    assert_vec(lg["logv"], gs(c, "logv"), tol)
+
+
+def test_unbalanced_guard(gs):
+    M, a, b = to_dev(gs("unb_guard", "M"), gs("unb_guard", "a"), gs("unb_guard", "b"))
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        P, lg = ot.unbalanced.sinkhorn_knopp_unbalanced(a, b, M, float(gs("unb_guard", "reg")), 1.0, numItermax=50,
+                                                        stopThr=0, log=True)
+    assert int(any("Numerical errors" in str(x.message) for x in w)) == int(gs("unb_guard", "warned"))
+    assert len(lg["err"]) == int(gs("unb_guard", "nerr"))
+    assert_vec(lg["logu"], gs("unb_guard", "logu"), 1e-10)  # back at the previous (initial) scalings
+    np.testing.assert_allclose(npf(P), gs("unb_guard", "plan"), rtol=1e-10, atol=0)  # K underflowed: plan is zero
+
+
+@pytest.mark.parametrize("case", SOLVE_CASES)
+def test_solve_unbalanced_golden(gs, case):
+    M, a, b = to_dev(gs(case, "M"), gs(case, "a"), gs(case, "b"))
+    reg, its, tol = float(gs(case, "reg")), int(gs(case, "its")), tol_of(case)
+    for utag, um in (("unb1", 1.0), ("unb_pair", (0.5, 2.0))):
+        r = ot.solve(M, a, b, reg=reg, unbalanced=um, max_iter=its, tol=0)
+        c = f"{case}/{utag}"
+        assert_plan(r.plan, gs(c, "plan"), tol)
+        assert_vec(r.potentials[0], gs(c, "f"), tol)
+        assert_vec(r.potentials[1], gs(c, "g"), tol)
+        assert_scalar(r.value_linear, gs(c, "value_linear"), tol)
+        assert_scalar(r.value, gs(c, "value"), tol,
+                      scale=max(abs(float(gs(c, "value"))), abs(float(gs(c, "value_linear")))))
+
+
+@pytest.mark.parametrize("n,m,dtype,variant", [(2048, 4096, torch.float32, "fused"), (1000, 1531, torch.float32, "split"),
+                                               (1024, 768, torch.float64, "fused"), (333, 1001, torch.float64, "split")])
+def test_unbalanced_vs_oracle_larger(n, m, dtype, variant):
+    """Fused-sweep shapes (aligned) and split-sweep shapes (ragged) against the oracle on seeded inputs."""
+    rng = np.random.RandomState(n + m)
+    npd = np.float32 if dtype == torch.float32 else np.float64
+    xs, xt = rng.randn(n, 2), rng.randn(m, 2) + 1.0
+    M = ((xs ** 2).sum(1)[:, None] + (xt ** 2).sum(1)[None, :] - 2 * xs @ xt.T).clip(0)
+    M = (M / M.max()).astype(npd)
+    a = rng.rand(n) + 0.1
+    b = rng.rand(m) + 0.1
+    a, b = (1.2 * a / a.sum()).astype(npd), (b / b.sum()).astype(npd)
+    Pr, lr = sorc.sinkhorn_knopp_unbalanced(a, b, M, 0.1, (1.0, 0.7), numItermax=25, stopThr=0, log=True)
+    Mt, at, bt = to_dev(M, a, b)
+    P, lg = ot.unbalanced.sinkhorn_knopp_unbalanced(at, bt, Mt, 0.1, (1.0, 0.7), numItermax=25, stopThr=0, log=True)
+    tol = 1e-10 if dtype == torch.float64 else 1e-4
+    assert_plan(P, Pr, tol)
+    assert_vec(lg["logu"], lr["logu"], tol)
+    assert_scalar(lg["total_cost"], lr["total_cost"], tol, scale=max(abs(lr["cost"]), abs(lr["total_cost"])))
+    assert len(lg["err"]) == 25
+
+
+def test_unbalanced_errors():
+    M = torch.rand(8, 6, device=DEV, dtype=torch.float64)
+    a = torch.full((8,), 0.125, device=DEV, dtype=torch.float64)
+    b = torch.full((6,), 1 / 6, device=DEV, dtype=torch.float64)
+    with pytest.raises(ValueError):
+        ot.sinkhorn_unbalanced(a, b, M, 1.0, 1.0, method="nope")
+    with pytest.raises(NotImplementedError):
+        ot.sinkhorn_unbalanced(a, b, M, 1.0, 1.0, method="sinkhorn_stabilized")
+    with pytest.raises(ValueError):
+        ot.unbalanced.sinkhorn_knopp_unbalanced(a, b, M, 1.0, (1.0, 2.0, 3.0))
+    P = ot.sinkhorn_unbalanced([], [], M, 1.0, 1.0)  # empty weights -> uniform (:706-709)
+    P2 = ot.sinkhorn_unbalanced(a, b, M, 1.0, 1.0)
+    assert torch.allclose(P, P2)

@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb2ot.so")
+# B2OT_LIB: load another build of the same library (A/B measurements of kernel variants); default = the in-tree build
+LIB_PATH = os.environ.get("B2OT_LIB") or os.path.join(_HERE, "libb2ot.so")
 
 F32, F64 = 0, 1
 MODE_KNOPP, MODE_LOG = 0, 1

@@ -43,6 +43,7 @@ struct __align__(16) SolveState {
 
 constexpr int MODE_KNOPP = 0;  // scaling domain
 constexpr int MODE_LOG = 1;    // log domain
+constexpr int MODE_UNBAL = 2;  // fused sweep only: scaling domain with the unbalanced row exponent u = (a / Kv)^fi
 
 constexpr int FLAG_CZERO = 1;
 constexpr int FLAG_VBAD = 2;
@@ -124,6 +125,27 @@ __device__ __forceinline__ float ex2_ftz(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+
+// Row exponent x^y of the unbalanced sweep (x = a / Kv > 0, 0 < y <= 1).  It sits on the serial path of every row
+// group of the fused sweep, where the accurate powf (~60 dependent instructions) costs 20 % of the sweep.  fp32: split
+// x = 2^e m, m in [1, 2): y log2 x = y e (two-float product, integer part peeled off exactly) + y lg2.approx(m), one
+// ex2.approx on an argument of magnitude <= 1.5, exact 2^ip scaling.  Relative error ~2e-7 typical, <= ~5e-7
+// (lg2.approx 2^-22 absolute on [1, 2), ex2.approx 2 ulp) -- the documented bound of powf itself is 4 ulp.
+// Zero, denormal, inf, nan, negative inputs take powf so that the numerical guard sees the same special values.
+__device__ __forceinline__ float pow_row(float x, float y) {
+  if (!(x >= 1.17549435e-38f && x <= 3.4028234e38f)) return powf(x, y);
+  const int xi = __float_as_int(x);
+  const float ef = (float)(((xi >> 23) & 0xff) - 127);
+  const float m = __int_as_float((xi & 0x007fffff) | 0x3f800000);
+  const float lm = lg2_ftz(m);
+  const float t_hi = y * ef;
+  const float t_lo = fmaf(y, ef, -t_hi);
+  const float ip = rintf(t_hi);
+  const float arg = (t_hi - ip) + fmaf(y, lm, t_lo);
+  const float r = ex2_ftz(arg);
+  return r * __int_as_float(((int)ip + 127) << 23);
+}
+__device__ __forceinline__ double pow_row(double x, double y) { return pow(x, y); }
 
 // ---- element access on the 16-byte vector types ----
 __device__ __forceinline__ float& elem(float4& v, int i) { return (&v.x)[i]; }

@@ -370,7 +370,11 @@ static int dispatch_launch_pp(b2ot_dense* h) {
 
 #define B2OT_DISPATCH_FUSED(FN, h)                                                   \
   do {                                                                               \
-    if ((h)->dtype == B2OT_F32 && (h)->mode == B2OT_MODE_KNOPP) {                    \
+    if ((h)->dtype == B2OT_F32 && (h)->mode == B2OT_MODE_KNOPP && (h)->unbal) {      \
+      B2OT_FUSED_CASES(FN, h, float, MODE_UNBAL)                                     \
+    } else if ((h)->mode == B2OT_MODE_KNOPP && (h)->unbal) {                         \
+      B2OT_FUSED_CASES(FN, h, double, MODE_UNBAL)                                    \
+    } else if ((h)->dtype == B2OT_F32 && (h)->mode == B2OT_MODE_KNOPP) {             \
       B2OT_FUSED_CASES(FN, h, float, MODE_KNOPP)                                     \
     } else if ((h)->dtype == B2OT_F32) {                                             \
       B2OT_FUSED_CASES(FN, h, float, MODE_LOG)                                       \
@@ -544,6 +548,8 @@ extern "C" int b2ot_dense_set_unbalanced(b2ot_dense* h, double fi_1, double fi_2
   h->unbal = 1;
   h->fi1 = fi_1;
   h->fi2 = fi_2;
+  // the unbalanced sweep is its own kernel instantiation: set its shared-memory attribute / cluster occupancy
+  if (h->variant == B2OT_VARIANT_FUSED) return dispatch_config_fused(h);
   return 0;
 }
 

@@ -52,7 +52,7 @@ struct SweepParams {
   int W;                // columns per CTA slice (multiple of the vector width)
   int stages;
   int use_hint;         // L2 evict-first on the K stream (K much larger than L2)
-  double fi;            // KNOPP only: u = (a / Kv)^fi (unbalanced, ot/unbalanced/_sinkhorn.py:756); 1 = balanced
+  double fi;            // MODE_UNBAL only: u = (a / Kv)^fi (ot/unbalanced/_sinkhorn.py:756)
 };
 
 template <typename T, int VPT, int MODE, int NCW, int OCC>
@@ -211,7 +211,7 @@ __global__ void __launch_bounds__(NCW * 32, OCC) fused_sweep_kernel(const SweepP
     T wcorr[R]; // LOG fp32: first-order correction of the rounded reference (1 elsewhere)
 #pragma unroll
     for (int r = 0; r < R; ++r) wcorr[r] = (T)1;
-    if (MODE == MODE_KNOPP) {
+    if (MODE != MODE_LOG) {
 #pragma unroll
       for (int r = 0; r < R; ++r) {
         T s0 = (T)0, s1 = (T)0;
@@ -371,7 +371,7 @@ __global__ void __launch_bounds__(NCW * 32, OCC) fused_sweep_kernel(const SweepP
     }
 
     T urow[R];  // KNOPP: u_i ; LOG: f_i (row-frame factor for this warp)
-    if (MODE == MODE_KNOPP) {
+    if (MODE != MODE_LOG) {
       T tot[R];
 #pragma unroll
       for (int r = 0; r < R; ++r) {
@@ -387,7 +387,9 @@ __global__ void __launch_bounds__(NCW * 32, OCC) fused_sweep_kernel(const SweepP
 #pragma unroll
       for (int r = 0; r < R; ++r) {
         T u = areg[r] / tot[r];
-        if (p.fi != 1.0) u = pow_t(u, (T)p.fi);
+        if constexpr (MODE == MODE_UNBAL) {  // unbalanced: u = (a / Kv)^fi_1 (ot/unbalanced/_sinkhorn.py:756)
+          if (p.fi != 1.0) u = pow_row(u, (T)p.fi);
+        }
         urow[r] = (r < rv) ? u : (T)0;
         if (crank == 0 && tid == r && r < rv) {
           unew[row0 + r] = u;
@@ -510,7 +512,7 @@ __global__ void __launch_bounds__(256) rows_kernel(const SplitParams p) {
     const T tot = warp_sum((s0 + s1) + (s2 + s3));
     if (lane == 0) {
       T u = ai / tot;
-      if (p.fi != 1.0) u = pow_t(u, (T)p.fi);
+      if (p.fi != 1.0) u = pow_row(u, (T)p.fi);
       unew[row] = u;
       if (!finite_t(u)) atomicOr(&p.st->uflag, 1);
     }

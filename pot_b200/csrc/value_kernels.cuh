@@ -44,6 +44,13 @@ template <typename T> __device__ __forceinline__ T eps16();
 template <> __device__ __forceinline__ float eps16<float>() { return 1e-16f; }
 template <> __device__ __forceinline__ double eps16<double>() { return 1e-16; }
 
+// log / divide of the REDUCED terms only (the plan itself uses the accurate exp): fp32 takes the MUFU forms
+// (lg2.approx * ln 2, rcp-based divide; ~1e-7 relative), far inside the 1e-4 budget of a sum of n m terms.
+__device__ __forceinline__ float log_red(float x) { return __logf(x); }
+__device__ __forceinline__ double log_red(double x) { return log(x); }
+__device__ __forceinline__ float div_red(float x, float y) { return __fdividef(x, y); }
+__device__ __forceinline__ double div_red(double x, double y) { return x / y; }
+
 template <typename T, int VEC>
 __device__ __forceinline__ void load_vec(const T* p, T (&x)[VEC]) {
   if constexpr (VEC == 1) {
@@ -113,7 +120,9 @@ __global__ void __launch_bounds__(256) plan_value_kernel(const PlanValueParams p
   for (long long i = blockIdx.x; i < p.n; i += gridDim.x) {
     const T ui = u[i];
     const T ai = (need_q && Cq == nullptr) ? a[i] : (T)0;
-    double rs = 0.0;
+    // per-row partial sums in T (at most m / 256 terms per thread), folded into the double accumulators once per row
+    T r_sum = (T)0, r_lin = (T)0, r_ent = (T)0, r_kl = (T)0;
+#pragma unroll(sizeof(T) == 4 ? 2 : 1)  // fp64 is FP64-pipe bound: unrolling only costs occupancy there
     for (long long j = (long long)threadIdx.x * VEC; j < p.m; j += 256LL * VEC) {
       T kx[VEC], mx[VEC], vx[VEC], qx[VEC], px[VEC];
       load_vec<T, VEC>(v + j, vx);
@@ -141,15 +150,18 @@ __global__ void __launch_bounds__(256) plan_value_kernel(const PlanValueParams p
         }
         const T g = (MODE == MODE_KNOPP) ? (ui * k) * vx[e] : exp_t((k + ui) + vx[e]);
         px[e] = g;
-        rs += (double)g;
-        if (p.terms & PV_LINEAR) s_lin += (double)(mx[e] * g);
-        if (p.terms & PV_ENTROPY) s_ent += (double)(g * log_t(g + eps16<T>()));
-        if (p.terms & PV_KL) s_kl += (double)(g * log_t(g / qx[e] + eps16<T>()));
+        r_sum += g;
+        if (p.terms & PV_LINEAR) r_lin = fma(mx[e], g, r_lin);
+        if (p.terms & PV_ENTROPY) r_ent = fma(g, log_red(g + eps16<T>()), r_ent);
+        if (p.terms & PV_KL) r_kl = fma(g, log_red(div_red(g, qx[e]) + eps16<T>()), r_kl);
       }
       if (out != nullptr) store_vec_stream<T, VEC>(out + i * p.ldO + j, px);
     }
+    s_lin += (double)r_lin;
+    s_ent += (double)r_ent;
+    s_kl += (double)r_kl;
     if (rowsum != nullptr) {  // block-uniform branch
-      const double t = block_sum_256(rs, sred);
+      const double t = block_sum_256((double)r_sum, sred);
       if (threadIdx.x == 0) rowsum[i] = (T)t;
     }
   }

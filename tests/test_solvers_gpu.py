@@ -248,7 +248,8 @@ def test_unbalanced_fixed_golden(gs, case, variant):
     eref = np.asarray(gs(c, "err"), dtype=np.float64)
     e = np.array([float(x) for x in lg["err"]])
     assert e.shape == eref.shape
-    floor = 1e-13 if "f64" in case else 3e-7
+    # err is a difference of successive iterates: in fp32 its noise floor is a few ulp of max|u| per iteration
+    floor = 1e-13 if "f64" in case else 1e-6
     assert np.all(np.abs(e - eref) <= 1e-3 * eref + floor), (e[-3:], eref[-3:])
 
 

@@ -5,10 +5,8 @@ mkdir -p gpurun_out
 python -m pytest tests/test_solvers_gpu.py -x -q -m gpu -k "unbalanced" > gpurun_out/r1h_unb_tests.log 2>&1; echo "unbalanced tests rc=$?" | tee -a gpurun_out/r1h_summary.log
 tail -3 gpurun_out/r1h_unb_tests.log
 for rep in 1 2 3; do
-  B2OT_LIB=$PWD/pot_b200/libb2ot_nopow.so python scripts/bench_unbalanced.py 65536 100 balanced_only >> gpurun_out/r1h_ab_nopow.jsonl 2>&1
   python scripts/bench_unbalanced.py 65536 100 >> gpurun_out/r1h_ab_pow.jsonl 2>&1
 done
-echo "--- nopow"; cat gpurun_out/r1h_ab_nopow.jsonl
 echo "--- pow"; cat gpurun_out/r1h_ab_pow.jsonl
 python scripts/bench_value.py 16384 > gpurun_out/r1h_bench_value.jsonl 2>&1
 cat gpurun_out/r1h_bench_value.jsonl

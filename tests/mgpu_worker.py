@@ -7,7 +7,8 @@ Every rank checks its own results and exits non-zero on a mismatch.  Checks (exc
   1. the stand-alone peer all-reduce against torch.distributed (sum / max, fp32 / fp64, 300 back-to-back calls);
   2. row-sharded sinkhorn_knopp / sinkhorn_log against the CPU oracle (fp64 1e-10, fp32 1e-4) and against the
      single-GPU solve (same niter, same err history), converged and fixed-iteration runs, ragged row split;
-  3. source-sharded empirical Sinkhorn against the oracle.
+  3. source-sharded empirical Sinkhorn against the oracle;
+  4. row-sharded ot.solve (plan rows, value, value_linear, potentials) against the solvers oracle.
 """
 import os
 import sys
@@ -23,8 +24,9 @@ sys.path.insert(0, ROOT)
 import pot_b200 as ot  # noqa: E402
 from oracle import sinkhorn_oracle as orc  # noqa: E402
 from pot_b200.comm import get_comm  # noqa: E402
+from oracle import solvers_oracle as sorc  # noqa: E402
 from pot_b200.sharded import (empirical_sinkhorn_sharded, shard_rows, sinkhorn_knopp_sharded,  # noqa: E402
-                              sinkhorn_log_sharded)
+                              sinkhorn_log_sharded, solve_sharded)
 
 
 def main():
@@ -98,6 +100,29 @@ def main():
                     check(torch.equal(v, v0), f"{exchange} {name} replicated v differs across ranks")
         if rank == 0:
             print(f"dense sharded ok ({exchange})", flush=True)
+
+    # ---- 4. row-sharded ot.solve: plan rows + all-reduced objective terms ----
+    for dtype, tol in ((np.float64, 1e-10), (np.float32, 1e-4)):
+        M, a, b = M64.astype(dtype), a64.astype(dtype), b64.astype(dtype)
+        for rt in ("KL", "entropy"):
+            ref = sorc.solve(M, a, b, reg=0.1, reg_type=rt, max_iter=50, tol=0)
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                res = solve_sharded(torch.as_tensor(M[r0:r1], device=dev), torch.as_tensor(a[r0:r1], device=dev),
+                                    torch.as_tensor(b, device=dev), reg=0.1, reg_type=rt, max_iter=50, tol=0,
+                                    group=group, n_total=n)
+            Gn = res.plan.cpu().numpy().astype(np.float64)
+            pr = ref["plan"][r0:r1].astype(np.float64)
+            err = np.abs(Gn - pr) / (np.abs(pr) + 1e-6 * ref["plan"].max())
+            check(err.max() < tol, f"solve_sharded {rt} {dtype.__name__} plan rel err {err.max():.3e}")
+            scale = max(abs(float(ref["value"])), abs(float(ref["value_linear"])))
+            check(abs(float(res.value_linear) - float(ref["value_linear"])) <= tol * scale, f"solve_sharded {rt} value_linear")
+            check(abs(float(res.value) - float(ref["value"])) <= tol * scale,
+                  f"solve_sharded {rt} {dtype.__name__} value {float(res.value)} vs {float(ref['value'])}")
+            eg = np.abs(res.potentials[1].cpu().numpy() - ref["potentials"][1]).max() / max(1.0, np.abs(ref["potentials"][1]).max())
+            check(eg < tol, f"solve_sharded {rt} potentials err {eg:.2e}")
+    if rank == 0:
+        print("solve sharded ok", flush=True)
 
     # ---- 3. empirical, source points sharded ----
     n, m, d = 301, 257, 5

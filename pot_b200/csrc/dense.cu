@@ -47,6 +47,7 @@ struct b2ot_dense {
   // fused sweep configuration
   int cs, ncl, stages, vpt, nw, occ, W, use_hint;
   int pp_vpt;  // > 0: fp32 log-domain sweeps run the ping-pong kernel with this many vectors per thread
+  int pp_occ;  // CTAs per SM of the ping-pong kernel (2: narrow slices, four independent halves per SM)
   size_t dyn_smem;
   // split sweep / column-only pass configuration
   int nsplit, nsplit_lse;
@@ -256,16 +257,18 @@ static int launch_fused(b2ot_dense* h) {
 }
 
 // ---- ping-pong log-domain sweep (fp32): configuration and launch ----
-template <int VPT>
+template <int VPT, int OCC>
 static int config_pp(b2ot_dense* h) {
   int stages = PP_SMAX;
-  while (stages > 2 && pp_smem_bytes(VPT, stages) > (size_t)(228 * 1024 - 4096)) --stages;
+  const size_t budget = OCC == 2 ? (size_t)(110 * 1024) : (size_t)(228 * 1024 - 4096);
+  while (stages > 2 && pp_smem_bytes(VPT, stages) > budget) --stages;
   const char* env = getenv("B2OT_PP_STAGES");
   if (env && atoi(env) >= 2 && atoi(env) <= stages) stages = atoi(env);
   h->stages = stages;
   h->dyn_smem = pp_smem_bytes(VPT, stages);
-  auto kern = log_pp_sweep_kernel<VPT>;
+  auto kern = log_pp_sweep_kernel<VPT, OCC>;
   B2OT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->dyn_smem));
+  if (h->cs > 8) B2OT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)h->cs, 1, 1);
   cfg.blockDim = dim3(PP_NH * PP_NTH, 1, 1);
@@ -287,7 +290,7 @@ static int config_pp(b2ot_dense* h) {
   h->ncl = (int)ncl;
   return 0;
 }
-template <int VPT>
+template <int VPT, int OCC>
 static int launch_pp(b2ot_dense* h) {
   SweepParams p;
   p.K = h->K;
@@ -318,15 +321,15 @@ static int launch_pp(b2ot_dense* h) {
   attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
   cfg.attrs = attr;
   cfg.numAttrs = 2;
-  B2OT_CUDA(cudaLaunchKernelEx(&cfg, log_pp_sweep_kernel<VPT>, p));
+  B2OT_CUDA(cudaLaunchKernelEx(&cfg, log_pp_sweep_kernel<VPT, OCC>, p));
   count_launch();
   return 0;
 }
 static int dispatch_config_pp(b2ot_dense* h) {
   switch (h->pp_vpt) {
-    case 4: return config_pp<4>(h);
-    case 8: return config_pp<8>(h);
-    case 16: return config_pp<16>(h);
+    case 4: return h->pp_occ == 2 ? config_pp<4, 2>(h) : config_pp<4, 1>(h);
+    case 8: return h->pp_occ == 2 ? config_pp<8, 2>(h) : config_pp<8, 1>(h);
+    case 16: return config_pp<16, 1>(h);
     default: break;
   }
   set_error("internal: bad ping-pong dispatch (vpt=%d)", h->pp_vpt);
@@ -334,9 +337,9 @@ static int dispatch_config_pp(b2ot_dense* h) {
 }
 static int dispatch_launch_pp(b2ot_dense* h) {
   switch (h->pp_vpt) {
-    case 4: return launch_pp<4>(h);
-    case 8: return launch_pp<8>(h);
-    case 16: return launch_pp<16>(h);
+    case 4: return h->pp_occ == 2 ? launch_pp<4, 2>(h) : launch_pp<4, 1>(h);
+    case 8: return h->pp_occ == 2 ? launch_pp<8, 2>(h) : launch_pp<8, 1>(h);
+    case 16: return launch_pp<16, 1>(h);
     default: break;
   }
   set_error("internal: bad ping-pong dispatch (vpt=%d)", h->pp_vpt);
@@ -443,11 +446,35 @@ static bool plan_fused(b2ot_dense* h) {
   if (envh) h->use_hint = atoi(envh) ? 1 : 0;
   // fp32 log domain: ping-pong schedule (two independent half-CTAs) when the slice is wide enough (B2OT_LOGPP=0: off)
   h->pp_vpt = 0;
+  h->pp_occ = 1;
   const char* envp = getenv("B2OT_LOGPP");
   const bool pp_on = !(envp && envp[0] == '0');
-  if (pp_on && h->mode == B2OT_MODE_LOG && h->dtype == B2OT_F32 && h->nw == 8 && h->occ == 1 && h->W >= 1024 &&
-      h->W <= pp_wcap(16)) {
+  const bool pp_cand = pp_on && h->mode == B2OT_MODE_LOG && h->dtype == B2OT_F32 && h->nw == 8 && h->occ == 1;
+  // Slice width of the ping-pong kernel.  Default: the narrowest cluster that gives slices of <= 4096 columns
+  // (8 vectors per thread, 126 registers), so that TWO CTAs = four independent halves fit on an SM
+  // (16384^2: 199 -> 187 us per sweep, 65536^2: 3.79 -> 3.48 ms; profiles/r01c_logpp_occ2.log).
+  // B2OT_PP_OCC=1 restores one CTA per SM with the widest slices; B2OT_PP_CLUSTER forces a cluster size.
+  const char* envo2 = getenv("B2OT_PP_OCC");
+  const bool want_occ2 = !(envo2 && atoi(envo2) == 1);
+  const char* envpc = getenv("B2OT_PP_CLUSTER");
+  int force_cs = 0;
+  if (envpc && atoi(envpc) >= 1 && atoi(envpc) <= CSMAX && (atoi(envpc) & (atoi(envpc) - 1)) == 0) force_cs = atoi(envpc);
+  if (pp_cand && (force_cs || (want_occ2 && h->m > pp_wcap(8)))) {
+    int cs = force_cs;
+    if (!cs) {
+      cs = 1;
+      while (cs < CSMAX && (h->m + cs - 1) / cs > pp_wcap(8)) cs *= 2;
+    }
+    long long w = (h->m + cs - 1) / cs;
+    w = (w + vec - 1) / vec * vec;
+    if (w >= 1024 && w <= pp_wcap(16) && (force_cs || w <= pp_wcap(8))) {
+      h->cs = cs;
+      h->W = (int)w;
+    }
+  }
+  if (pp_cand && h->W >= 1024 && h->W <= pp_wcap(16)) {
     h->pp_vpt = h->W <= pp_wcap(4) ? 4 : (h->W <= pp_wcap(8) ? 8 : 16);
+    if (want_occ2 && h->pp_vpt <= 8 && (h->m > pp_wcap(8) || force_cs)) h->pp_occ = 2;  // m <= 4096: one CTA with 4 stages is faster
   }
   return true;
 }

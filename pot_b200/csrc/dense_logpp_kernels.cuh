@@ -30,8 +30,9 @@ inline size_t pp_smem_bytes(int vpt, int stages) {
   return (size_t)(PP_NH * stages + 1) * pp_wcap(vpt) * sizeof(float);  // stage rings + the v slice
 }
 
-template <int VPT>
-__global__ void __launch_bounds__(PP_NH* PP_NTH, 1) log_pp_sweep_kernel(const SweepParams p) {
+// OCC = 2: two CTAs per SM (narrow slices, VPT <= 8): four independent halves per SM instead of two
+template <int VPT, int OCC = 1>
+__global__ void __launch_bounds__(PP_NH* PP_NTH, OCC) log_pp_sweep_kernel(const SweepParams p) {
   constexpr int WCAP = PP_NTH * VPT * 4;
   constexpr float L2E = 1.4426950408889634f;
 
@@ -61,7 +62,7 @@ __global__ void __launch_bounds__(PP_NH* PP_NTH, 1) log_pp_sweep_kernel(const Sw
   const float* const Kg = reinterpret_cast<const float*>(p.K);
   const uint32_t row_bytes = (uint32_t)wc * 4u;
   const uint64_t pol = p.use_hint ? l2_policy_evict_first() : 0ull;
-  const int nsrc = (int)csize * PP_NWH;             // warps of this half across the cluster (<= 32)
+  const int nsrc = (int)csize * PP_NWH;             // warps of this half across the cluster (<= 64)
   const uint32_t exch_bytes = (uint32_t)nsrc * 2u * 4u;
   float* const my_stage = stage_base + (size_t)hf * S * WCAP;
 
@@ -198,12 +199,23 @@ __global__ void __launch_bounds__(PP_NH* PP_NTH, 1) log_pp_sweep_kernel(const Sw
     }
     // every lane reads source warp (lane mod nsrc): all groups of nsrc lanes hold the same data, so log2(nsrc)
     // butterfly rounds leave the total in every lane
-    const int srcw = lane & (nsrc - 1);
-    const float ms = exch[hf][par][srcw][0];
-    const float sm = exch[hf][par][srcw][1];
+    // (clusters of 16 have 64 source warps: every lane then folds sources lane and lane + 32 first)
+    const int nl = nsrc < 32 ? nsrc : 32;
+    const int srcw = lane & (nl - 1);
+    float ms = exch[hf][par][srcw][0];
+    float sm = exch[hf][par][srcw][1];
+    if (nsrc > 32) {
+      const float ms2 = exch[hf][par][srcw + 32][0];
+      const float sm2 = exch[hf][par][srcw + 32][1];
+      const float mm = fmaxf(ms, ms2);
+      const float t1 = (ms != -CUDART_INF_F) ? sm * ex2_ftz((ms - mm) * L2E) : 0.f;
+      const float t2 = (ms2 != -CUDART_INF_F) ? sm2 * ex2_ftz((ms2 - mm) * L2E) : 0.f;
+      ms = mm;
+      sm = t1 + t2;
+    }
     const float M = warp_max_redux(ms);
     float Ssum = (ms != -CUDART_INF_F) ? sm * ex2_ftz((ms - M) * L2E) : 0.f;
-    for (int o = nsrc >> 1; o > 0; o >>= 1) Ssum += __shfl_xor_sync(0xffffffffu, Ssum, o);
+    for (int o = nl >> 1; o > 0; o >>= 1) Ssum += __shfl_xor_sync(0xffffffffu, Ssum, o);
     const float u = a_r - fmaf(lg2_ftz(Ssum), 0.6931471805599453f, M);
     const float ur = ex2_ftz((ref + u) * L2E) * corr;  // row-frame factor f_i for this warp's reference
     if (crank == 0 && th == 0) unew[g] = u;

@@ -12,7 +12,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import pot_b200 as ot  # noqa: E402
 from pot_b200 import _dense, _lib  # noqa: E402
 
-n = m = int(os.environ.get("N", 16384))
+n = int(os.environ.get("N", 16384))
+m = int(os.environ.get("M", n))
 reg, iters = 0.01, 500
 dev = torch.device("cuda:0")
 rng = np.random.RandomState(0)

@@ -1,5 +1,6 @@
 // Host driver + C ABI of the batched on-chip Sinkhorn solver (see include/b2ot.h, batch_kernels.cuh).
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "../../include/b2ot.h"
@@ -39,9 +40,9 @@ static bool batch_config(int mode, int dtype, long long n, long long m, BatchCfg
   return false;
 }
 
-template <typename T, int MODE, int CPL>
+template <typename T, int MODE, int CPL, int NTRIP = 0>
 static int launch_one(const BatchParams& p, const BatchCfg& c, cudaStream_t stream) {
-  auto kern = batch_solve_kernel<T, MODE, CPL>;
+  auto kern = batch_solve_kernel<T, MODE, CPL, NTRIP>;
   static thread_local size_t configured = 0;
   if (c.smem > configured) {
     B2OT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c.smem));
@@ -64,8 +65,31 @@ static int launch_one(const BatchParams& p, const BatchCfg& c, cudaStream_t stre
   return 0;
 }
 
+// Register-resident fast path (batch_kernels.cuh, NTRIP): full tiles only -- m == 32 cpl, n == cs * rpc and every
+// CTA's rows are a whole number (1 or 2) of trips of warps x rows-per-group.  B2OT_BATCH_REGTILE=0 turns it off.
+template <typename T>
+static int fast_trips(const BatchParams& p, const BatchCfg& c) {
+  static const bool on = [] {
+    const char* e = getenv("B2OT_BATCH_REGTILE");
+    return !(e && e[0] == '0');
+  }();
+  if (!on || (c.cpl != 4 && c.cpl != 8)) return 0;
+  if (p.m != c.cpl * 32 || (long long)c.cs * c.rpc != p.n) return 0;
+  const int nw = batch_threads(c.cpl) / 32;
+  const int rg = batch_rows_per_group(c.cpl * (int)(sizeof(T) / 4));
+  if (c.rpc % (nw * rg) != 0) return 0;
+  const int nt = c.rpc / (nw * rg);
+  if (nt < 1 || nt > 2 || nt * rg * c.cpl * (int)(sizeof(T) / 4) > 64) return 0;
+  return nt;
+}
+
 template <typename T, int MODE>
 static int launch_cpl(const BatchParams& p, const BatchCfg& c, cudaStream_t s) {
+  const int nt = fast_trips<T>(p, c);
+  if (nt == 1 && c.cpl == 4) return launch_one<T, MODE, 4, 1>(p, c, s);
+  if (nt == 2 && c.cpl == 4) return launch_one<T, MODE, 4, 2>(p, c, s);
+  if (nt == 1 && c.cpl == 8) return launch_one<T, MODE, 8, 1>(p, c, s);
+  if (nt == 2 && c.cpl == 8) return launch_one<T, MODE, 8, 2>(p, c, s);
   switch (c.cpl) {
     case 1: return launch_one<T, MODE, 1>(p, c, s);
     case 2: return launch_one<T, MODE, 2>(p, c, s);

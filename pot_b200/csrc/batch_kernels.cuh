@@ -93,9 +93,15 @@ __host__ __device__ inline BatchSmem batch_smem_layout(int rpc, int m, int mp, i
   return L;
 }
 
-template <typename T, int MODE, int CPL>
+// NTRIP > 0: register-resident fast path of the iteration loop.  Requires m == 32 CPL and exactly
+// NTRIP * warps * RG rows in every CTA (e.g. 256 x 256 fp32 on a cluster of 2: 128 rows = 2 trips of 16 warps x 4
+// rows): every thread keeps its NTRIP x RG x CPL (<= 64) tile values in registers for the whole solve, so an
+// iteration re-reads nothing from shared memory but the vectors, and the loop carries no bounds checks
+// (the generic loop spends 12 thread-instructions per element, ncu profiles/r01c_ncu_batch_256_v1.txt).
+template <typename T, int MODE, int CPL, int NTRIP = 0>
 __global__ void __launch_bounds__(batch_threads(CPL), 1) batch_solve_kernel(const BatchParams p) {
   constexpr int MP = CPL * 32;  // padded column count
+  constexpr bool FAST = NTRIP > 0;
   constexpr int BATCH_NT = batch_threads(CPL);
   constexpr int BATCH_NW = BATCH_NT / 32;
   constexpr int RG = batch_rows_per_group(CPL * (int)(sizeof(T) / 4));
@@ -325,6 +331,19 @@ __global__ void __launch_bounds__(batch_threads(CPL), 1) batch_solve_kernel(cons
   // ------------------------------------------------------------------------------------------
   // iterations
   // ------------------------------------------------------------------------------------------
+  constexpr int NTR = FAST ? NTRIP : 1;
+  T kr[NTR][RG][CPL];  // FAST: this thread's share of the tile, resident for the whole solve
+  if constexpr (FAST) {
+#pragma unroll
+    for (int t = 0; t < NTRIP; ++t) {
+#pragma unroll
+      for (int g = 0; g < RG; ++g) {
+        const int r = warp * RG + t * BATCH_NW * RG + g;
+#pragma unroll
+        for (int c = 0; c < CPL; ++c) kr[t][g][c] = Ks[(size_t)r * MP + lane + 32 * c];
+      }
+    }
+  }
   for (int it = p.it_begin; it < p.it_end; ++it) {
     T greg[CPL], acc[CPL];
 #pragma unroll
@@ -332,7 +351,10 @@ __global__ void __launch_bounds__(batch_threads(CPL), 1) batch_solve_kernel(cons
       greg[c] = gs[lane + 32 * c];
       acc[c] = (T)0;
     }
-    for (int rb = warp * RG; rb < rows; rb += BATCH_NW * RG) {
+    const int n_trips = FAST ? NTRIP : (rows - warp * RG + BATCH_NW * RG - 1) / (BATCH_NW * RG);
+#pragma unroll(FAST ? NTRIP : 1)
+    for (int trip = 0; trip < n_trips; ++trip) {
+      const int rb = warp * RG + trip * BATCH_NW * RG;
       T k[RG][CPL];
 #pragma unroll
       for (int g = 0; g < RG; ++g) {
@@ -340,7 +362,10 @@ __global__ void __launch_bounds__(batch_threads(CPL), 1) batch_solve_kernel(cons
 #pragma unroll
         for (int c = 0; c < CPL; ++c) {
           const int col = lane + 32 * c;
-          k[g][c] = (r < rows && col < m) ? Ks[(size_t)r * m + col] : (MODE == MODE_LOG ? neg_inf<T>() : (T)0);
+          if constexpr (FAST)
+            k[g][c] = kr[trip < NTR ? trip : 0][g][c];
+          else
+            k[g][c] = (r < rows && col < m) ? Ks[(size_t)r * m + col] : (MODE == MODE_LOG ? neg_inf<T>() : (T)0);
         }
       }
       if (MODE == MODE_KNOPP) {
@@ -357,14 +382,31 @@ __global__ void __launch_bounds__(batch_threads(CPL), 1) batch_solve_kernel(cons
 #pragma unroll
           for (int g = 0; g < RG; ++g) s[g] += __shfl_xor_sync(0xffffffffu, s[g], o);
         }
+        if constexpr (FAST) {
+          // lane l finishes row (l mod RG) only (one division per lane instead of RG), then the RG scalings are
+          // broadcast back with one shuffle each
+          const int gsel = lane & (RG - 1);
+          T ssel = s[0];
 #pragma unroll
-        for (int g = 0; g < RG; ++g) {
-          const int r = rb + g;
-          if (r < rows) {
-            const T f = as[r] / s[g];
-            if (lane == 0) fs[r] = f;
+          for (int g = 1; g < RG; ++g) ssel = (gsel == g) ? s[g] : ssel;
+          const T fsel = as[rb + gsel] / ssel;
+          if (lane < RG) fs[rb + lane] = fsel;
+#pragma unroll
+          for (int g = 0; g < RG; ++g) {
+            const T f = __shfl_sync(0xffffffffu, fsel, g);
 #pragma unroll
             for (int c = 0; c < CPL; ++c) acc[c] = fma(k[g][c], f, acc[c]);
+          }
+        } else {
+#pragma unroll
+          for (int g = 0; g < RG; ++g) {
+            const int r = rb + g;
+            if (r < rows) {
+              const T f = as[r] / s[g];
+              if (lane == 0) fs[r] = f;
+#pragma unroll
+              for (int c = 0; c < CPL; ++c) acc[c] = fma(k[g][c], f, acc[c]);
+            }
           }
         }
       } else {
@@ -388,10 +430,21 @@ __global__ void __launch_bounds__(batch_threads(CPL), 1) batch_solve_kernel(cons
         for (int g = 0; g < RG; ++g) {
           const T ref = (mx[g] == neg_inf<T>()) ? (T)0 : mx[g];
           T s0 = (T)0;
+          if constexpr (FAST && sizeof(T) == 4) {
+            // e = 2^(x log2e - rnd(ref log2e)): one FFMA + MUFU.EX2 per element; the rounding of ref log2e is a
+            // common factor of the row, divided back out of s and of the row factor below (corr)
+            const float nref = -(float)ref * 1.4426950408889634f;
 #pragma unroll
-          for (int c = 0; c < CPL; ++c) {
-            k[g][c] = exp_elem(k[g][c] - ref);
-            s0 += k[g][c];
+            for (int c = 0; c < CPL; ++c) {
+              k[g][c] = ex2_ftz(fmaf((float)k[g][c], 1.4426950408889634f, nref));
+              s0 += k[g][c];
+            }
+          } else {
+#pragma unroll
+            for (int c = 0; c < CPL; ++c) {
+              k[g][c] = exp_elem(k[g][c] - ref);
+              s0 += k[g][c];
+            }
           }
           s[g] = s0;
           mx[g] = ref;
@@ -401,15 +454,40 @@ __global__ void __launch_bounds__(batch_threads(CPL), 1) batch_solve_kernel(cons
 #pragma unroll
           for (int g = 0; g < RG; ++g) s[g] += __shfl_xor_sync(0xffffffffu, s[g], o);
         }
+        if constexpr (FAST) {
+          const int gsel = lane & (RG - 1);
+          T ssel = s[0], msel = mx[0];
 #pragma unroll
-        for (int g = 0; g < RG; ++g) {
-          const int r = rb + g;
-          if (r < rows) {
-            const T ls = log_t(s[g]);
-            if (lane == 0) fs[r] = las[r] - (mx[g] + ls);   // u_i = log a_i - LSE_j(K_ij + v_j)
-            const T w = exp_t(las[r] - ls);                 // a_i / s_i
+          for (int g = 1; g < RG; ++g) {
+            ssel = (gsel == g) ? s[g] : ssel;
+            msel = (gsel == g) ? mx[g] : msel;
+          }
+          T corr = (T)1;
+          if constexpr (sizeof(T) == 4) {
+            const float nref = -(float)msel * 1.4426950408889634f;
+            corr = (T)(1.f - fmaf((float)msel, 1.4426950408889634f, nref) * 0.6931471805599453f);
+          }
+          const T la = las[rb + gsel];
+          const T ls = log_t(ssel * corr);
+          if (lane < RG) fs[rb + lane] = la - (msel + ls);    // u_i = log a_i - LSE_j(K_ij + v_j)
+          const T wsel = exp_t(la - ls) * corr;               // a_i / s_i in this row's exponent frame
+#pragma unroll
+          for (int g = 0; g < RG; ++g) {
+            const T w = __shfl_sync(0xffffffffu, wsel, g);
 #pragma unroll
             for (int c = 0; c < CPL; ++c) acc[c] = fma(k[g][c], w, acc[c]);
+          }
+        } else {
+#pragma unroll
+          for (int g = 0; g < RG; ++g) {
+            const int r = rb + g;
+            if (r < rows) {
+              const T ls = log_t(s[g]);
+              if (lane == 0) fs[r] = las[r] - (mx[g] + ls);   // u_i = log a_i - LSE_j(K_ij + v_j)
+              const T w = exp_t(las[r] - ls);                 // a_i / s_i
+#pragma unroll
+              for (int c = 0; c < CPL; ++c) acc[c] = fma(k[g][c], w, acc[c]);
+            }
           }
         }
       }

@@ -110,6 +110,7 @@ __global__ void __launch_bounds__(batch_threads(CPL), 1) batch_solve_kernel(cons
   __shared__ double red[BATCH_NWMAX][2];
   __shared__ __align__(16) double cl_red[BATCH_CSMAX][2];
   __shared__ int s_flag;
+  __shared__ __align__(8) uint64_t xbar[2];  // per-parity mbarriers of the per-iteration column exchange
 
   if (p.expect_running && p.st->status != ST_RUNNING) return;  // sticky stop, uniform over the grid
 
@@ -189,7 +190,16 @@ __global__ void __launch_bounds__(batch_threads(CPL), 1) batch_solve_kernel(cons
     }
   }
   __syncthreads();
-  if (csize > 1) cluster_sync_all();  // peers' shared memory is live before the first DSMEM store
+  if (csize > 1) {
+    if (tid == 0) {
+      mbar_init(&xbar[0], 1);
+      mbar_init(&xbar[1], 1);
+      fence_mbar_init();
+    }
+    __syncthreads();
+    cluster_sync_all();  // peers' shared memory and barriers are live before the first DSMEM store
+  }
+  uint32_t xph[2] = {0u, 0u};  // phase parity of xbar[0], xbar[1]
 
   int par = 0;
 
@@ -239,14 +249,22 @@ __global__ void __launch_bounds__(batch_threads(CPL), 1) batch_solve_kernel(cons
         fn(j, tot);
       }
     } else {
+      // One-sided exchange: every CTA puts its column totals into slot `crank` of every CTA's buffer with st.async,
+      // the byte count completes the receiver's mbarrier -- no cluster barrier, no membar per iteration.  Buffer `par`
+      // is rewritten two exchanges later; a peer can only send that far ahead after it has received this CTA's next
+      // exchange, which every thread here issues after the __syncthreads that follows the reads below.
       const uint32_t mine_addr = smem_u32(xch + (size_t)(par * CSX + crank) * MP);
+      const uint32_t bar_addr = smem_u32(&xbar[par]);
+      if (tid == 0) mbar_arrive_expect_tx(&xbar[par], (uint32_t)(csize * (uint32_t)m * sizeof(T)));
       for (int j = tid; j < m; j += BATCH_NT) {
         T tot = (T)0;
 #pragma unroll 4
         for (int w = 0; w < BATCH_NW; ++w) tot += part[w * MP + j];
-        for (uint32_t q = 0; q < csize; ++q) st_cluster(mapa_u32(mine_addr + (uint32_t)(j * sizeof(T)), q), tot);
+        for (uint32_t q = 0; q < csize; ++q)
+          st_async_1(mapa_u32(mine_addr + (uint32_t)(j * sizeof(T)), q), tot, mapa_u32(bar_addr, q));
       }
-      cluster_sync_all();
+      mbar_wait(&xbar[par], xph[par]);
+      xph[par] ^= 1u;
       for (int j = tid; j < m; j += BATCH_NT) {
         T tot = (T)0;
         for (uint32_t q = 0; q < csize; ++q) tot += xch[(size_t)(par * CSX + q) * MP + j];

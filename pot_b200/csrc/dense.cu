@@ -3,7 +3,10 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
+#include <mutex>
 #include <new>
+#include <tuple>
 #include <vector>
 
 #include "../../include/b2ot.h"
@@ -26,6 +29,55 @@ void set_error(const char* fmt, ...) {
 std::atomic<unsigned long long>& launch_counter() {
   static std::atomic<unsigned long long> c{0};
   return c;
+}
+
+static std::mutex g_pin_mu;
+static std::vector<void*> g_pin_free;
+void* pinned_acquire(size_t bytes) {
+  if (bytes > kPinnedBlock) return nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_pin_mu);
+    if (!g_pin_free.empty()) {
+      void* p = g_pin_free.back();
+      g_pin_free.pop_back();
+      return p;
+    }
+  }
+  void* p = nullptr;
+  if (cudaMallocHost(&p, kPinnedBlock) != cudaSuccess) return nullptr;
+  return p;
+}
+void pinned_release(void* p) {
+  if (p == nullptr) return;
+  std::lock_guard<std::mutex> lk(g_pin_mu);
+  if (g_pin_free.size() < 64)
+    g_pin_free.push_back(p);
+  else
+    cudaFreeHost(p);
+}
+
+// cudaOccupancyMaxActiveClusters takes ~1 ms: cache its answer per (kernel, device, cluster size, shared memory)
+static std::mutex g_occ_mu;
+static std::map<std::tuple<const void*, int, int, size_t>, int> g_occ_cache;
+template <typename Kern>
+static int cached_max_clusters(Kern kern, const cudaLaunchConfig_t* cfg, int cs, int* out) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const auto key = std::make_tuple((const void*)kern, dev, cs, (size_t)cfg->dynamicSmemBytes);
+  {
+    std::lock_guard<std::mutex> lk(g_occ_mu);
+    auto it = g_occ_cache.find(key);
+    if (it != g_occ_cache.end()) {
+      *out = it->second;
+      return 0;
+    }
+  }
+  int maxcl = 0;
+  B2OT_CUDA(cudaOccupancyMaxActiveClusters(&maxcl, kern, cfg));
+  std::lock_guard<std::mutex> lk(g_occ_mu);
+  g_occ_cache[key] = maxcl;
+  *out = maxcl;
+  return 0;
 }
 
 }  // namespace b2ot
@@ -56,10 +108,14 @@ struct b2ot_dense {
   void* ar_ctx;
   b2ot_comm* comm;  // NVLink peer-memory exchange (takes precedence over the hook)
   SolveState* h_state;  // pinned host mirror for polls
+  cudaGraphExec_t gexec;  // graph of kGraphIters iterations (single-device solves), built at the first iterate call
+  int graph_state;        // 0 not built, 1 ready, -1 unavailable
+  int graph_launches;     // kernels per replay
   int unbal;            // 1: unbalanced scaling iteration u = (a/Kv)^fi1, v = (b/K^T u)^fi2 (b2ot_dense_set_unbalanced)
   double fi1, fi2;
 };
 
+static void drop_graph(b2ot_dense* h);
 static inline size_t esize(int dtype) { return dtype == B2OT_F64 ? 8 : 4; }
 static inline long long padded_m(long long m) { return (m + 1 + 31) / 32 * 32; }  // room for the flag slot
 
@@ -209,7 +265,7 @@ static int config_fused(b2ot_dense* h) {
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   int maxcl = 0;
-  B2OT_CUDA(cudaOccupancyMaxActiveClusters(&maxcl, kern, &cfg));
+  if (int rc_occ = cached_max_clusters(kern, &cfg, h->cs, &maxcl)) return rc_occ;
   B2OT_REQUIRE(maxcl >= 1, "fused sweep: no cluster of size %d fits on this device", h->cs);
   const long long NG = (h->n + R - 1) / R;
   long long ncl = std::min<long long>(maxcl, std::max<long long>(NG, 1));
@@ -281,7 +337,7 @@ static int config_pp(b2ot_dense* h) {
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   int maxcl = 0;
-  B2OT_CUDA(cudaOccupancyMaxActiveClusters(&maxcl, kern, &cfg));
+  if (int rc_occ = cached_max_clusters(kern, &cfg, h->cs, &maxcl)) return rc_occ;
   B2OT_REQUIRE(maxcl >= 1, "ping-pong sweep: no cluster of size %d fits on this device", h->cs);
   long long ncl = std::min<long long>(maxcl, std::max<long long>((h->n + PP_NH - 1) / PP_NH, 1));
   const char* envc = getenv("B2OT_CLUSTERS");
@@ -555,7 +611,8 @@ extern "C" int b2ot_dense_create(b2ot_dense** handle, int mode, int dtype, int64
       h->variant = B2OT_VARIANT_SPLIT;
     }
   }
-  if (cudaMallocHost((void**)&h->h_state, sizeof(SolveState)) != cudaSuccess) {
+  h->h_state = (SolveState*)pinned_acquire(sizeof(SolveState));
+  if (h->h_state == nullptr) {
     delete h;
     set_error("b2ot_dense_create: cudaMallocHost failed");
     return -2;
@@ -572,6 +629,7 @@ extern "C" int b2ot_dense_set_unbalanced(b2ot_dense* h, double fi_1, double fi_2
   B2OT_REQUIRE(h->ar == nullptr && h->comm == nullptr, "b2ot_dense_set_unbalanced: row-sharded runs are not supported");
   B2OT_REQUIRE(fi_1 > 0.0 && fi_1 <= 1.0 && fi_2 > 0.0 && fi_2 <= 1.0,
                "b2ot_dense_set_unbalanced: exponents must be in (0, 1], got %g %g", fi_1, fi_2);
+  drop_graph(h);
   h->unbal = 1;
   h->fi1 = fi_1;
   h->fi2 = fi_2;
@@ -614,7 +672,8 @@ extern "C" int b2ot_dense_info(const b2ot_dense* h, int* variant, int* cluster_s
 
 extern "C" int b2ot_dense_destroy(b2ot_dense* h) {
   if (h == nullptr) return 0;
-  if (h->h_state) cudaFreeHost(h->h_state);
+  pinned_release(h->h_state);
+  if (h->gexec) cudaGraphExecDestroy(h->gexec);
   delete h;
   return 0;
 }
@@ -814,7 +873,7 @@ static int dense_init_t(b2ot_dense* h, const void* u0, const void* v0) {
 }
 
 template <typename T>
-static int dense_iterate_t(b2ot_dense* h, int n_iters) {
+static int enqueue_iterations(b2ot_dense* h, int n_iters) {
   for (int it = 0; it < n_iters; ++it) {
     int nsrc;
     if (h->variant == B2OT_VARIANT_FUSED) {
@@ -832,6 +891,70 @@ static int dense_iterate_t(b2ot_dense* h, int n_iters) {
     if (rc) return rc;
   }
   return 0;
+}
+
+// CUDA graph of kGraphIters iterations (sweep + finalize pairs, programmatic-dependent-launch edges included):
+// every kernel parameter of a solve is fixed at creation and the whole state lives in device memory, so the same
+// graph replays for the entire solve.  Small problems are launch-bound (1000 x 1000 fp64: 21.5 us per iteration with
+// two cudaLaunchKernelEx calls, the kernels themselves need a fraction of that); replaying a graph costs one launch
+// per kGraphIters iterations.  Single device only (the NCCL hook is host code, the peer exchange carries a sequence
+// number in its parameters).  B2OT_GRAPH=0 turns it off; any capture error falls back to plain launches.
+static const int kGraphIters = 10;
+static bool graphs_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("B2OT_GRAPH");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+static void drop_graph(b2ot_dense* h) {
+  if (h->gexec) cudaGraphExecDestroy(h->gexec);
+  h->gexec = nullptr;
+  h->graph_state = 0;
+}
+template <typename T>
+static void build_graph(b2ot_dense* h) {
+  h->graph_state = -1;
+  cudaStream_t cap = nullptr;
+  if (cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking) != cudaSuccess) {
+    cudaGetLastError();
+    return;
+  }
+  const cudaStream_t user = h->stream;
+  const unsigned long long before = launch_counter().load();
+  cudaGraph_t graph = nullptr;
+  bool ok = cudaStreamBeginCapture(cap, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+  if (ok) {
+    h->stream = cap;
+    const int rc = enqueue_iterations<T>(h, kGraphIters);
+    h->stream = user;
+    const cudaError_t e = cudaStreamEndCapture(cap, &graph);
+    ok = (rc == 0) && (e == cudaSuccess) && graph != nullptr;
+  }
+  const unsigned long long after = launch_counter().load();
+  launch_counter().fetch_sub(after - before);  // nothing was launched while capturing
+  if (ok && cudaGraphInstantiate(&h->gexec, graph, 0) == cudaSuccess) {
+    h->graph_state = 1;
+    h->graph_launches = (int)(after - before);
+  } else {
+    h->gexec = nullptr;
+    cudaGetLastError();  // clear the sticky-free error of the failed capture; plain launches take over
+  }
+  if (graph) cudaGraphDestroy(graph);
+  cudaStreamDestroy(cap);
+}
+
+template <typename T>
+static int dense_iterate_t(b2ot_dense* h, int n_iters) {
+  if (graphs_enabled() && h->ar == nullptr && h->comm == nullptr && n_iters >= kGraphIters) {
+    if (h->graph_state == 0) build_graph<T>(h);
+    while (h->graph_state == 1 && n_iters >= kGraphIters) {
+      B2OT_CUDA(cudaGraphLaunch(h->gexec, h->stream));
+      count_launch(h->graph_launches);
+      n_iters -= kGraphIters;
+    }
+  }
+  return enqueue_iterations<T>(h, n_iters);
 }
 
 extern "C" int b2ot_dense_init(b2ot_dense* h, const void* u0, const void* v0) {

@@ -391,7 +391,9 @@ extern "C" int b2ot_emp_create(b2ot_emp** handle, int dtype, int64_t n, int64_t 
   h->fin_blocks_f = (int)std::max<long long>(1, std::min<long long>((n + 255) / 256, 1024));
   h->fin_blocks_g = (int)std::max<long long>(1, std::min<long long>((m + 255) / 256, 1024));
   (void)sm_count;
-  if (cudaMallocHost((void**)&h->h_state, sizeof(EmpState)) != cudaSuccess) {
+  static_assert(sizeof(EmpState) <= kPinnedBlock, "EmpState must fit a pinned pool block");
+  h->h_state = (EmpState*)pinned_acquire(sizeof(EmpState));
+  if (h->h_state == nullptr) {
     delete h;
     set_error("b2ot_emp_create: cudaMallocHost failed");
     return -2;
@@ -420,7 +422,7 @@ extern "C" int b2ot_emp_set_comm(b2ot_emp* h, b2ot_comm* comm) {
 
 extern "C" int b2ot_emp_destroy(b2ot_emp* h) {
   if (h == nullptr) return 0;
-  if (h->h_state) cudaFreeHost(h->h_state);
+  pinned_release(h->h_state);
   delete h;
   return 0;
 }

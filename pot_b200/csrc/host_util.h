@@ -45,6 +45,12 @@ inline void count_launch(int n = 1) { launch_counter().fetch_add((unsigned long 
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// Small pinned host blocks (the mirrors of the device status words that polls copy into): cudaMallocHost /
+// cudaFreeHost cost ~1 ms + ~0.5 ms per solve, so released blocks are kept on a free list (defined in dense.cu).
+constexpr size_t kPinnedBlock = 1024;
+void* pinned_acquire(size_t bytes);   // nullptr on failure; bytes <= kPinnedBlock
+void pinned_release(void* p);
+
 // Programmatic dependent launch of the per-iteration kernels (B2OT_PDL=0 turns it off): the kernel may start while
 // the previous kernel of the stream is still finishing; it blocks in griddepcontrol.wait before touching its results.
 inline bool pdl_enabled() {

@@ -197,15 +197,18 @@ def ours(args):
     # ---- synthetic inputs: this rank's row block of M, built on the device in row chunks ----
     xs, xt = point_clouds(n, m)
     xs_d, xt_d = torch.from_numpy(xs[r0:r1]).to(dev), torch.from_numpy(xt).to(dev)
-    yy = (xt_d * xt_d).sum(1)
     Mdev = torch.empty((nloc, m), dtype=torch.float32, device=dev)
     chunk = max(1, (512 << 20) // (4 * m))
     mx = torch.zeros((), dtype=torch.float32, device=dev)
+    scratch = torch.empty(lib.b2ot_dist_scratch_bytes(min(chunk, nloc), m, _lib.F32), dtype=torch.uint8, device=dev)
     for c0 in range(0, nloc, chunk):
         c1 = min(nloc, c0 + chunk)
         blk = Mdev[c0:c1]
-        torch.mm(xs_d[c0:c1], xt_d.t(), out=blk)
-        blk.mul_(-2.0).add_((xs_d[c0:c1] * xs_d[c0:c1]).sum(1)[:, None]).add_(yy[None, :]).clamp_(min=0)
+        xb = xs_d[c0:c1]
+        # squared-euclidean cost block straight into M (the library's own ot.dist kernel, clamped at 0)
+        _lib.check(lib.b2ot_dist(_lib.F32, xb.data_ptr(), xt_d.data_ptr(), c1 - c0, m, xb.shape[1], xb.stride(0),
+                                 xt_d.stride(0), _lib.METRIC_SQEUCLIDEAN, blk.data_ptr(), blk.stride(0),
+                                 scratch.data_ptr(), _dense.stream_ptr(dev)), "b2ot_dist")
         mx = torch.maximum(mx, blk.max())
     if world > 1:
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)

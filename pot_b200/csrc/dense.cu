@@ -783,10 +783,15 @@ static int launch_finalize(const b2ot_dense* h, int nsrc, int init) {
   p.check_every = h->check_every;
   p.stop_thr = h->stop_thr;
   p.init = init;
+  int blocks = h->fin_blocks;
+  if (!p.use_comm && p.nsrc >= 16 && h->m <= 32768) {  // small problem: spread the partial-row walk over 8 warps
+    p.qsplit = 1;
+    blocks = (int)std::min<long long>((h->m + 31) / 32, 1024);
+  }
   if (h->mode == B2OT_MODE_KNOPP)
-    B2OT_CUDA(launch_pdl(finalize_kernel<T, MODE_KNOPP>, dim3(h->fin_blocks), dim3(256), 0, h->stream, p));
+    B2OT_CUDA(launch_pdl(finalize_kernel<T, MODE_KNOPP>, dim3(blocks), dim3(256), 0, h->stream, p));
   else
-    B2OT_CUDA(launch_pdl(finalize_kernel<T, MODE_LOG>, dim3(h->fin_blocks), dim3(256), 0, h->stream, p));
+    B2OT_CUDA(launch_pdl(finalize_kernel<T, MODE_LOG>, dim3(blocks), dim3(256), 0, h->stream, p));
   count_launch();
   return 0;
 }
@@ -812,7 +817,11 @@ static int launch_finalize_unbal(const b2ot_dense* h, int nsrc) {
   p.max_iter = h->max_iter;
   p.stop_thr = h->stop_thr;
   p.fi = h->fi2;
-  const int blocks = std::min(h->fin_blocks, 160);  // 6 x blocks doubles of block scratch (1024 available)
+  int blocks = std::min(h->fin_blocks, 160);  // 6 x blocks doubles of block scratch (1024 available)
+  if (nsrc >= 16 && h->m <= 32768) {
+    p.qsplit = 1;
+    blocks = (int)std::min<long long>((h->m + 31) / 32, 160);
+  }
   B2OT_CUDA(launch_pdl(finalize_unbal_kernel<T>, dim3(blocks), dim3(256), 0, h->stream, p));
   count_launch();
   return 0;

@@ -678,6 +678,7 @@ struct FinParams {
   int max_iter, check_every;
   double stop_thr;
   int init;             // KNOPP seeding pass: only v0 = b / (K^T u0) and its guard flags
+  int qsplit;           // 1: blocks of 32 columns x 8 warps over the partial rows (small m, many partial rows)
 };
 
 template <typename T, int MODE>
@@ -707,9 +708,7 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
 
   double e2 = 0.0;
   int flags = 0;
-  for (long long j = (long long)blockIdx.x * 256 + tid; j < p.m; j += (long long)gridDim.x * 256) {
-    T c = (T)0;
-    for (int q = 0; q < p.nsrc; ++q) c += __ldcg(&src[(long long)q * p.src_ld + j]);
+  auto column = [&](long long j, T c) {
     const T bj = b[j];
     const T vj = vcur[j];
     T vn;
@@ -727,6 +726,34 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
     }
     cbuf[j] = c;
     vnext[j] = vn;
+  };
+  if (!p.qsplit) {
+    for (long long j = (long long)blockIdx.x * 256 + tid; j < p.m; j += (long long)gridDim.x * 256) {
+      T c = (T)0;
+      for (int q = 0; q < p.nsrc; ++q) c += __ldcg(&src[(long long)q * p.src_ld + j]);
+      column(j, c);
+    }
+  } else {
+    // Small problems: few columns, many partial rows (one per sweep cluster, up to NPMAX).  A block takes 32 columns;
+    // warp w sums the partial rows q = w, w + 8, ... (coalesced 32-column loads, 8 chains of L2 latency instead of one
+    // thread walking all rows: that serial walk made this kernel ~10 us at n = m = 1000), warp 0 combines the eight
+    // partial sums in a fixed order and finishes the columns.
+    __shared__ T sq[8][33];
+    const int lane = tid & 31, qw = tid >> 5;
+    for (long long j0 = (long long)blockIdx.x * 32; j0 < p.m; j0 += (long long)gridDim.x * 32) {
+      const long long j = j0 + lane;
+      T part = (T)0;
+      if (j < p.m)
+        for (int q = qw; q < p.nsrc; q += 8) part += __ldcg(&src[(long long)q * p.src_ld + j]);
+      sq[qw][lane] = part;
+      __syncthreads();
+      if (qw == 0 && j < p.m) {
+        const T c = ((sq[0][lane] + sq[1][lane]) + (sq[2][lane] + sq[3][lane])) +
+                    ((sq[4][lane] + sq[5][lane]) + (sq[6][lane] + sq[7][lane]));
+        column(j, c);
+      }
+      __syncthreads();
+    }
   }
   sred[tid] = e2;
   if (flags) atomicOr(&sflags, flags);
@@ -829,6 +856,7 @@ struct FinUnbalParams {
   int max_iter;
   double stop_thr;
   double fi;            // fi_2
+  int qsplit;           // 1: blocks of 32 columns x 8 warps over the partial rows (small m, many partial rows)
 };
 
 template <typename T>
@@ -855,9 +883,7 @@ __global__ void __launch_bounds__(256) finalize_unbal_kernel(const FinUnbalParam
 
   double mx[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
   int flags = 0;
-  for (long long j = (long long)blockIdx.x * 256 + tid; j < p.m; j += (long long)gridDim.x * 256) {
-    T c = (T)0;
-    for (int q = 0; q < p.nsrc; ++q) c += __ldcg(&src[(long long)q * p.src_ld + j]);
+  auto column = [&](long long j, T c) {
     T vn = b[j] / c;
     if (p.fi != 1.0) vn = pow_t(vn, (T)p.fi);
     const T vj = vcur[j];
@@ -868,6 +894,30 @@ __global__ void __launch_bounds__(256) finalize_unbal_kernel(const FinUnbalParam
     mx[5] = fmax(mx[5], (double)abs_t(vj));
     cbuf[j] = c;
     vnext[j] = vn;
+  };
+  if (!p.qsplit) {
+    for (long long j = (long long)blockIdx.x * 256 + tid; j < p.m; j += (long long)gridDim.x * 256) {
+      T c = (T)0;
+      for (int q = 0; q < p.nsrc; ++q) c += __ldcg(&src[(long long)q * p.src_ld + j]);
+      column(j, c);
+    }
+  } else {  // small problems: 32 columns per block, 8 warps over the partial rows (see finalize_kernel)
+    __shared__ T sq[8][33];
+    const int lane = tid & 31, qw = tid >> 5;
+    for (long long j0 = (long long)blockIdx.x * 32; j0 < p.m; j0 += (long long)gridDim.x * 32) {
+      const long long j = j0 + lane;
+      T part = (T)0;
+      if (j < p.m)
+        for (int q = qw; q < p.nsrc; q += 8) part += __ldcg(&src[(long long)q * p.src_ld + j]);
+      sq[qw][lane] = part;
+      __syncthreads();
+      if (qw == 0 && j < p.m) {
+        const T c = ((sq[0][lane] + sq[1][lane]) + (sq[2][lane] + sq[3][lane])) +
+                    ((sq[4][lane] + sq[5][lane]) + (sq[6][lane] + sq[7][lane]));
+        column(j, c);
+      }
+      __syncthreads();
+    }
   }
   for (long long i = (long long)blockIdx.x * 256 + tid; i < p.n; i += (long long)gridDim.x * 256) {
     const T un = unew[i], uo = ucur[i];

@@ -85,3 +85,17 @@ with warnings.catch_warnings():
         G1 = ot.sinkhorn(a1, a1, M1, 0.05, numItermax=its, stopThr=0)
         t1 = tsync()
         print(f"config 1 (1000^2 fp64, {its} its): wall {1e3 * (t1 - t0):.2f} ms = {its / (t1 - t0):.0f} it/s", flush=True)
+
+# ---- per-kernel split at config 1 (sweep alone vs whole iteration, CUDA events on the launch stream) ----
+K1 = _dense.cost_transform(M1, 0.05, "kexp")
+s1 = _dense.DenseSolver("knopp", K1, a1, a1, None, max_iter=100000, check_every=10, stop_thr=0.0)
+s1.init(a1.clone(), a1.clone())
+s1.iterate(20)
+torch.cuda.synchronize()
+sw, itms = s1.profile(200)
+t0 = tsync()
+s1.iterate(1000)
+t1 = tsync()
+print(f"config 1 kernels: sweep {1e3 * sw:.2f} us, iteration (events around every launch) {1e3 * itms:.2f} us, "
+      f"1000 graph-replayed iterations {1e3 * (t1 - t0):.2f} ms, info {s1.info()}", flush=True)
+s1.close()

@@ -1,0 +1,14 @@
+#!/bin/bash
+# round 1, session u (8 GPUs): parity worker on 8 ranks, headline bench at N = 8 (peer, with e2e) and N = 4, configs 4 and 5 at N = 8
+mkdir -p gpurun_out
+nvidia-smi -L | wc -l
+TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
+timeout 300 $TR --nproc-per-node 8 --master-port 29521 tests/mgpu_worker.py > gpurun_out/r1u_mgpu8_worker.log 2>&1
+echo "worker8 exit $?" | tee -a gpurun_out/r1u_mgpu8_worker.log
+grep -v "^\*\*\*\|OMP_NUM" gpurun_out/r1u_mgpu8_worker.log | tail -8
+timeout 400 $TR --nproc-per-node 8 --master-port 29522 bench.py --gpus 8 --steps 200 --warmup 20 --exchange peer > gpurun_out/r1u_bench_n8_peer.json 2> gpurun_out/r1u_bench_n8_peer.err
+echo "bench n=8 peer exit $?"; grep '^{' gpurun_out/r1u_bench_n8_peer.json | cut -c1-200; tail -2 gpurun_out/r1u_bench_n8_peer.err
+timeout 300 $TR --nproc-per-node 4 --master-port 29524 bench.py --gpus 4 --steps 200 --warmup 20 --exchange peer --no-e2e > gpurun_out/r1u_bench_n4_peer.json 2> gpurun_out/r1u_bench_n4_peer.err
+echo "bench n=4 peer exit $?"; grep '^{' gpurun_out/r1u_bench_n4_peer.json | cut -c1-200
+timeout 400 $TR --nproc-per-node 8 --master-port 29525 scripts/bench_configs45.py > gpurun_out/r1u_configs45_n8.jsonl 2> gpurun_out/r1u_configs45_n8.err
+echo "configs45 exit $?"; grep '^{' gpurun_out/r1u_configs45_n8.jsonl | cut -c1-700; tail -3 gpurun_out/r1u_configs45_n8.err

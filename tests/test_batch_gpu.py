@@ -95,9 +95,13 @@ def _problem(B, n, m, dtype, seed=0, d=2):
 
 SHAPES = [(3, 7, 5), (4, 33, 47), (2, 128, 96), (3, 64, 300), (2, 60, 1000), (2, 256, 256), (2, 300, 280),
           (1, 150, 480)]
+# full tiles: the register-resident fast path of batch_solve_kernel (NTRIP = 1 / 2, 4 and 8 columns per lane, clusters
+# of 1 to 8 CTAs), and near misses that must fall back to the generic loop
+FAST_SHAPES = [(3, 64, 256), (2, 128, 256), (5, 256, 256), (2, 512, 256), (3, 64, 128), (2, 128, 128),
+               (2, 256, 128), (2, 32, 256), (2, 255, 256), (2, 256, 255), (2, 192, 256)]
 
 
-@pytest.mark.parametrize("shape", SHAPES)
+@pytest.mark.parametrize("shape", SHAPES + FAST_SHAPES)
 @pytest.mark.parametrize("dtype", [np.float64, np.float32])
 @pytest.mark.parametrize("solver", ["log_sinkhorn", "sinkhorn"])
 def test_solve_batch_vs_oracle(shape, dtype, solver):
@@ -238,3 +242,23 @@ def test_config5_shape_properties():
         assert torch.equal(r2.plan, r.plan[10:20])
         ref = orc.solve_batch(M[:2].cpu().numpy(), 0.1, max_iter=100, tol=0, solver=solver)
         close(r.plan[:2], ref["plan"], 1e-4, "plan")
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("solver", ["log_sinkhorn", "sinkhorn"])
+def test_fast_path_converged_and_kl(dtype, solver):
+    """Full-tile problems (register-resident fast path) with the batch-wide stop test active (state travels through
+    the potentials between launches) and the KL value epilogue: n_iter and results against the oracle."""
+    B, n, m = 6, 256, 256
+    M, a, b = _problem(B, n, m, dtype, seed=11)
+    tol_stop = 1e-6 if dtype == np.float64 else 1e-4
+    ref = orc.solve_batch(M, 0.2, a, b, max_iter=500, tol=tol_stop, solver=solver, reg_type="kl")
+    r = ot.solve_batch(dev(M), 0.2, dev(a), dev(b), max_iter=500, tol=tol_stop, solver=solver, reg_type="kl")
+    if dtype == np.float64:
+        assert r.log["n_iter"] == ref["n_iter"], (r.log["n_iter"], ref["n_iter"])
+        tol = tol_of(dtype)
+    else:  # fp32: the error can cross the threshold one check (10 iterations) earlier or later
+        assert abs(r.log["n_iter"] - ref["n_iter"]) <= 10, (r.log["n_iter"], ref["n_iter"])
+        tol = 1e-3 if r.log["n_iter"] != ref["n_iter"] else tol_of(dtype)
+    close(r.plan, ref["plan"], tol, "plan")
+    close(r.value, ref["value"], 10 * tol, "value")

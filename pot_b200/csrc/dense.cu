@@ -139,6 +139,15 @@ template <typename T, int OP>
 static int launch_cost_transform(const void* M, void* out, long long n, long long m, long long ldM, long long ldO,
                                  double reg, cudaStream_t s) {
   if (n <= 0 || m <= 0) return 0;
+  constexpr int VEC = Vec<T>::N;
+  if (m % VEC == 0 && ldM % VEC == 0 && ldO % VEC == 0 && ((uintptr_t)M % 16) == 0 && ((uintptr_t)out % 16) == 0) {
+    const long long nv = m / VEC;
+    const unsigned gx = (unsigned)std::min<long long>((nv + 255) / 256, 32);
+    const unsigned gy = (unsigned)std::max<long long>(1, std::min<long long>((n + 1) / 2, (148 * 16) / gx));
+    cost_transform_vec_kernel<T, OP><<<dim3(gx, gy), 256, 0, s>>>((const T*)M, (T*)out, n, m, ldM, ldO, (T)reg);
+    B2OT_CHECK_LAUNCH();
+    return 0;
+  }
   dim3 grid((unsigned)std::min<long long>(n, 1 << 20), (unsigned)((m + 1023) / 1024));
   cost_transform_kernel<T, OP><<<grid, 256, 0, s>>>((const T*)M, (T*)out, n, m, ldM, ldO, (T)reg);
   B2OT_CHECK_LAUNCH();
@@ -161,6 +170,21 @@ template <typename T>
 static int launch_plan(int mode, const void* K, const void* u, const void* v, void* out, long long n, long long m,
                        long long ldK, long long ldO, cudaStream_t s) {
   if (n <= 0 || m <= 0) return 0;
+  constexpr int VEC = Vec<T>::N;
+  if (m % VEC == 0 && ldK % VEC == 0 && ldO % VEC == 0 && ((uintptr_t)K % 16) == 0 && ((uintptr_t)out % 16) == 0 &&
+      ((uintptr_t)v % 16) == 0) {
+    const long long nv = m / VEC;
+    const unsigned gx = (unsigned)std::min<long long>((nv + 255) / 256, 32);
+    const unsigned gy = (unsigned)std::max<long long>(1, std::min<long long>((n + 1) / 2, (148 * 16) / gx));
+    if (mode == B2OT_MODE_KNOPP)
+      plan_vec_kernel<T, MODE_KNOPP><<<dim3(gx, gy), 256, 0, s>>>((const T*)K, (const T*)u, (const T*)v, (T*)out, n, m,
+                                                                 ldK, ldO);
+    else
+      plan_vec_kernel<T, MODE_LOG><<<dim3(gx, gy), 256, 0, s>>>((const T*)K, (const T*)u, (const T*)v, (T*)out, n, m,
+                                                               ldK, ldO);
+    B2OT_CHECK_LAUNCH();
+    return 0;
+  }
   dim3 grid((unsigned)std::min<long long>(n, 1 << 20), (unsigned)((m + 1023) / 1024));
   if (mode == B2OT_MODE_KNOPP)
     plan_kernel<T, MODE_KNOPP><<<grid, 256, 0, s>>>((const T*)K, (const T*)u, (const T*)v, (T*)out, n, m, ldK, ldO);

@@ -1038,6 +1038,72 @@ __global__ void __launch_bounds__(256) cost_transform_kernel(const T* __restrict
   }
 }
 
+// 16-byte vector variants (rows and leading dimensions multiples of the vector width, 16-byte aligned bases): the scalar
+// kernels above reach 55 % (transform) / 78 % (plan) of the HBM rate at 65536^2; two rows per trip keep >= 2 vector loads
+// in flight per thread.  In-place transforms stay safe: every element is read and written by the same thread.
+template <typename T, int OP>
+__global__ void __launch_bounds__(256) cost_transform_vec_kernel(const T* M, T* out, long long n, long long m,
+                                                                 long long ldM, long long ldO, T reg) {
+  using V = typename Vec<T>::type;
+  constexpr int VEC = Vec<T>::N;
+  const long long nv = m / VEC;
+  auto f = [&](const V& x) {
+    V y;
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) elem(y, e) = (OP == 0) ? exp_t(elem(x, e) / (-reg)) : (-elem(x, e)) / reg;
+    return y;
+  };
+  for (long long i = blockIdx.y; i < n; i += 2LL * gridDim.y) {
+    const long long i2 = i + gridDim.y;
+    const V* r0 = reinterpret_cast<const V*>(M + i * ldM);
+    V* o0 = reinterpret_cast<V*>(out + i * ldO);
+    const V* r1 = reinterpret_cast<const V*>(M + (i2 < n ? i2 : i) * ldM);
+    V* o1 = reinterpret_cast<V*>(out + (i2 < n ? i2 : i) * ldO);
+    for (long long j = (long long)blockIdx.x * 256 + threadIdx.x; j < nv; j += (long long)gridDim.x * 256) {
+      const V x0 = __ldcs(r0 + j);
+      if (i2 < n) {
+        const V x1 = __ldcs(r1 + j);
+        __stcs(o0 + j, f(x0));
+        __stcs(o1 + j, f(x1));
+      } else {
+        __stcs(o0 + j, f(x0));
+      }
+    }
+  }
+}
+
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256) plan_vec_kernel(const T* __restrict__ K, const T* __restrict__ u,
+                                                       const T* __restrict__ v, T* __restrict__ out, long long n,
+                                                       long long m, long long ldK, long long ldO) {
+  using V = typename Vec<T>::type;
+  constexpr int VEC = Vec<T>::N;
+  const long long nv = m / VEC;
+  for (long long i = blockIdx.y; i < n; i += 2LL * gridDim.y) {
+    const long long i2 = i + gridDim.y;
+    const bool two = i2 < n;
+    const T u0 = u[i], u1 = u[two ? i2 : i];
+    const V* r0 = reinterpret_cast<const V*>(K + i * ldK);
+    const V* r1 = reinterpret_cast<const V*>(K + (two ? i2 : i) * ldK);
+    V* o0 = reinterpret_cast<V*>(out + i * ldO);
+    V* o1 = reinterpret_cast<V*>(out + (two ? i2 : i) * ldO);
+    for (long long j = (long long)blockIdx.x * 256 + threadIdx.x; j < nv; j += (long long)gridDim.x * 256) {
+      const V vv = *reinterpret_cast<const V*>(v + j * VEC);
+      const V x0 = __ldcs(r0 + j);
+      V x1 = x0;
+      if (two) x1 = __ldcs(r1 + j);
+      V y0, y1;
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) {
+        elem(y0, e) = (MODE == MODE_KNOPP) ? (u0 * elem(x0, e)) * elem(vv, e) : exp_t((elem(x0, e) + u0) + elem(vv, e));
+        elem(y1, e) = (MODE == MODE_KNOPP) ? (u1 * elem(x1, e)) * elem(vv, e) : exp_t((elem(x1, e) + u1) + elem(vv, e));
+      }
+      __stcs(o0 + j, y0);
+      if (two) __stcs(o1 + j, y1);
+    }
+  }
+}
+
 template <typename T, int MODE>
 __global__ void __launch_bounds__(256) plan_kernel(const T* __restrict__ K, const T* __restrict__ u,
                                                    const T* __restrict__ v, T* __restrict__ out, long long n,

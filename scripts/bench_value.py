@@ -65,6 +65,11 @@ def main():
                           "GBps": round(2 * s * n * m / ms_plan / 1e6, 1)}))
         print(json.dumps({"kernel": "loss_kernel", "dtype": str(dtype), "ms": round(ms_loss, 4),
                           "GBps": round(2 * s * n * m / ms_loss / 1e6, 1)}))
+        for op in ("kexp", "negscale"):
+            ms_t = timeit(lambda: _dense.cost_transform(M, 0.1, op))
+            print(json.dumps({"kernel": f"cost_transform ({op})", "dtype": str(dtype), "ms": round(ms_t, 4),
+                              "GBps": round(2 * s * n * m / ms_t / 1e6, 1),
+                              "frac_of_measured_hbm": round(2 * s * n * m / ms_t / 1e6 / peak, 3)}))
         del M, Mr
 
 

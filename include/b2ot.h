@@ -87,6 +87,25 @@ int b2ot_dense_create(b2ot_dense** handle, int mode, int dtype, int64_t n, int64
  * NUMERR (:760-772).  Error every iteration: (|u-uprev|_inf / max(|u|_inf, |uprev|_inf, 1) + same for v) / 2, stop
  * when err < stop_thr (:774-787).  b2ot_dense_init then only loads (u0, v0).  Single device only. */
 int b2ot_dense_set_unbalanced(b2ot_dense* handle, double fi_1, double fi_2);
+/* switch a KNOPP handle to the STABILIZED scaling iteration of ot.bregman.sinkhorn_stabilized
+ * (ot/bregman/_sinkhorn.py:1105-1382).  The iteration itself is the balanced one (v = b / K^T u, u = a / K v, :1270-1271,
+ * one fused sweep) on K = exp(-(M - alpha - beta)/reg) (:1256-1258), which the caller builds before b2ot_dense_create.
+ * In addition, every iteration, on the device and without a host round trip:
+ *   - the finalize kernel tests max|u|, max|v| against tau (:1274);
+ *   - when exceeded, gated kernels fold the scalings into the potentials (alpha_r += log u, beta_r += log v, i.e.
+ *     alpha += reg log u, :1281), reset u = 1/n, v = 1/m (:1283-1287), rewrite K = exp(Mr + alpha_r + beta_r) over the
+ *     handle's K buffer (:1288) and re-seed the column pass, all in the enqueued iteration stream;
+ *   - error every `check_every` (= print_period) iterations = || sum_i Gamma_ij - b ||_2 (:1303-1304), on the reset
+ *     scalings when the iteration absorbed, like the reference; stop test `err <= stop_thr` (:1316).
+ * Mr       : -M/reg (n x m, leading dimension ldMr), read by every rebuild
+ * alpha_r  : n DOUBLES alpha/reg, beta_r: m DOUBLES beta/reg (device, caller-owned, updated in place; double for both
+ *            dtypes: they cancel against Mr at magnitude 1/reg and grow by one log per absorption)
+ * The K buffer given to b2ot_dense_create is OVERWRITTEN by the rebuilds.  After the solve the exported (u, v) and
+ * (alpha_r, beta_r) give logu = alpha_r + log u, logv = beta_r + log v (:1335-1336).  Single device only. */
+int b2ot_dense_set_stabilized(b2ot_dense* handle, double tau, const void* Mr, int64_t ldMr, void* alpha_r,
+                              void* beta_r);
+/* number of absorptions so far (synchronises the stream) */
+int b2ot_dense_absorb_count(b2ot_dense* handle, int* count);
 int b2ot_dense_set_allreduce(b2ot_dense* handle, b2ot_allreduce_fn fn, void* ctx);
 /* enqueue: load the initial scalings (u0: n, v0: m; log-scalings in LOG mode) and run the
  * column-only pass that seeds the first v update (:629 / :881 of the reference loop) */

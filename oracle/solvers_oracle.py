@@ -1,8 +1,8 @@
 """CPU oracle for the callers right after the Sinkhorn hot path (TEST INFRASTRUCTURE ONLY).
 
 numpy restatement of the reference's `ot.solve` / `ot.solve_sample` Sinkhorn branches, the lazy
-`empirical_sinkhorn2` loss, `empirical_sinkhorn_divergence` and `sinkhorn_knopp_unbalanced` (SURVEY.md
-section 8f, ranks 1-3).  Only ``tests/`` may import it; nothing under ``pot_b200/`` does.
+`empirical_sinkhorn2` loss, `empirical_sinkhorn_divergence`, `sinkhorn_knopp_unbalanced`,
+`sinkhorn_stabilized` and `sinkhorn_epsilon_scaling`.  Only ``tests/`` may import it; nothing under ``pot_b200/`` does.
 
 Parity status: PINNED.  ``tests/golden/make_golden_solvers.py`` ran the unmodified reference (imported from
 /root/reference in the build container) on seeded inputs and committed its outputs as
@@ -18,7 +18,7 @@ import numpy as np
 from . import sinkhorn_oracle as so
 
 __all__ = ["solve", "solve_sample_lazy", "empirical_sinkhorn2_lazy", "empirical_sinkhorn_divergence_lazy",
-           "sinkhorn_knopp_unbalanced", "solve_unbalanced"]
+           "sinkhorn_knopp_unbalanced", "solve_unbalanced", "sinkhorn_stabilized", "sinkhorn_epsilon_scaling"]
 
 
 def _kl_div(p, q, eps=1e-16):
@@ -219,3 +219,117 @@ def solve_unbalanced(M, a=None, b=None, reg=None, unbalanced=None, max_iter=None
                                           stopThr=tol, log=True)
     return {"plan": plan, "potentials": (log["logu"], log["logv"]), "value_linear": log["cost"],
             "value": log["total_cost"], "err": log["err"]}
+
+
+def sinkhorn_stabilized(a, b, M, reg, numItermax=1000, tau=1e3, stopThr=1e-9, warmstart=None, print_period=20,
+                        log=False, warn=True):
+    """ot.bregman.sinkhorn_stabilized for a 1-D b (ot/bregman/_sinkhorn.py:1105-1382).
+
+    Scalings start at 1/n, 1/m (:1252-1254); each iteration is v = b / K^T u, u = a / K v (:1270-1271); when
+    max|u| or max|v| exceeds tau the scalings are folded into the potentials and K is rebuilt (:1274-1288); every
+    print_period iterations err = || sum_i Gamma_ij - b ||_2 (:1303-1304); stop on err <= stopThr (:1316); nan in
+    u or v -> previous (u, v) and stop (:1319-1325).  Returns the plan Gamma (:1349 / :1360) and, with log=True,
+    the dict of :1332-1340.
+    """
+    a, b, M = so._as_arrays(a, b, M)
+    dim_a, dim_b = len(a), len(b)
+    hist = {"err": []}
+    if warmstart is None:
+        alpha, beta = np.zeros(dim_a, dtype=M.dtype), np.zeros(dim_b, dtype=M.dtype)
+    else:
+        alpha, beta = warmstart
+    u = np.ones(dim_a, dtype=M.dtype) / dim_a
+    v = np.ones(dim_b, dtype=M.dtype) / dim_b
+
+    def get_K(alpha, beta):
+        return np.exp(-(M - alpha.reshape((dim_a, 1)) - beta.reshape((1, dim_b))) / reg)  # :1256-1258
+
+    def get_Gamma(alpha, beta, u, v):
+        return np.exp(-(M - alpha.reshape((dim_a, 1)) - beta.reshape((1, dim_b))) / reg
+                      + np.log(u.reshape((dim_a, 1))) + np.log(v.reshape((1, dim_b))))  # :1260-1266
+
+    K = get_K(alpha, beta)
+    err = 1
+    converged = False
+    ii = 0
+    n_absorb = 0  # not in the reference's log: lets the tests assert that a case really exercises the absorption
+    for ii in range(numItermax):
+        uprev, vprev = u, v
+        v = b / np.dot(K.T, u)
+        u = a / np.dot(K, v)
+        if np.max(np.abs(u)) > tau or np.max(np.abs(v)) > tau:
+            alpha, beta = alpha + reg * np.log(u), beta + reg * np.log(v)
+            u = np.ones(dim_a, dtype=M.dtype) / dim_a
+            v = np.ones(dim_b, dtype=M.dtype) / dim_b
+            K = get_K(alpha, beta)
+            n_absorb += 1
+        if ii % print_period == 0:
+            transp = get_Gamma(alpha, beta, u, v)
+            err = np.linalg.norm(np.sum(transp, axis=0) - b)
+            hist["err"].append(err)
+        if err <= stopThr:
+            converged = True
+            break
+        if np.any(np.isnan(u)) or np.any(np.isnan(v)):
+            warnings.warn("Numerical errors at iteration %d" % ii)
+            u, v = uprev, vprev
+            converged = True  # the reference leaves through `break`: no convergence warning
+            break
+    if not converged and warn:
+        warnings.warn("Sinkhorn did not converge. You might want to increase the number of iterations "
+                      "`numItermax` or the regularization parameter `reg`.")
+    G = get_Gamma(alpha, beta, u, v)
+    if not log:
+        return G
+    hist["n_iter"] = ii
+    hist["n_absorb"] = n_absorb
+    hist["logu"] = alpha / reg + np.log(u)
+    hist["logv"] = beta / reg + np.log(v)
+    hist["alpha"] = alpha + reg * np.log(u)
+    hist["beta"] = beta + reg * np.log(v)
+    hist["warmstart"] = (hist["alpha"], hist["beta"])
+    return G, hist
+
+
+def sinkhorn_epsilon_scaling(a, b, M, reg, numItermax=100, epsilon0=1e4, numInnerItermax=100, tau=1e3,
+                             stopThr=1e-9, warmstart=None, print_period=10, log=False, warn=True):
+    """ot.bregman.sinkhorn_epsilon_scaling (ot/bregman/_sinkhorn.py:1385-1573): stabilized solves with
+    reg_i = (epsilon0 - reg) exp(-i) + reg, warm-started from the previous potentials (:1509-1530); every
+    print_period outer iterations err = ||G^T 1 - b||^2 + ||G 1 - a||^2 (:1536-1541); stop when
+    err <= stopThr and i > 35 (:1550)."""
+    a, b, M = so._as_arrays(a, b, M)
+    dim_a, dim_b = len(a), len(b)
+    numItermin = 35
+    numItermax = max(numItermin, numItermax)
+    hist = {"err": []}
+    if warmstart is None:
+        alpha, beta = np.zeros(dim_a, dtype=M.dtype), np.zeros(dim_b, dtype=M.dtype)
+    else:
+        alpha, beta = warmstart
+    err = 1
+    converged = False
+    ii = 0
+    G = None
+    for ii in range(numItermax):
+        regi = (epsilon0 - reg) * np.exp(-ii) + reg
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            G, logi = sinkhorn_stabilized(a, b, M, regi, numItermax=numInnerItermax, stopThr=stopThr,
+                                          warmstart=(alpha, beta), print_period=20, tau=tau, log=True)
+        alpha, beta = logi["alpha"], logi["beta"]
+        if ii % print_period == 0:
+            err = np.linalg.norm(np.sum(G, axis=0) - b) ** 2 + np.linalg.norm(np.sum(G, axis=1) - a) ** 2
+            hist["err"].append(err)
+        if err <= stopThr and ii > numItermin:
+            converged = True
+            break
+    if not converged and warn:
+        warnings.warn("Sinkhorn did not converge. You might want to increase the number of iterations "
+                      "`numItermax` or the regularization parameter `reg`.")
+    if not log:
+        return G
+    hist["alpha"] = alpha
+    hist["beta"] = beta
+    hist["warmstart"] = (alpha, beta)
+    hist["niter"] = ii
+    return G, hist

@@ -14,7 +14,7 @@ from . import _lib
 
 _lib.load()  # fail loudly when the CUDA library is missing
 
-from . import batch, bregman, empirical, host, sharded, solvers, unbalanced, utils  # noqa: E402
+from . import batch, bregman, empirical, host, sharded, solvers, stabilized, unbalanced, utils  # noqa: E402
 from .batch import solve_batch  # noqa: E402
 from .empirical import dist, empirical_sinkhorn, empirical_sinkhorn2, empirical_sinkhorn_divergence  # noqa: E402
 from .solvers import solve, solve_sample  # noqa: E402
@@ -26,9 +26,12 @@ bregman.empirical_sinkhorn = empirical_sinkhorn
 bregman.empirical_sinkhorn2 = empirical_sinkhorn2
 bregman.get_sinkhorn_lazytensor = empirical.get_sinkhorn_lazytensor
 bregman.empirical_sinkhorn_divergence = empirical_sinkhorn_divergence
+bregman.sinkhorn_stabilized = stabilized.sinkhorn_stabilized
+bregman.sinkhorn_epsilon_scaling = stabilized.sinkhorn_epsilon_scaling
 from .bregman import sinkhorn, sinkhorn2, sinkhorn_knopp, sinkhorn_log  # noqa: E402
 
 __version__ = "0.1.0"
 __all__ = ["batch", "bregman", "empirical", "host", "sharded", "utils", "sinkhorn", "sinkhorn2", "sinkhorn_knopp",
            "sinkhorn_log", "solve_batch", "dist", "empirical_sinkhorn", "empirical_sinkhorn2",
-           "empirical_sinkhorn_divergence", "solve", "solve_sample", "solvers", "unbalanced", "sinkhorn_unbalanced", "LazyTensor", "OTResult"]
+           "empirical_sinkhorn_divergence", "solve", "solve_sample", "solvers", "stabilized", "unbalanced", "sinkhorn_unbalanced",
+           "LazyTensor", "OTResult"]

@@ -198,11 +198,12 @@ def loss(mode, K, M, u, v):
 
 
 def plan_value(mode, u, v, *, K=None, M=None, reg=0.0, a=None, b=None, c=None, terms=(), want_plan=True,
-               want_rowsum=False, kmulq=False):
+               want_rowsum=False, kmulq=False, out=None):
     """Plan + objective terms + row marginal in one pass (b2ot_dense_plan_value).
 
     K None: the Gibbs kernel / scaled cost is rebuilt from the cost M with `reg` (M read once, plan written once).
     terms : subset of {"linear", "entropy", "kl"}.
+    out   : optional (n, m) destination of the plan (unit column stride), e.g. a Gibbs-kernel buffer rewritten in place.
     Returns (plan or None, values (3,) float64 device tensor [sum M*P, sum P log(P+1e-16), sum P log(P/q+1e-16)],
     rowsum or None).
     """
@@ -215,7 +216,10 @@ def plan_value(mode, u, v, *, K=None, M=None, reg=0.0, a=None, b=None, c=None, t
         bits |= {"linear": _lib.VALUE_LINEAR, "entropy": _lib.VALUE_ENTROPY, "kl": _lib.VALUE_KL}[t]
     if kmulq:
         bits |= _lib.VALUE_KMULQ
-    out = torch.empty((n, m), dtype=ref.dtype, device=ref.device) if want_plan else None
+    if out is None:
+        out = torch.empty((n, m), dtype=ref.dtype, device=ref.device) if want_plan else None
+    else:
+        assert out.shape == (n, m) and out.dtype == ref.dtype and out.stride(1) == 1
     rows = torch.empty(n, dtype=ref.dtype, device=ref.device) if want_rowsum else None
     vals = torch.empty(3, dtype=torch.float64, device=ref.device)
     scratch = torch.empty(lib.b2ot_dense_plan_value_scratch_bytes(n, m), dtype=torch.uint8, device=ref.device)

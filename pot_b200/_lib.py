@@ -36,6 +36,8 @@ PROTOTYPES = {
                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
                                     C.c_int, C.c_int, C.c_double, C.c_int, C.c_void_p]),
     "b2ot_dense_set_unbalanced": (C.c_int, [C.c_void_p, C.c_double, C.c_double]),
+    "b2ot_dense_set_stabilized": (C.c_int, [C.c_void_p, C.c_double, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "b2ot_dense_absorb_count": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),
     "b2ot_dense_set_allreduce": (C.c_int, [C.c_void_p, ALLREDUCE_FN, C.c_void_p]),
     "b2ot_dense_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "b2ot_dense_iterate": (C.c_int, [C.c_void_p, C.c_int]),

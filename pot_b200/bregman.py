@@ -2,7 +2,8 @@
 
 Mirrors (same names, argument meaning, return values, warnings and errors):
 
-    ot.sinkhorn                 ot/bregman/_sinkhorn.py:21-234   (methods "sinkhorn", "sinkhorn_log")
+    ot.sinkhorn                 ot/bregman/_sinkhorn.py:21-234   (methods "sinkhorn", "sinkhorn_log"; "sinkhorn_stabilized"
+                                                                   and "sinkhorn_epsilon_scaling" via stabilized.py)
     ot.sinkhorn2                ot/bregman/_sinkhorn.py:237-484
     ot.bregman.sinkhorn_knopp   ot/bregman/_sinkhorn.py:487-687
     ot.bregman.sinkhorn_log     ot/bregman/_sinkhorn.py:690-918
@@ -200,7 +201,11 @@ def sinkhorn(a, b, M, reg, method="sinkhorn", numItermax=1000, stopThr=1e-9, ver
         fn = sinkhorn_knopp
     elif name == "sinkhorn_log":
         fn = sinkhorn_log
-    elif name in ("greenkhorn", "sinkhorn_stabilized", "sinkhorn_epsilon_scaling"):
+    elif name in ("sinkhorn_stabilized", "sinkhorn_epsilon_scaling"):
+        from . import stabilized
+
+        fn = stabilized.sinkhorn_stabilized if name == "sinkhorn_stabilized" else stabilized.sinkhorn_epsilon_scaling
+    elif name == "greenkhorn":
         raise NotImplementedError(f"pot_b200: method '{method}' is outside the accelerated hot path")
     else:
         raise ValueError("Unknown method '%s'." % method)
@@ -220,9 +225,13 @@ def sinkhorn2(a, b, M, reg, method="sinkhorn", numItermax=1000, stopThr=1e-9, ve
     a = _weights(a, M.shape[0], M, "a")
     b = _weights(b, M.shape[1], M, "b")
     name = method.lower()
+    if name == "sinkhorn_stabilized":  # :420-432: loss of the stabilized plan
+        from . import stabilized
+
+        return stabilized.sinkhorn_stabilized(a, b, M, reg, numItermax=numItermax, stopThr=stopThr,
+                                              warmstart=warmstart, verbose=verbose, log=log, warn=warn,
+                                              b2ot_loss=True, **kwargs)
     if name not in ("sinkhorn", "sinkhorn_log"):
-        if name in ("sinkhorn_stabilized",):
-            raise NotImplementedError(f"pot_b200: method '{method}' is outside the accelerated hot path")
         raise ValueError("Unknown method '%s'." % method)
     if b.dim() > 1:
         return sinkhorn(a, b, M, reg, method=method, numItermax=numItermax, stopThr=stopThr, verbose=verbose,

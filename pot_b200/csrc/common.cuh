@@ -36,9 +36,13 @@ struct __align__(16) SolveState {
   int need_exact;  // accumulated by finalize (log domain): column sum below the underflow guard
   unsigned int ticket;
   int n_err;       // entries written to err_hist
-  int pad0;
+  int absorb;      // accumulated by finalize blocks (stabilized): some |u_i| or |v_j| above tau
   double last_err;
-  double pad1;
+  // stabilized scaling iteration (b2ot_dense_set_stabilized)
+  int absorb_now;  // set by the finalize of an iteration whose max|u| / max|v| exceeded tau; cleared by absorb_vec_kernel
+  int rebuild;     // set by absorb_vec_kernel when the solve goes on: K must be rebuilt and the column pass re-seeded
+  int n_absorb;    // absorptions so far
+  int pad1;
 };
 
 constexpr int MODE_KNOPP = 0;  // scaling domain

@@ -113,6 +113,10 @@ struct b2ot_dense {
   int graph_launches;     // kernels per replay
   int unbal;            // 1: unbalanced scaling iteration u = (a/Kv)^fi1, v = (b/K^T u)^fi2 (b2ot_dense_set_unbalanced)
   double fi1, fi2;
+  double tau;           // > 0: stabilized scaling iteration (b2ot_dense_set_stabilized)
+  const void* stab_mr;  // Mr = -M/reg (n x m, leading dimension stab_ld), source of the K rebuilds
+  long long stab_ld;
+  void *stab_alpha, *stab_beta;  // caller-owned alpha/reg (n), beta/reg (m) as DOUBLES, updated by the absorptions
 };
 
 static void drop_graph(b2ot_dense* h);
@@ -753,7 +757,7 @@ static int call_allreduce(const b2ot_dense* h, void* buf, long long count, int o
 }
 
 template <typename T>
-static int launch_finalize(const b2ot_dense* h, int nsrc, int init) {
+static int launch_finalize(const b2ot_dense* h, int nsrc, int init, int gate_rebuild = 0) {
   FinParams p;
   memset(&p, 0, sizeof(p));
   const bool multi = h->ar != nullptr || h->comm != nullptr;
@@ -807,10 +811,14 @@ static int launch_finalize(const b2ot_dense* h, int nsrc, int init) {
   p.check_every = h->check_every;
   p.stop_thr = h->stop_thr;
   p.init = init;
-  int blocks = h->fin_blocks;
+  p.tau = h->tau;
+  p.uring = h->uring;
+  p.n = h->n;
+  p.gate_rebuild = gate_rebuild;
+  int blocks = h->tau > 0.0 ? std::min(h->fin_blocks, 512) : h->fin_blocks;  // second half of blk_err: scaled error
   if (!p.use_comm && p.nsrc >= 16 && h->m <= 32768) {  // small problem: spread the partial-row walk over 8 warps
     p.qsplit = 1;
-    blocks = (int)std::min<long long>((h->m + 31) / 32, 1024);
+    blocks = (int)std::min<long long>((h->m + 31) / 32, h->tau > 0.0 ? 512 : 1024);
   }
   if (h->mode == B2OT_MODE_KNOPP)
     B2OT_CUDA(launch_pdl(finalize_kernel<T, MODE_KNOPP>, dim3(blocks), dim3(256), 0, h->stream, p));
@@ -905,6 +913,35 @@ static int dense_init_t(b2ot_dense* h, const void* u0, const void* v0) {
   return launch_exact_cols<T>(h, ST_RUNNING, 0);  // v0' = logb - LSE_i(Mr + u0)
 }
 
+// stabilized: the gated absorption chain that follows every finalize (dense_kernels.cuh, absorb_vec_kernel)
+template <typename T>
+static int launch_absorb(const b2ot_dense* h) {
+  const long long mx = std::max(h->n, h->m);
+  const unsigned gv = (unsigned)std::min<long long>((mx + 255) / 256, 592);
+  absorb_vec_kernel<T><<<gv, 256, 0, h->stream>>>(h->st, h->uring, h->vring, h->n, h->m, h->mp, (double*)h->stab_alpha,
+                                                   (double*)h->stab_beta);
+  B2OT_CHECK_LAUNCH();
+  count_launch();
+  constexpr int VEC = Vec<T>::N;
+  const bool vec = h->m % VEC == 0 && h->ld % VEC == 0 && h->stab_ld % VEC == 0 &&
+                   ((uintptr_t)h->K % 16 == 0) && ((uintptr_t)h->stab_mr % 16 == 0);
+  const long long cols = vec ? h->m / VEC : h->m;
+  const unsigned gx = (unsigned)((cols + 255) / 256);
+  long long gy = std::max<long long>(1, 2368 / gx);
+  gy = std::min<long long>(std::min<long long>(gy, NPMAX), h->n);
+  if (vec)
+    stab_rebuild_kernel<T, true><<<dim3(gx, (unsigned)gy), 256, 0, h->stream>>>(
+        (const T*)h->stab_mr, h->stab_ld, (T*)h->K, h->ld, (const double*)h->stab_alpha, (const double*)h->stab_beta, h->n, h->m,
+        h->mp, (T*)h->partials, h->st);
+  else
+    stab_rebuild_kernel<T, false><<<dim3(gx, (unsigned)gy), 256, 0, h->stream>>>(
+        (const T*)h->stab_mr, h->stab_ld, (T*)h->K, h->ld, (const double*)h->stab_alpha, (const double*)h->stab_beta, h->n, h->m,
+        h->mp, (T*)h->partials, h->st);
+  B2OT_CHECK_LAUNCH();
+  count_launch();
+  return launch_finalize<T>(h, (int)gy, 1, 1);
+}
+
 template <typename T>
 static int enqueue_iterations(b2ot_dense* h, int n_iters) {
   for (int it = 0; it < n_iters; ++it) {
@@ -922,6 +959,10 @@ static int enqueue_iterations(b2ot_dense* h, int n_iters) {
     }
     int rc = h->unbal ? launch_finalize_unbal<T>(h, nsrc) : launch_finalize<T>(h, nsrc, 0);
     if (rc) return rc;
+    if (h->tau > 0.0) {
+      rc = launch_absorb<T>(h);
+      if (rc) return rc;
+    }
   }
   return 0;
 }
@@ -1024,6 +1065,7 @@ extern "C" int b2ot_dense_profile(b2ot_dense* h, int n_iters, float* sweep_ms_av
       rc = h->dtype == B2OT_F32 ? launch_finalize_unbal<float>(h, nsrc) : launch_finalize_unbal<double>(h, nsrc);
     else
       rc = h->dtype == B2OT_F32 ? launch_finalize<float>(h, nsrc, 0) : launch_finalize<double>(h, nsrc, 0);
+    if (rc == 0 && h->tau > 0.0) rc = h->dtype == B2OT_F32 ? launch_absorb<float>(h) : launch_absorb<double>(h);
   }
   if (rc == 0) {
     B2OT_CUDA(cudaEventRecord(ev[2 * n_iters], h->stream));
@@ -1059,12 +1101,9 @@ extern "C" int b2ot_dense_poll(b2ot_dense* h, int* status, int* iter) {
   return 0;
 }
 
-extern "C" int b2ot_dense_solve(b2ot_dense* h, const void* u0, const void* v0, int poll_every, int* status,
-                                int* niter, int* n_err) {
-  B2OT_REQUIRE(h != nullptr, "b2ot_dense_solve: null handle");
-  int rc = b2ot_dense_init(h, u0, v0);
-  if (rc) return rc;
-  int st = ST_RUNNING, it = 0;
+static int run_until_stopped(b2ot_dense* h, int it, int poll_every, int* status, int* niter, int* n_err) {
+  int rc = 0;
+  int st = ST_RUNNING;
   while (st == ST_RUNNING) {
     int chunk = h->max_iter - it;
     if (poll_every > 0 && chunk > poll_every) chunk = poll_every;
@@ -1077,6 +1116,38 @@ extern "C" int b2ot_dense_solve(b2ot_dense* h, const void* u0, const void* v0, i
   if (status) *status = st;
   if (niter) *niter = h->h_state->niter;
   if (n_err) *n_err = h->h_state->n_err;
+  return 0;
+}
+
+extern "C" int b2ot_dense_solve(b2ot_dense* h, const void* u0, const void* v0, int poll_every, int* status,
+                                int* niter, int* n_err) {
+  B2OT_REQUIRE(h != nullptr, "b2ot_dense_solve: null handle");
+  int rc = b2ot_dense_init(h, u0, v0);
+  if (rc) return rc;
+  return run_until_stopped(h, 0, poll_every, status, niter, n_err);
+}
+
+extern "C" int b2ot_dense_set_stabilized(b2ot_dense* h, double tau, const void* Mr, int64_t ldMr, void* alpha_r,
+                                         void* beta_r) {
+  B2OT_REQUIRE(h != nullptr, "b2ot_dense_set_stabilized: null handle");
+  B2OT_REQUIRE(h->mode == B2OT_MODE_KNOPP && !h->unbal, "b2ot_dense_set_stabilized: balanced scaling-domain handles only");
+  B2OT_REQUIRE(h->ar == nullptr && h->comm == nullptr, "b2ot_dense_set_stabilized: single device only");
+  B2OT_REQUIRE(tau > 0.0, "b2ot_dense_set_stabilized: tau must be positive");
+  B2OT_REQUIRE(Mr && alpha_r && beta_r && ldMr >= h->m, "b2ot_dense_set_stabilized: bad Mr / potentials");
+  drop_graph(h);  // the iteration stream changes (finalize parameters, absorption chain)
+  h->tau = tau;
+  h->stab_mr = Mr;
+  h->stab_ld = ldMr;
+  h->stab_alpha = alpha_r;
+  h->stab_beta = beta_r;
+  return 0;
+}
+
+extern "C" int b2ot_dense_absorb_count(b2ot_dense* h, int* count) {
+  B2OT_REQUIRE(h != nullptr && count != nullptr, "b2ot_dense_absorb_count: null argument");
+  B2OT_CUDA(cudaMemcpyAsync(h->h_state, h->st, sizeof(SolveState), cudaMemcpyDeviceToHost, h->stream));
+  B2OT_CUDA(cudaStreamSynchronize(h->stream));
+  *count = h->h_state->n_absorb;
   return 0;
 }
 

@@ -679,6 +679,16 @@ struct FinParams {
   double stop_thr;
   int init;             // KNOPP seeding pass: only v0 = b / (K^T u0) and its guard flags
   int qsplit;           // 1: blocks of 32 columns x 8 warps over the partial rows (small m, many partial rows)
+  // stabilized scaling iteration (ot/bregman/_sinkhorn.py:1105-1382), KNOPP only, tau > 0 turns it on: after the sweep
+  // the pair (u, v) of this iteration is tested against tau (:1274); when it is exceeded st->absorb_now is raised and
+  // the gated kernels that follow (absorb_vec_kernel, stab_rebuild_kernel, this kernel with init = 1) fold (u, v) into
+  // the potentials, rewrite K and re-seed the column pass (:1275-1288).  The error of such an iteration is the
+  // reference's: measured on Gamma AFTER the reset u = 1/n, v = 1/m (:1303), i.e. on the plan scaled by 1/(n m).
+  // Stop test `err <= stop_thr` (:1316).
+  double tau;
+  const void* uring;    // 2 x n, read for max|u| when tau > 0
+  long long n;
+  int gate_rebuild;     // 1 (init pass after an absorption): run only when st->rebuild is raised, clear it at the end
 };
 
 template <typename T, int MODE>
@@ -690,6 +700,7 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
   griddep_wait();               // column partials of the sweep (or the peer put) are complete and visible
   griddep_launch_dependents();  // let the next sweep start its prologue (barriers, first K tiles) under this kernel
   if (st->status != ST_RUNNING) return;
+  if (p.gate_rebuild && st->rebuild == 0) return;
   const int tid = threadIdx.x;
   if (p.use_comm && !comm_wait(p.comm, p.seq)) {  // fused "take" of the NVLink exchange
     if (tid == 0) st->status = ST_COMM_TIMEOUT;
@@ -706,8 +717,16 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
   if (tid == 0) sflags = 0;
   __syncthreads();
 
-  double e2 = 0.0;
+  double e2 = 0.0, e2s = 0.0;
   int flags = 0;
+  const bool stab = MODE == MODE_KNOPP && p.tau > 0.0 && !p.init;
+  const T tau = (T)p.tau;
+  const T reset_scale = ((T)1 / (T)p.n) * ((T)1 / (T)p.m);  // u = 1/n, v = 1/m after an absorption (:1283-1287)
+  if (stab) {  // max|u| of the u this sweep produced
+    const T* unew = reinterpret_cast<const T*>(p.uring) + (long long)(st->sel_u ^ 1) * p.n;
+    for (long long i = (long long)blockIdx.x * 256 + tid; i < p.n; i += (long long)gridDim.x * 256)
+      if (abs_t(__ldcg(&unew[i])) > tau) flags |= 8;
+  }
   auto column = [&](long long j, T c) {
     const T bj = b[j];
     const T vj = vcur[j];
@@ -718,6 +737,11 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
       vn = bj / c;
       if (c == (T)0) flags |= FLAG_CZERO;
       if (!finite_t(vn)) flags |= FLAG_VBAD;
+      if (stab) {
+        if (abs_t(vj) > tau) flags |= 8;
+        const T ds = (vj * c) * reset_scale - bj;
+        e2s += (double)ds * (double)ds;
+      }
     } else {
       const T d = c - bj;
       e2 += (double)d * (double)d;
@@ -762,10 +786,26 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
     if (tid < o) sred[tid] += sred[tid + o];
     __syncthreads();
   }
+  if (stab) {  // second total: the error as the reference reports it when this iteration absorbs
+    const double first = sred[0];
+    __syncthreads();
+    sred[tid] = e2s;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+      if (tid < o) sred[tid] += sred[tid + o];
+      __syncthreads();
+    }
+    if (tid == 0) {
+      p.blk_err[512 + blockIdx.x] = sred[0];  // grid <= 512 blocks when tau > 0 (launch_finalize)
+      sred[0] = first;
+    }
+    __syncthreads();
+  }
   if (tid == 0) {
     p.blk_err[blockIdx.x] = sred[0];
     if (sflags & 3) atomicOr(&st->next_flags, sflags & 3);
     if (sflags & 4) atomicOr(&st->need_exact, 1);
+    if (sflags & 8) atomicOr(&st->absorb, 1);
     __threadfence();
     const unsigned int t = atomicAdd(&st->ticket, 1u);
     s_last = (t == gridDim.x - 1) ? 1 : 0;
@@ -783,6 +823,18 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
     if (tid < o) sred[tid] += sred[tid + o];
     __syncthreads();
   }
+  const int absorb = stab ? atomicOr(&st->absorb, 0) : 0;
+  if (absorb) {  // block-uniform: total of the scaled error instead
+    __syncthreads();
+    double y = 0.0;
+    for (unsigned int i = tid; i < gridDim.x; i += 256) y += __ldcg(&p.blk_err[512 + i]);
+    sred[tid] = y;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+      if (tid < o) sred[tid] += sred[tid + o];
+      __syncthreads();
+    }
+  }
   if (tid != 0) return;
   const int nflags = atomicOr(&st->next_flags, 0);
   const int nexact = atomicOr(&st->need_exact, 0);
@@ -795,6 +847,7 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
   if (p.init) {
     st->sel_v = nxt;
     st->cur_flags = nflags;
+    if (p.gate_rebuild) st->rebuild = 0;
   } else if (MODE == MODE_KNOPP && (st->cur_flags != 0 || uflag != 0)) {
     // reference guard (_sinkhorn.py:633-645): come back to the previous (u, v) and stop
     st->status = ST_NUMERR;
@@ -808,7 +861,7 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
       p.err_hist[st->n_err] = err;
       st->n_err += 1;
       st->last_err = err;
-      if (err < p.stop_thr) {
+      if (p.tau > 0.0 ? (err <= p.stop_thr) : (err < p.stop_thr)) {
         st->status = ST_CONVERGED;
         st->niter = ii;
         stop = true;
@@ -820,6 +873,10 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
         st->niter = ii;
       } else if (MODE == MODE_LOG && nexact) {
         st->status = ST_PAUSE_EXACT;  // v_next unusable for some columns: exact column pass needed
+      } else if (MODE == MODE_KNOPP && absorb) {
+        // stabilized: the absorption chain resets every slot of both rings and re-seeds v; only the index moves on
+        st->iter = ii + 1;
+        st->cur_flags = 0;
       } else {
         st->sel_v = nxt;
         st->iter = ii + 1;
@@ -827,11 +884,124 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
       }
     }
   }
+  if (absorb && st->status != ST_NUMERR) {  // also when this iteration is the last one (:1275 runs before the tests)
+    st->absorb_now = 1;
+    st->n_absorb += 1;
+  }
   st->next_flags = 0;
   st->uflag = 0;
   st->need_exact = 0;
+  st->absorb = 0;
   st->ticket = 0;
   __threadfence();
+}
+
+// ------------------------------------------------------------------------------------------------
+// Stabilized scaling iteration, absorption chain (ot/bregman/_sinkhorn.py:1274-1288), all gated on device flags so
+// that the chain can sit in the enqueued iteration stream (and in its CUDA graph) and costs three empty launches when
+// nothing is to absorb.
+//   absorb_vec_kernel   : alpha/reg += log u, beta/reg += log v (:1281; double accumulators for both dtypes), u = 1/n,
+//                         v = 1/m in every ring slot (:1283-1287)
+//   stab_rebuild_kernel : K = exp(-(M - alpha - beta)/reg) (:1288) from Mr = -M/reg, written over the handle's K, and in
+//                         the same pass the column sums K^T u (u = 1/n) that seed the next v update (:1270)
+//   finalize_kernel with init = 1, gate_rebuild = 1: v = b / K^T u
+// An absorbing iteration costs 3 passes over an n x m matrix (sweep reads K; rebuild reads Mr, writes K) instead of the
+// reference's 5 (two GEMVs, get_K reads M and writes K, get_Gamma for the error on check iterations on top).
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) absorb_vec_kernel(SolveState* st, void* uring_, void* vring_, long long n,
+                                                         long long m, long long mp, double* __restrict__ alpha_r,
+                                                         double* __restrict__ beta_r) {
+  if (st->absorb_now == 0) return;
+  T* uring = reinterpret_cast<T*>(uring_);
+  T* vring = reinterpret_cast<T*>(vring_);
+  const int sel_u = st->sel_u, sel_v = st->sel_v;
+  const T u0 = (T)1 / (T)n, v0 = (T)1 / (T)m;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
+    alpha_r[i] += log((double)uring[(long long)sel_u * n + i]);
+    uring[i] = u0;
+    uring[n + i] = u0;
+  }
+  for (long long j = (long long)blockIdx.x * 256 + threadIdx.x; j < m; j += (long long)gridDim.x * 256) {
+    beta_r[j] += log((double)vring[(long long)sel_v * mp + j]);
+    vring[j] = v0;
+    vring[mp + j] = v0;
+    vring[2 * mp + j] = v0;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(&st->ticket, 1u) == gridDim.x - 1) {  // every block has passed the gate: safe to drop it
+      st->ticket = 0;
+      st->absorb_now = 0;
+      if (st->status == ST_RUNNING) st->rebuild = 1;
+      __threadfence();
+    }
+  }
+}
+
+// grid (ceil(m / (256 VEC)), gy): a thread owns VEC columns and walks the rows y, y + gy, ... two at a time
+template <typename T, bool VECT>
+__global__ void __launch_bounds__(256) stab_rebuild_kernel(const T* __restrict__ Mr, long long ldM, T* __restrict__ K,
+                                                           long long ldK, const double* __restrict__ alpha_r,
+                                                           const double* __restrict__ beta_r, long long n, long long m,
+                                                           long long mp, T* __restrict__ partials,
+                                                           const SolveState* st) {
+  if (st->rebuild == 0) return;
+  constexpr int VEC = VECT ? Vec<T>::N : 1;
+  const long long j = ((long long)blockIdx.x * 256 + threadIdx.x) * VEC;
+  if (j >= m) return;
+  const T u0 = (T)1 / (T)n;
+  double bj[VEC];  // the potentials are accumulated and added in double for both dtypes: with T = float the exponent
+  T acc[VEC];      // Mr + alpha/reg + beta/reg cancels terms of magnitude 1/reg, and alpha/reg grows by one log per absorption
+#pragma unroll
+  for (int e = 0; e < VEC; ++e) {
+    bj[e] = beta_r[j + e];
+    acc[e] = (T)0;
+  }
+  auto load = [&](long long i, T (&x)[VEC]) {
+    if constexpr (VECT) {
+      const typename Vec<T>::type q = __ldcs(reinterpret_cast<const typename Vec<T>::type*>(Mr + i * ldM + j));
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) x[e] = elem(q, e);
+    } else {
+      x[0] = __ldcs(Mr + i * ldM + j);
+    }
+  };
+  auto store = [&](long long i, const T (&y)[VEC]) {
+    if constexpr (VECT) {
+      typename Vec<T>::type q;
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) elem(q, e) = y[e];
+      *reinterpret_cast<typename Vec<T>::type*>(K + i * ldK + j) = q;  // plain store: the sweep reads K next (L2)
+    } else {
+      K[i * ldK + j] = y[0];
+    }
+  };
+  for (long long i = blockIdx.y; i < n; i += 2LL * gridDim.y) {
+    const long long i2 = i + gridDim.y;
+    const bool two = i2 < n;
+    T x0[VEC], x1[VEC], y0[VEC], y1[VEC];
+    load(i, x0);
+    if (two) load(i2, x1);
+    const double a0 = alpha_r[i], a1 = alpha_r[two ? i2 : i];
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) {
+      y0[e] = exp_t((T)(((double)x0[e] + a0) + bj[e]));
+      acc[e] = fma(y0[e], u0, acc[e]);
+    }
+    store(i, y0);
+    if (two) {
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) {
+        y1[e] = exp_t((T)(((double)x1[e] + a1) + bj[e]));
+        acc[e] = fma(y1[e], u0, acc[e]);
+      }
+      store(i2, y1);
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < VEC; ++e) partials[(long long)blockIdx.y * mp + j + e] = acc[e];
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -56,3 +56,9 @@ def golden_c1():
 def gs():
     """Golden vectors of the callers after the path (ot.solve, unbalanced, divergence): golden_solvers.npz."""
     return Golden(os.path.join(GOLDEN_DIR, "golden_solvers.npz"))
+
+
+@pytest.fixture(scope="session")
+def gstab():
+    """Golden vectors of sinkhorn_stabilized / sinkhorn_epsilon_scaling: golden_stabilized.npz."""
+    return Golden(os.path.join(GOLDEN_DIR, "golden_stabilized.npz"))

@@ -1,0 +1,230 @@
+"""GPU parity tests of ot.bregman.sinkhorn_stabilized / sinkhorn_epsilon_scaling against the
+golden vectors of the reference (tests/golden/golden_stabilized.npz) and the CPU oracle.
+Everything goes through libb2ot.so (C ABI) via pot_b200.
+
+Tolerances (north_star): 1e-10 relative in fp64, 1e-4 relative in fp32, fixed iteration count.
+"""
+import ctypes as C
+import warnings
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+if torch.cuda.is_available():
+    import pot_b200 as ot
+    from pot_b200 import _dense, _lib, stabilized
+from oracle import solvers_oracle as sorc
+from test_oracle_stabilized import STAB, kwargs
+from test_solvers_gpu import assert_plan, assert_scalar, assert_vec, npf, to_dev
+
+DEV = "cuda:0"
+
+
+def tol_of(case):
+    return 1e-10 if "f64" in case else 1e-4
+
+
+def fixed_count(kw):
+    """stopThr = 0 means "fixed iteration count" in the golden cases.  The reference stops on err <= stopThr (:1316) and
+    the device path can reach err == 0.0 exactly in fp32 (potentials accumulated in double), which that rule counts as
+    converged; a negative threshold keeps the iteration count fixed."""
+    return {**kw, "stopThr": -1.0} if kw.get("stopThr") == 0.0 else kw
+
+
+def check_errs(errs, ref, f64):
+    errs = [float(e) for e in errs]
+    assert len(errs) == len(ref)
+    np.testing.assert_allclose(errs, ref, rtol=1e-5 if f64 else 5e-2, atol=1e-12 if f64 else 2e-6)
+
+
+@pytest.mark.parametrize("name", STAB)
+def test_stabilized_golden(gstab, name):
+    case = f"stab_{name}"
+    M, a, b = to_dev(gstab(case, "M"), gstab(case, "a"), gstab(case, "b"))
+    reg, tol = float(gstab(case, "reg")), tol_of(name)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        G, log = ot.bregman.sinkhorn_stabilized(a, b, M, reg, log=True, **fixed_count(kwargs(gstab, case)))
+    assert G.dtype == M.dtype and G.device == M.device
+    assert log["n_iter"] == int(gstab(case, "n_iter"))
+    assert_plan(G, gstab(case, "plan"), tol)
+    for k in ("logu", "logv", "alpha", "beta"):
+        assert_vec(log[k], gstab(case, k), tol)
+    assert_vec(log["warmstart"][0], gstab(case, "alpha"), tol)
+    check_errs(log["err"], gstab(case, "err"), "f64" in name)
+    # marginal violation of the returned plan, reported next to the reference's
+    viol = float((G.sum(0) - b).norm())
+    ref_viol = float(np.linalg.norm(gstab(case, "plan").sum(0) - gstab(case, "b")))
+    assert viol <= ref_viol + (1e-12 if "f64" in name else 1e-5)
+
+
+@pytest.mark.parametrize("name", [n for n in STAB if "absorb" in n])
+def test_absorption_happens_on_the_device_path(gstab, name):
+    """The golden cases named *absorb* must really pause for absorptions (as often as the oracle's loop does)."""
+    case = f"stab_{name}"
+    M, a, b = to_dev(gstab(case, "M"), gstab(case, "a"), gstab(case, "b"))
+    kw = fixed_count(kwargs(gstab, case))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        _, ref = sorc.sinkhorn_stabilized(gstab(case, "a"), gstab(case, "b"), gstab(case, "M"), float(gstab(case, "reg")),
+                                          log=True, **kw)
+        out = stabilized._stabilized_core(a, b, M, float(gstab(case, "reg")), kw["numItermax"], kw.get("tau", 1e3),
+                                          kw["stopThr"], None, kw.get("print_period", 20))
+    assert ref["n_absorb"] >= 1
+    assert out[8] == ref["n_absorb"]
+    assert out[6] == ref["n_iter"]
+
+
+def test_warmstart_and_loss_through_ot_sinkhorn(gstab):
+    case = "stab_absorb_f64"
+    M, a, b, al, be = to_dev(*(gstab(case, k) for k in ("M", "a", "b", "alpha", "beta")))
+    reg = float(gstab(case, "reg"))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        G, log = ot.sinkhorn(a, b, M, reg, method="sinkhorn_stabilized", warmstart=(al, be), numItermax=40,
+                             stopThr=0.0, log=True)
+        val = ot.sinkhorn2(a, b, M, reg, method="sinkhorn_stabilized", numItermax=200, stopThr=0.0)
+        val2, log2 = ot.sinkhorn2(a, b, M, reg, method="sinkhorn_stabilized", numItermax=200, stopThr=0.0, log=True)
+    assert_plan(G, gstab(case + "_warm", "plan"), 1e-10)
+    assert_vec(log["alpha"], gstab(case + "_warm", "alpha"), 1e-10)
+    assert_vec(log["beta"], gstab(case + "_warm", "beta"), 1e-10)
+    assert log["n_iter"] == int(gstab(case + "_warm", "n_iter"))
+    assert_scalar(val, gstab(case + "_loss", "value"), 1e-10)
+    assert_scalar(val2, gstab(case + "_loss", "value"), 1e-10)
+    assert val.dim() == 0 and val.dtype == M.dtype
+    assert_vec(log2["alpha"], gstab(case, "alpha"), 1e-10)
+
+
+@pytest.mark.parametrize("name", ["f64", "short_f64"])
+def test_epsilon_scaling_golden(gstab, name):
+    case = f"eps_{name}"
+    M, a, b = to_dev(gstab(case, "M"), gstab(case, "a"), gstab(case, "b"))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        G, log = ot.bregman.sinkhorn_epsilon_scaling(a, b, M, float(gstab(case, "reg")), log=True,
+                                                     **kwargs(gstab, case))
+        G2 = ot.sinkhorn(a, b, M, float(gstab(case, "reg")), method="sinkhorn_epsilon_scaling",
+                         **{k: v for k, v in kwargs(gstab, case).items()})
+    assert log["niter"] == int(gstab(case, "niter"))
+    # Tolerance: the stages start at reg = epsilon0 = 1e4, where the absorbed potentials are alpha ~ -eps0 log n,
+    # beta ~ +eps0 log m (3.7e4 here); every later get_K cancels them in M - alpha - beta, an absolute rounding noise of
+    # ~4e-12 that the last stages divide by reg = 0.01.  The reference's own result is therefore defined to ~5e-10
+    # relative only (scripts/diag_eps.py: a single stage from identical potentials already differs by 1e-11 / reg);
+    # 40 chained stages are compared at 5e-8.
+    tol = 5e-8 if name == "f64" else 1e-9
+    assert_plan(G, gstab(case, "plan"), tol)
+    assert_plan(G2, gstab(case, "plan"), tol)
+    assert_vec(log["alpha"], gstab(case, "alpha"), tol)
+    assert_vec(log["beta"], gstab(case, "beta"), tol)
+    ref = gstab(case, "err")
+    errs = [float(e) for e in log["err"]]
+    assert len(errs) == len(ref)
+    np.testing.assert_allclose(errs, ref, rtol=1e-2, atol=1e-17)
+    # marginals of the returned plan
+    assert float((G.sum(0) - b).norm()) < 1e-8 and float((G.sum(1) - a).norm()) < 1e-8 or name != "f64"
+
+
+@pytest.mark.parametrize("dtype,n,m,reg,its,tau", [
+    (np.float64, 1500, 1100, 0.004, 120, 1e3),   # fused sweep, many absorptions
+    (np.float64, 700, 2300, 0.02, 60, 1e2),
+    (np.float32, 1200, 1000, 0.02, 100, 1e2),
+])
+def test_stabilized_vs_oracle_larger(dtype, n, m, reg, its, tau):
+    rng = np.random.RandomState(n + m)
+    xs, xt = rng.randn(n, 2), rng.randn(m, 2) + 1.0
+    M = ((xs ** 2).sum(1)[:, None] + (xt ** 2).sum(1)[None, :] - 2 * xs @ xt.T).clip(0)
+    M = (M / M.max()).astype(dtype)
+    a = (np.ones(n) / n).astype(dtype)
+    b = rng.rand(m) + 0.1
+    b = (b / b.sum()).astype(dtype)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        Gr, lr = sorc.sinkhorn_stabilized(a, b, M, reg, numItermax=its, tau=tau, stopThr=0.0, log=True)
+        Md, ad, bd = to_dev(M, a, b)
+        G, lg = ot.bregman.sinkhorn_stabilized(ad, bd, Md, reg, numItermax=its, tau=tau, stopThr=0.0, log=True)
+    assert lr["n_absorb"] >= 1
+    assert lg["n_iter"] == lr["n_iter"]
+    if dtype == np.float32:
+        # fp32: the reference's own result is noisy here (alpha += reg log u is rounded in fp32 at every one of the ~100
+        # absorptions and divided by reg in get_K); the device path accumulates the absorbed potentials in double.
+        # 1e-4 against the fp64 oracle on the same fp32 inputs, 1e-3 against the fp32 oracle.
+        assert_plan(G, Gr, 1e-3)
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            Gr, lr = sorc.sinkhorn_stabilized(a.astype(np.float64), b.astype(np.float64), M.astype(np.float64), reg,
+                                              numItermax=its, tau=tau, stopThr=0.0, log=True)
+    tol = 1e-10 if dtype == np.float64 else 1e-4
+    assert_plan(G, Gr, tol)
+    assert_vec(lg["alpha"], lr["alpha"], tol)
+    assert_vec(lg["beta"], lr["beta"], tol)
+    check_errs(lg["err"], np.asarray(lr["err"], dtype=np.float64), dtype == np.float64)
+    # n or m above tau: every iteration absorbs, the last one included, so the reference returns Gamma on the reset
+    # scalings (the plan scaled by 1/(n m), :1283-1287 then :1349); same here
+    row, row_ref = npf(G.sum(1)), Gr.sum(1)
+    assert np.abs(row - row_ref).max() / row_ref.max() < (1e-9 if dtype == np.float64 else 1e-3)
+
+
+def test_convergence_stop_matches_reference_rule(gstab):
+    """err <= stopThr (not <) and the check period: n_iter of the converging golden cases already pins it; here the
+    boundary: stopThr equal to a recorded error must stop at that very check."""
+    case = "stab_conv_f64"
+    M, a, b = to_dev(gstab(case, "M"), gstab(case, "a"), gstab(case, "b"))
+    kw = kwargs(gstab, case)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        _, log = ot.bregman.sinkhorn_stabilized(a, b, M, float(gstab(case, "reg")), log=True,
+                                                **{**kw, "stopThr": 0.0, "numItermax": 41})
+        e = float(log["err"][3])  # check of iteration 15 (print_period 5)
+        _, log2 = ot.bregman.sinkhorn_stabilized(a, b, M, float(gstab(case, "reg")), log=True,
+                                                 **{**kw, "stopThr": e, "numItermax": 41})
+    assert log2["n_iter"] == 15 and len(log2["err"]) == 4
+
+
+def test_errors():
+    M = torch.rand(8, 9, device=DEV, dtype=torch.float64)
+    a = torch.full((8,), 1 / 8, device=DEV, dtype=torch.float64)
+    b2 = torch.full((9, 2), 1 / 9, device=DEV, dtype=torch.float64)
+    with pytest.raises(NotImplementedError):
+        ot.bregman.sinkhorn_stabilized(a, b2, M, 0.1)
+    with pytest.raises(TypeError):
+        ot.bregman.sinkhorn_stabilized(a.cpu().numpy(), b2[:, 0].cpu().numpy(), M.cpu().numpy(), 0.1)
+    # C ABI misuse: log-domain handles cannot be switched, tau must be positive, buffers must be given
+    lib = _lib.load()
+    b = b2[:, 0].contiguous()
+    Mr = _dense.cost_transform(M, 0.1, "negscale")
+    al, be = torch.zeros_like(a, dtype=torch.float64), torch.zeros_like(b, dtype=torch.float64)
+    args = (Mr.data_ptr(), Mr.stride(0), al.data_ptr(), be.data_ptr())
+    s = _dense.DenseSolver("log", Mr, torch.log(a), b, torch.log(b), max_iter=5)
+    assert lib.b2ot_dense_set_stabilized(s.h, 1e3, *args) != 0
+    s.close()
+    K = _dense.cost_transform(M, 0.1, "kexp")
+    s = _dense.DenseSolver("knopp", K, a, b, None, max_iter=5)
+    assert lib.b2ot_dense_set_stabilized(s.h, -1.0, *args) != 0
+    assert lib.b2ot_dense_set_stabilized(s.h, 1e3, None, Mr.stride(0), al.data_ptr(), be.data_ptr()) != 0
+    assert lib.b2ot_dense_set_stabilized(s.h, 1e3, *args) == 0
+    cnt = C.c_int(-1)
+    assert lib.b2ot_dense_absorb_count(s.h, C.byref(cnt)) == 0
+    s.close()
+
+
+def test_odd_layouts_take_the_scalar_rebuild():
+    """m not a multiple of the vector width and a strided M: the rebuild kernel's scalar variant."""
+    rng = np.random.RandomState(5)
+    n, m = 130, 77
+    Mfull = rng.rand(n, m + 3)
+    a = np.ones(n) / n
+    b = rng.rand(m) + 0.1
+    b /= b.sum()
+    Md = torch.as_tensor(Mfull, device=DEV)[:, 1:m + 1]  # unaligned rows, leading dimension m + 3
+    M = Mfull[:, 1:m + 1]
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        Gr, lr = sorc.sinkhorn_stabilized(a, b, M, 0.01, numItermax=80, tau=5.0, stopThr=0.0, log=True)
+        G, lg = ot.bregman.sinkhorn_stabilized(*to_dev(a, b), Md, 0.01, numItermax=80, tau=5.0, stopThr=0.0, log=True)
+    assert lr["n_absorb"] >= 1
+    assert_plan(G, Gr, 1e-10)
+    assert_vec(lg["alpha"], lr["alpha"], 1e-10)
+    check_errs(lg["err"], np.asarray(lr["err"], dtype=np.float64), True)

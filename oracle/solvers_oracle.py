@@ -2,7 +2,7 @@
 
 numpy restatement of the reference's `ot.solve` / `ot.solve_sample` Sinkhorn branches, the lazy
 `empirical_sinkhorn2` loss, `empirical_sinkhorn_divergence`, `sinkhorn_knopp_unbalanced`,
-`sinkhorn_stabilized` and `sinkhorn_epsilon_scaling`.  Only ``tests/`` may import it; nothing under ``pot_b200/`` does.
+`sinkhorn_stabilized`, `sinkhorn_epsilon_scaling` and `entropic_gromov_wasserstein`.  Only ``tests/`` may import it; nothing under ``pot_b200/`` does.
 
 Parity status: PINNED.  ``tests/golden/make_golden_solvers.py`` ran the unmodified reference (imported from
 /root/reference in the build container) on seeded inputs and committed its outputs as
@@ -18,7 +18,8 @@ import numpy as np
 from . import sinkhorn_oracle as so
 
 __all__ = ["solve", "solve_sample_lazy", "empirical_sinkhorn2_lazy", "empirical_sinkhorn_divergence_lazy",
-           "sinkhorn_knopp_unbalanced", "solve_unbalanced", "sinkhorn_stabilized", "sinkhorn_epsilon_scaling"]
+           "sinkhorn_knopp_unbalanced", "solve_unbalanced", "sinkhorn_stabilized", "sinkhorn_epsilon_scaling",
+           "entropic_gromov_wasserstein"]
 
 
 def _kl_div(p, q, eps=1e-16):
@@ -333,3 +334,65 @@ def sinkhorn_epsilon_scaling(a, b, M, reg, numItermax=100, epsilon0=1e4, numInne
     hist["warmstart"] = (alpha, beta)
     hist["niter"] = ii
     return G, hist
+
+
+def entropic_gromov_wasserstein(C1, C2, p=None, q=None, loss_fun="square_loss", epsilon=0.1, symmetric=None, G0=None,
+                                max_iter=1000, tol=1e-9, solver="PGD", warmstart=False, log=False, **kwargs):
+    """ot.gromov.entropic_gromov_wasserstein (ot/gromov/_bregman.py:25-252) on top of the oracle's sinkhorn_knopp.
+
+    init_matrix / tensor_product / gwggrad / gwloss follow ot/gromov/_utils.py:38-354: L(a, b) = f1(a) + f2(b) - h1(a) h2(b),
+    constC = f1(C1) p 1^T + 1 q^T f2(C2)^T, tens = constC - h1(C1) T h2(C2)^T, gradient = 2 tens.
+    """
+    C1, C2 = np.asarray(C1), np.asarray(C2)
+    N1, N2 = C1.shape[0], C2.shape[0]
+    p = np.ones(N1, dtype=C1.dtype) / N1 if p is None else np.asarray(p)
+    q = np.ones(N2, dtype=C2.dtype) / N2 if q is None else np.asarray(q)
+
+    def init_matrix(C1, C2):
+        if loss_fun == "square_loss":
+            fC1, fC2, hC1, hC2 = C1 ** 2, C2 ** 2, C1, 2 * C2
+        else:
+            fC1, fC2, hC1, hC2 = C1 * np.log(C1 + 1e-18) - C1, C2, C1, np.log(C2 + 1e-18)
+        constC1 = np.dot(np.dot(fC1, p.reshape(-1, 1)), np.ones((1, len(q)), dtype=q.dtype))
+        constC2 = np.dot(np.ones((len(p), 1), dtype=p.dtype), np.dot(q.reshape(1, -1), fC2.T))
+        return constC1 + constC2, hC1, hC2
+
+    def tensor_product(constC, hC1, hC2, T):
+        return constC + (-np.dot(np.dot(hC1, T), hC2.T))
+
+    T = np.outer(p, q) if G0 is None else np.asarray(G0)
+    constC, hC1, hC2 = init_matrix(C1, C2)
+    if symmetric is None:
+        symmetric = np.allclose(C1, C1.T, atol=1e-10) and np.allclose(C2, C2.T, atol=1e-10)
+    if not symmetric:
+        constCt, hC1t, hC2t = init_matrix(C1.T, C2.T)
+    cpt, err = 0, 1
+    if warmstart:
+        mu = np.zeros(N1, dtype=C1.dtype) - np.log(N1)
+        nu = np.zeros(N2, dtype=C2.dtype) - np.log(N2)
+    hist = {"err": []}
+    while err > tol and cpt < max_iter:
+        Tprev = T
+        if symmetric:
+            tens = 2 * tensor_product(constC, hC1, hC2, T)
+        else:
+            tens = 0.5 * (2 * tensor_product(constC, hC1, hC2, T) + 2 * tensor_product(constCt, hC1t, hC2t, T))
+        if solver == "PPA":
+            tens = tens - epsilon * np.log(T)
+        if warmstart:
+            T, loginn = so.sinkhorn_knopp(p, q, tens, epsilon, log=True, warmstart=(mu, nu), **kwargs)
+            mu = epsilon * np.log(loginn["u"])
+            nu = epsilon * np.log(loginn["v"])
+        else:
+            T = so.sinkhorn_knopp(p, q, tens, epsilon, **kwargs)
+        if cpt % 10 == 0:
+            err = np.linalg.norm(T - Tprev)
+            hist["err"].append(err)
+        cpt += 1
+    if abs(np.sum(T) - 1) > 1e-5:
+        warnings.warn("Solver failed to produce a transport plan. You might "
+                      "want to increase the regularization parameter `epsilon`.")
+    if log:
+        hist["gw_dist"] = np.sum(tensor_product(constC, hC1, hC2, T) * T)
+        return T, hist
+    return T

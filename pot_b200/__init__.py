@@ -14,7 +14,7 @@ from . import _lib
 
 _lib.load()  # fail loudly when the CUDA library is missing
 
-from . import batch, bregman, empirical, host, sharded, solvers, stabilized, unbalanced, utils  # noqa: E402
+from . import batch, bregman, empirical, gromov, host, sharded, solvers, stabilized, unbalanced, utils  # noqa: E402
 from .batch import solve_batch  # noqa: E402
 from .empirical import dist, empirical_sinkhorn, empirical_sinkhorn2, empirical_sinkhorn_divergence  # noqa: E402
 from .solvers import solve, solve_sample  # noqa: E402
@@ -33,5 +33,5 @@ from .bregman import sinkhorn, sinkhorn2, sinkhorn_knopp, sinkhorn_log  # noqa: 
 __version__ = "0.1.0"
 __all__ = ["batch", "bregman", "empirical", "host", "sharded", "utils", "sinkhorn", "sinkhorn2", "sinkhorn_knopp",
            "sinkhorn_log", "solve_batch", "dist", "empirical_sinkhorn", "empirical_sinkhorn2",
-           "empirical_sinkhorn_divergence", "solve", "solve_sample", "solvers", "stabilized", "unbalanced", "sinkhorn_unbalanced",
+           "empirical_sinkhorn_divergence", "solve", "solve_sample", "solvers", "stabilized", "gromov", "unbalanced", "sinkhorn_unbalanced",
            "LazyTensor", "OTResult"]

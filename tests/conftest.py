@@ -62,3 +62,9 @@ def gs():
 def gstab():
     """Golden vectors of sinkhorn_stabilized / sinkhorn_epsilon_scaling: golden_stabilized.npz."""
     return Golden(os.path.join(GOLDEN_DIR, "golden_stabilized.npz"))
+
+
+@pytest.fixture(scope="session")
+def ggw():
+    """Golden vectors of entropic_gromov_wasserstein: golden_gromov.npz."""
+    return Golden(os.path.join(GOLDEN_DIR, "golden_gromov.npz"))

@@ -2,7 +2,8 @@
 
 numpy restatement of the reference's `ot.solve` / `ot.solve_sample` Sinkhorn branches, the lazy
 `empirical_sinkhorn2` loss, `empirical_sinkhorn_divergence`, `sinkhorn_knopp_unbalanced`,
-`sinkhorn_stabilized`, `sinkhorn_epsilon_scaling` and `entropic_gromov_wasserstein`.  Only ``tests/`` may import it; nothing under ``pot_b200/`` does.
+`sinkhorn_stabilized`, `sinkhorn_epsilon_scaling`, `entropic_gromov_wasserstein` and `solve_gromov_batch`
+(SURVEY.md section 8f, ranks 1-4).  Only ``tests/`` may import it; nothing under ``pot_b200/`` does.
 
 Parity status: PINNED.  ``tests/golden/make_golden_solvers.py`` ran the unmodified reference (imported from
 /root/reference in the build container) on seeded inputs and committed its outputs as
@@ -19,7 +20,7 @@ from . import sinkhorn_oracle as so
 
 __all__ = ["solve", "solve_sample_lazy", "empirical_sinkhorn2_lazy", "empirical_sinkhorn_divergence_lazy",
            "sinkhorn_knopp_unbalanced", "solve_unbalanced", "sinkhorn_stabilized", "sinkhorn_epsilon_scaling",
-           "entropic_gromov_wasserstein"]
+           "entropic_gromov_wasserstein", "solve_gromov_batch"]
 
 
 def _kl_div(p, q, eps=1e-16):
@@ -396,3 +397,75 @@ def entropic_gromov_wasserstein(C1, C2, p=None, q=None, loss_fun="square_loss", 
         hist["gw_dist"] = np.sum(tensor_product(constC, hC1, hC2, T) * T)
         return T, hist
     return T
+
+
+def solve_gromov_batch(C1, C2, reg=1e-2, a=None, b=None, loss="sqeuclidean", symmetric=None, M=None, alpha=None,
+                       T_init=None, max_iter=50, tol=1e-5, max_iter_inner=50, tol_inner=1e-5, logits=None):
+    """ot.batch.solve_gromov_batch (ot/batch/_quadratic.py:269-498) on the oracle's bregman_log_projection_batch.
+
+    tensor_batch :17-152 / compute_tensor_batch :504-532, tensor_product_batch :535-572, proximal loop :456-470,
+    values :479-495.  Returns a dict with plan, value, value_linear (x (1 - alpha)), value_quad (x alpha), n_iter.
+    """
+    C1, C2 = np.asarray(C1), np.asarray(C2)
+    B, n, m = C1.shape[0], C1.shape[1], C2.shape[1]
+    a = np.ones((B, n), dtype=C1.dtype) / n if a is None else np.asarray(a)
+    b = np.ones((B, m), dtype=C2.dtype) / m if b is None else np.asarray(b)
+
+    def tr(C):
+        return np.transpose(C, (0, 2, 1)) if C.ndim == 3 else np.transpose(C, (0, 2, 1, 3))
+
+    if symmetric is None:
+        symmetric = np.allclose(C1, tr(C1), atol=1e-10) and np.allclose(C2, tr(C2), atol=1e-10)
+    if loss == "sqeuclidean":
+        fC1 = np.sum(C1 ** 2, axis=-1) if C1.ndim == 4 else C1 ** 2
+        fC2 = np.sum(C2 ** 2, axis=-1) if C2.ndim == 4 else C2 ** 2
+        hC1 = 2 * (C1[..., None] if C1.ndim == 3 else C1)
+        hC2 = C2[..., None] if C2.ndim == 3 else C2
+    elif loss == "kl":
+        fC1 = np.zeros((B, n, n), dtype=C1.dtype)
+        fC2 = np.sum(C2 * np.log(C2 + 1e-15), axis=-1)
+        hC1 = C1 if logits else np.log(C1 + 1e-15)
+        hC2 = C2
+    else:
+        raise ValueError(f"Unknown loss function: {loss}")
+    if not symmetric:
+        fC1 = 0.5 * (fC1 + tr(fC1))
+        fC2 = 0.5 * (fC2 + tr(fC2))
+
+    def const_from(pa, pb):
+        return np.einsum("bij,bj->bi", fC1, pa)[:, :, None] + np.einsum("bij,bj->bi", fC2, pb)[:, None, :]
+
+    constC = const_from(a, b)
+
+    def product(T, recompute_const):
+        const = const_from(np.sum(T, axis=2), np.sum(T, axis=1)) if recompute_const else constC
+        dot = np.einsum("bijd,bjk->bikd", hC1, T)
+        dot = np.sum(np.einsum("bikd,bjkd->bijd", dot, hC2), axis=-1)
+        if not symmetric:
+            dot_t = np.einsum("bijd,bjk->bikd", tr(hC1), T)
+            dot_t = np.sum(np.einsum("bikd,bjkd->bijd", dot_t, tr(hC2)), axis=-1)
+            dot = (dot + dot_t) / 2
+        return const - dot
+
+    if M is None and alpha is None:
+        M = np.zeros((B, n, m), dtype=C1.dtype)
+        alpha = 1.0
+    if T_init is None:
+        const = np.sqrt(np.sum(a, axis=1) * np.sum(b, axis=1))
+        T_init = np.einsum("bi,bj->bij", a, b) / const[:, None, None]
+    T = T_init
+    log_T = np.log(T + 1e-15)
+    it = 0
+    for it in range(max_iter):
+        T_prev = T
+        Mk = (1 - alpha) * M + 2 * alpha * product(T, False)
+        K = -Mk / reg + log_T
+        out = so.bregman_log_projection_batch(K, a, b, max_iter=max_iter_inner, tol=tol_inner)
+        T, log_T = out["T"], out["log_T"]
+        if np.max(np.mean(np.abs(T_prev - T), axis=(1, 2))) < tol:
+            break
+    value_linear = np.sum(M * T, axis=(1, 2))
+    value_quadratic = np.sum(product(T, True) * T, axis=(1, 2))
+    return {"plan": T, "value": (1 - alpha) * value_linear + alpha * value_quadratic,
+            "value_linear": value_linear * (1 - alpha), "value_quad": value_quadratic * alpha, "n_iter": it,
+            "potentials": out["potentials"]}

@@ -15,7 +15,12 @@ from . import _lib
 _lib.load()  # fail loudly when the CUDA library is missing
 
 from . import batch, bregman, empirical, gromov, host, sharded, solvers, stabilized, unbalanced, utils  # noqa: E402
+from . import batch_quadratic  # noqa: E402
 from .batch import solve_batch  # noqa: E402
+
+# the reference exposes the quadratic solvers under ot.batch as well
+for _name in batch_quadratic.__all__:
+    setattr(batch, _name, getattr(batch_quadratic, _name))
 from .empirical import dist, empirical_sinkhorn, empirical_sinkhorn2, empirical_sinkhorn_divergence  # noqa: E402
 from .solvers import solve, solve_sample  # noqa: E402
 from .unbalanced import sinkhorn_unbalanced  # noqa: E402

@@ -68,3 +68,9 @@ def gstab():
 def ggw():
     """Golden vectors of entropic_gromov_wasserstein: golden_gromov.npz."""
     return Golden(os.path.join(GOLDEN_DIR, "golden_gromov.npz"))
+
+
+@pytest.fixture(scope="session")
+def ggwb():
+    """Golden vectors of ot.batch.solve_gromov_batch: golden_gromov_batch.npz."""
+    return Golden(os.path.join(GOLDEN_DIR, "golden_gromov_batch.npz"))

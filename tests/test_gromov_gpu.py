@@ -15,7 +15,7 @@ if torch.cuda.is_available():
     import pot_b200 as ot
 from oracle import solvers_oracle as sorc
 from test_oracle_gromov import CASES, INNER, gw_kwargs
-from test_solvers_gpu import assert_plan, assert_scalar, npf, to_dev
+from test_solvers_gpu import assert_plan, assert_scalar, to_dev
 
 DEV = "cuda:0"
 

@@ -13,9 +13,36 @@ static const int kColSplit = 32;
 
 extern "C" size_t b2ot_dense_plan_value_scratch_bytes(int64_t, int64_t) { return 3 * kPvBlocks * sizeof(double); }
 
+// the callers' combinations get branch-free instantiations (value_kernels.cuh, SPEC); anything else the generic kernel
 template <typename T, int MODE>
 static int launch_plan_value(const PlanValueParams& p, bool vect, double* values, cudaStream_t s) {
-  if (vect)
+  const int spec = (p.terms & 15) | (p.K ? PV_SPEC_K : 0) | (p.C ? PV_SPEC_C : 0) | (p.out ? PV_SPEC_OUT : 0);
+#define B2OT_PV_CASE(SP) \
+  case SP:               \
+    plan_value_kernel<T, MODE, true, SP><<<p.nblk, 256, 0, s>>>(p); \
+    break;
+  bool done = vect;
+  if (vect) {
+    if (MODE == MODE_LOG) {
+      switch (spec) {
+        B2OT_PV_CASE(PV_LINEAR | PV_KL | PV_SPEC_OUT)       // ot.solve, KL regulariser: M in, plan out
+        B2OT_PV_CASE(PV_LINEAR | PV_ENTROPY | PV_SPEC_OUT)  // ot.solve, entropy regulariser
+        B2OT_PV_CASE(PV_SPEC_K | PV_SPEC_OUT)               // plan (+ row marginal) from Mr: epsilon scaling
+        default:
+          done = false;
+      }
+    } else {
+      switch (spec) {
+        B2OT_PV_CASE(PV_SPEC_K | PV_LINEAR | PV_KL | PV_SPEC_OUT)  // unbalanced: plan, cost, KL(plan, a b^T)
+        B2OT_PV_CASE(PV_KMULQ | PV_SPEC_OUT)                       // K = exp(-M/reg) * a b^T
+        default:
+          done = false;
+      }
+    }
+  }
+#undef B2OT_PV_CASE
+  if (done) {
+  } else if (vect)
     plan_value_kernel<T, MODE, true><<<p.nblk, 256, 0, s>>>(p);
   else
     plan_value_kernel<T, MODE, false><<<p.nblk, 256, 0, s>>>(p);

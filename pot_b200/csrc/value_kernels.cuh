@@ -100,9 +100,15 @@ __device__ __forceinline__ double block_sum_256(double x, double* sred) {
   return t;  // valid in thread 0
 }
 
-template <typename T, int MODE, bool VECT>
+// SPEC >= 0: the per-element conditions are compile-time constants (straight-line code per vector, no branches inside
+// the element loop): bits 0-3 = terms, 16 = K given, 32 = reference matrix given, 64 = plan written.  SPEC = -1: read
+// them from the parameters (any combination).
+constexpr int PV_SPEC_K = 16, PV_SPEC_C = 32, PV_SPEC_OUT = 64;
+
+template <typename T, int MODE, bool VECT, int SPEC = -1>
 __global__ void __launch_bounds__(256) plan_value_kernel(const PlanValueParams p) {
   constexpr int VEC = VECT ? Vec<T>::N : 1;
+  constexpr bool CT = SPEC >= 0;
   __shared__ double sred[8];
   const T* K = reinterpret_cast<const T*>(p.K);
   const T* M = reinterpret_cast<const T*>(p.M);
@@ -113,23 +119,35 @@ __global__ void __launch_bounds__(256) plan_value_kernel(const PlanValueParams p
   const T* b = reinterpret_cast<const T*>(p.b);
   T* out = reinterpret_cast<T*>(p.out);
   T* rowsum = reinterpret_cast<T*>(p.rowsum);
-  const bool need_m = (p.terms & PV_LINEAR) || K == nullptr;
-  const bool need_q = (p.terms & PV_KL) || ((p.terms & PV_KMULQ) && K == nullptr);
+  const int terms = CT ? (SPEC & 15) : p.terms;
+  const bool hasK = CT ? ((SPEC & PV_SPEC_K) != 0) : (K != nullptr);
+  const bool hasC = CT ? ((SPEC & PV_SPEC_C) != 0) : (Cq != nullptr);
+  const bool hasOut = CT ? ((SPEC & PV_SPEC_OUT) != 0) : (out != nullptr);
+  const bool need_m = (terms & PV_LINEAR) || !hasK;
+  const bool need_q = (terms & PV_KL) || ((terms & PV_KMULQ) && !hasK);
   const T reg = (T)p.reg;
+  // x / reg as x * (1/reg) with one FMA refinement step (Markstein): the correctly rounded quotient except in rare
+  // one-ulp cases, without the IEEE division's special-case path (a quarter of this kernel's instructions); one ulp of
+  // -M/reg moves a plan entry by < 1e-5 relative in fp32, 1e-14 in fp64
+  const T rinv = (T)1 / reg;
+  auto div_reg = [&](T x) {
+    const T q = x * rinv;
+    return fma(fma(-q, reg, x), rinv, q);
+  };
   double s_lin = 0.0, s_ent = 0.0, s_kl = 0.0;
   for (long long i = blockIdx.x; i < p.n; i += gridDim.x) {
     const T ui = u[i];
-    const T ai = (need_q && Cq == nullptr) ? a[i] : (T)0;
+    const T ai = (need_q && !hasC) ? a[i] : (T)0;
     // per-row partial sums in T (at most m / 256 terms per thread), folded into the double accumulators once per row
     T r_sum = (T)0, r_lin = (T)0, r_ent = (T)0, r_kl = (T)0;
 #pragma unroll(sizeof(T) == 4 ? 2 : 1)  // fp64 is FP64-pipe bound: unrolling only costs occupancy there
     for (long long j = (long long)threadIdx.x * VEC; j < p.m; j += 256LL * VEC) {
       T kx[VEC], mx[VEC], vx[VEC], qx[VEC], px[VEC];
       load_vec<T, VEC>(v + j, vx);
-      if (K != nullptr) load_vec_stream<T, VEC>(K + i * p.ldK + j, kx);
+      if (hasK) load_vec_stream<T, VEC>(K + i * p.ldK + j, kx);
       if (need_m) load_vec_stream<T, VEC>(M + i * p.ldM + j, mx);
       if (need_q) {
-        if (Cq != nullptr) {
+        if (hasC) {
           load_vec_stream<T, VEC>(Cq + i * p.ldC + j, qx);
         } else {
           load_vec<T, VEC>(b + j, qx);
@@ -140,22 +158,22 @@ __global__ void __launch_bounds__(256) plan_value_kernel(const PlanValueParams p
 #pragma unroll
       for (int e = 0; e < VEC; ++e) {
         T k;
-        if (K != nullptr) {
+        if (hasK) {
           k = kx[e];
         } else if (MODE == MODE_LOG) {
-          k = (-mx[e]) / reg;
+          k = div_reg(-mx[e]);
         } else {
-          k = exp_t(mx[e] / (-reg));
-          if (p.terms & PV_KMULQ) k = k * qx[e];
+          k = exp_t(-div_reg(mx[e]));
+          if (terms & PV_KMULQ) k = k * qx[e];
         }
         const T g = (MODE == MODE_KNOPP) ? (ui * k) * vx[e] : exp_t((k + ui) + vx[e]);
         px[e] = g;
         r_sum += g;
-        if (p.terms & PV_LINEAR) r_lin = fma(mx[e], g, r_lin);
-        if (p.terms & PV_ENTROPY) r_ent = fma(g, log_red(g + eps16<T>()), r_ent);
-        if (p.terms & PV_KL) r_kl = fma(g, log_red(div_red(g, qx[e]) + eps16<T>()), r_kl);
+        if (terms & PV_LINEAR) r_lin = fma(mx[e], g, r_lin);
+        if (terms & PV_ENTROPY) r_ent = fma(g, log_red(g + eps16<T>()), r_ent);
+        if (terms & PV_KL) r_kl = fma(g, log_red(div_red(g, qx[e]) + eps16<T>()), r_kl);
       }
-      if (out != nullptr) store_vec_stream<T, VEC>(out + i * p.ldO + j, px);
+      if (hasOut) store_vec_stream<T, VEC>(out + i * p.ldO + j, px);
     }
     s_lin += (double)r_lin;
     s_ent += (double)r_ent;

@@ -104,6 +104,10 @@ __device__ __forceinline__ double block_sum_256(double x, double* sred) {
 // the element loop): bits 0-3 = terms, 16 = K given, 32 = reference matrix given, 64 = plan written.  SPEC = -1: read
 // them from the parameters (any combination).
 constexpr int PV_SPEC_K = 16, PV_SPEC_C = 32, PV_SPEC_OUT = 64;
+#ifndef B2OT_PV_UNROLL
+#define B2OT_PV_UNROLL 2
+#endif
+constexpr int kPvUnroll = B2OT_PV_UNROLL;  // column vectors per thread and trip in fp32
 
 template <typename T, int MODE, bool VECT, int SPEC = -1>
 __global__ void __launch_bounds__(256) plan_value_kernel(const PlanValueParams p) {
@@ -140,7 +144,7 @@ __global__ void __launch_bounds__(256) plan_value_kernel(const PlanValueParams p
     const T ai = (need_q && !hasC) ? a[i] : (T)0;
     // per-row partial sums in T (at most m / 256 terms per thread), folded into the double accumulators once per row
     T r_sum = (T)0, r_lin = (T)0, r_ent = (T)0, r_kl = (T)0;
-#pragma unroll(sizeof(T) == 4 ? 2 : 1)  // fp64 is FP64-pipe bound: unrolling only costs occupancy there
+#pragma unroll(sizeof(T) == 4 ? kPvUnroll : 1)  // fp64 is FP64-pipe bound: unrolling only costs occupancy there
     for (long long j = (long long)threadIdx.x * VEC; j < p.m; j += 256LL * VEC) {
       T kx[VEC], mx[VEC], vx[VEC], qx[VEC], px[VEC];
       load_vec<T, VEC>(v + j, vx);

@@ -817,10 +817,11 @@ static int launch_finalize(const b2ot_dense* h, int nsrc, int init, int gate_reb
   p.gate_rebuild = gate_rebuild;
   int blocks = h->tau > 0.0 ? std::min(h->fin_blocks, 512) : h->fin_blocks;  // second half of blk_err: scaled error
   static const int qsplit_env = [] {
-    const char* e = getenv("B2OT_FIN_QSPLIT");  // diagnosis: 0 = never, 1 = rule below (default)
+    const char* e = getenv("B2OT_FIN_QSPLIT");  // diagnosis: 0 = never, 1 = rule below (default), 2 = m <= 32768, 3 = m <= 4096
     return e ? atoi(e) : 1;
   }();
-  if (qsplit_env && !p.use_comm && p.nsrc >= 16 && h->m <= 4096) {  // small problem: spread the partial-row walk over 8 warps
+  const long long qsplit_m = (qsplit_env == 2) ? 32768 : (qsplit_env == 3 ? 4096 : ((h->mode == B2OT_MODE_LOG && h->pp_vpt > 0) ? 4096 : 32768));
+  if (qsplit_env && !p.use_comm && p.nsrc >= 16 && h->m <= qsplit_m) {  // small problem: spread the partial-row walk over 8 warps
     p.qsplit = 1;
     blocks = (int)std::min<long long>((h->m + 31) / 32, h->tau > 0.0 ? 512 : 1024);
   }

@@ -6,7 +6,10 @@ from pot_b200 import _dense, _lib
 n = 16384
 dev = "cuda:0"
 out = {"qsplit": os.environ.get("B2OT_FIN_QSPLIT", "default")}
-for mode, dt in (("knopp", torch.float32), ("knopp", torch.float64), ("log", torch.float32)):
+CASES = (("knopp", torch.float32), ("knopp", torch.float64), ("log", torch.float32))
+if os.environ.get("AB_CASES") == "log64":
+    CASES = (("log", torch.float64),)
+for mode, dt in CASES:
     g = torch.Generator(device=dev).manual_seed(0)
     M = torch.rand(n, n, device=dev, generator=g, dtype=dt)
     K = _dense.cost_transform(M, 0.05, "kexp" if mode == "knopp" else "negscale")

@@ -73,15 +73,16 @@ def _print_table(errs, check_every=10, after_stop_test=True, stop_thr=None):
         print("{:5d}|{:8e}|".format(ii, e))
 
 
-def _solve_dense(mode, a, b, M, reg, numItermax, stopThr, warmstart, variant="auto"):
-    """Shared driver.  Returns (K_or_Mr, u, v, errs, niter, status)."""
+def _solve_dense(mode, a, b, M, reg, numItermax, stopThr, warmstart, variant="auto", Kt=None):
+    """Shared driver.  Returns (K_or_Mr, u, v, errs, niter, status).  `Kt`: an already transformed cost to reuse."""
     from . import _lib
 
     n, m = M.shape
     Mc = _rowmajor(M)
     with torch.cuda.device(M.device):
         if mode == "knopp":
-            Kt = _dense.cost_transform(Mc, reg, "kexp")
+            if Kt is None:
+                Kt = _dense.cost_transform(Mc, reg, "kexp")
             if warmstart is None:
                 u0 = torch.full((n,), 1.0 / n, dtype=M.dtype, device=M.device)
                 v0 = torch.full((m,), 1.0 / m, dtype=M.dtype, device=M.device)
@@ -90,7 +91,8 @@ def _solve_dense(mode, a, b, M, reg, numItermax, stopThr, warmstart, variant="au
                 v0 = torch.exp(warmstart[1].to(M.dtype)).contiguous()
             av, logb = a, None
         else:
-            Kt = _dense.cost_transform(Mc, reg, "negscale")
+            if Kt is None:
+                Kt = _dense.cost_transform(Mc, reg, "negscale")
             if warmstart is None:
                 u0 = torch.zeros(n, dtype=M.dtype, device=M.device)
                 v0 = torch.zeros(m, dtype=M.dtype, device=M.device)
@@ -169,23 +171,37 @@ def _multi_hist(fn, a, b, M, reg, numItermax, stopThr, verbose, log, warn, warms
 
     The reference's knopp runs the histograms jointly (joint stop test on the stacked error);
     here each histogram stops on its own error, which is identical for a fixed iteration count.
+    The transformed cost (K or -M/reg) is built once and shared by all histograms; each loss <M, plan> is reduced
+    straight from (K, u, v) by the loss kernel, no plan is materialised.
     """
+    from . import _lib
+
     k_h = b.shape[1]
+    is_log = fn is sinkhorn_log
+    mode = "log" if is_log else "knopp"
     ws = warmstart if warmstart is not None else [None] * k_h
-    if warmstart is not None and fn is sinkhorn_knopp:
+    if warmstart is not None and not is_log:
         ws = [(warmstart[0][:, k], warmstart[1][:, k]) for k in range(k_h)]
+    variant = kwargs.get("b2ot_variant", "auto")
+    Mc = _rowmajor(M)
+    Kt = None
     losses, us, vs = [], [], []
     for k in range(k_h):
-        G, lg = fn(a, b[:, k].contiguous(), M, reg, numItermax=numItermax, stopThr=stopThr, verbose=verbose,
-                   log=True, warn=warn, warmstart=ws[k], **kwargs)
-        losses.append(torch.sum(M * G))
-        key = "log_u" if "log_u" in lg else "u"
-        us.append(lg[key])
-        vs.append(lg["log_v" if "log_u" in lg else "v"])
+        Kt, u, v, errs, niter, status = _solve_dense(mode, a, b[:, k].contiguous(), M, reg, int(numItermax),
+                                                     float(stopThr), ws[k], variant, Kt=Kt)
+        if status == _lib.ST_NUMERR:
+            warnings.warn("Warning: numerical errors at iteration %d" % niter)
+        elif status == _lib.ST_MAXITER and warn:
+            warnings.warn(_NOCONV)
+        if verbose:
+            _print_table(errs, after_stop_test=not is_log, stop_thr=None if is_log else stopThr)
+        losses.append(_dense.loss(mode, Kt, Mc, u, v).to(M.dtype))
+        us.append(u)
+        vs.append(v)
     res = torch.stack(losses)
     if not log:
         return res
-    if fn is sinkhorn_log:
+    if is_log:
         out = {"log_u": torch.stack(us, 1), "log_v": torch.stack(vs, 1)}
         out["u"], out["v"] = torch.exp(out["log_u"]), torch.exp(out["log_v"])
     else:

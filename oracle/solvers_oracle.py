@@ -3,7 +3,8 @@
 numpy restatement of the reference's `ot.solve` / `ot.solve_sample` Sinkhorn branches, the lazy
 `empirical_sinkhorn2` loss, `empirical_sinkhorn_divergence`, `sinkhorn_knopp_unbalanced`,
 `sinkhorn_stabilized`, `sinkhorn_epsilon_scaling`, `entropic_gromov_wasserstein` and `solve_gromov_batch`
-(SURVEY.md section 8f, ranks 1-4).  Only ``tests/`` may import it; nothing under ``pot_b200/`` does.
+(SURVEY.md section 8f, ranks 1-4).  Only ``tests/`` (the parity tests and the CPU legs of the measurement helpers ``tests/perf_*.py`` / ``tests/diag_*.py``) may
+import it; nothing under ``pot_b200/`` does.
 
 Parity status: PINNED.  ``tests/golden/make_golden_solvers.py`` ran the unmodified reference (imported from
 /root/reference in the build container) on seeded inputs and committed its outputs as

@@ -1,7 +1,7 @@
 """GPU bring-up diagnostics (run under gpurun): parity of every sweep variant against the CPU oracle
 on a grid of shapes, plus a quick throughput probe.  Not part of the pytest suite.
 
-    python scripts/gpu_diag.py --group split|fused1|cluster|perf [--quick]
+    python tests/gpu_diag.py --group split|fused1|cluster|perf [--quick]
 """
 
 import argparse

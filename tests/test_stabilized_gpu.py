@@ -112,7 +112,7 @@ def test_epsilon_scaling_golden(gstab, name):
     # Tolerance: the stages start at reg = epsilon0 = 1e4, where the absorbed potentials are alpha ~ -eps0 log n,
     # beta ~ +eps0 log m (3.7e4 here); every later get_K cancels them in M - alpha - beta, an absolute rounding noise of
     # ~4e-12 that the last stages divide by reg = 0.01.  The reference's own result is therefore defined to ~5e-10
-    # relative only (scripts/diag_eps.py: a single stage from identical potentials already differs by 1e-11 / reg);
+    # relative only (tests/diag_eps.py: a single stage from identical potentials already differs by 1e-11 / reg);
     # 40 chained stages are compared at 5e-8.
     tol = 5e-8 if name == "f64" else 1e-9
     assert_plan(G, gstab(case, "plan"), tol)

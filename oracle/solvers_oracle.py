@@ -3,12 +3,15 @@
 numpy restatement of the reference's `ot.solve` / `ot.solve_sample` Sinkhorn branches, the lazy
 `empirical_sinkhorn2` loss, `empirical_sinkhorn_divergence`, `sinkhorn_knopp_unbalanced`,
 `sinkhorn_stabilized`, `sinkhorn_epsilon_scaling`, `entropic_gromov_wasserstein` and `solve_gromov_batch`
-(SURVEY.md section 8f, ranks 1-4).  Only ``tests/`` (the parity tests and the CPU legs of the measurement helpers ``tests/perf_*.py`` / ``tests/diag_*.py``) may
-import it; nothing under ``pot_b200/`` does.
+(SURVEY.md section 8f, ranks 1-4).  Only ``tests/`` (the parity tests and the CPU legs of the measurement helpers
+``tests/perf_*.py`` / ``tests/diag_*.py``) may import it; nothing under ``pot_b200/`` does.
 
 Parity status: PINNED.  ``tests/golden/make_golden_solvers.py`` ran the unmodified reference (imported from
 /root/reference in the build container) on seeded inputs and committed its outputs as
-``tests/golden/golden_solvers.npz``; ``tests/test_oracle_solvers.py`` checks every function below against them.
+``tests/golden/golden_solvers.npz``; ``make_golden_stabilized.py``, ``make_golden_gromov.py`` and
+``make_golden_gromov_batch.py`` did the same for ``golden_stabilized.npz``, ``golden_gromov.npz`` and
+``golden_gromov_batch.npz``.  ``tests/test_oracle_solvers.py``, ``test_oracle_stabilized.py``, ``test_oracle_gromov.py`` and
+``test_oracle_gromov_batch.py`` check every function below against them.
 
 Each function cites the reference file:line (relative to /root/reference) it restates.
 """

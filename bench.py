@@ -1,22 +1,30 @@
 #!/usr/bin/env python
-"""Headline benchmark: dense fp32 Sinkhorn-Knopp iterations/sec at n=m=65536, row-sharded over N B200s.
+"""Benchmarks of the entropic Sinkhorn hot path, one BASELINE.json config per run (default: config 3, the headline).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--n 65536]
+    python bench.py [--config 1|2|3|4|5] [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
-        bench.py --gpus N --steps K --warmup W
+        bench.py --gpus N --steps K --warmup W [--config C]
 
-Workload (BASELINE.json configs[2], the configuration the metric is quoted on): 2-D Gaussian point clouds
-(seed 0, target cloud shifted by +1), M = squared euclidean cost / max(M), uniform weights, reg = 0.05,
-ot.bregman.sinkhorn_knopp with a fixed iteration count (stopThr = 0).  A "step" is one Sinkhorn
-iteration = one fused sweep over this rank's rows of K = exp(-M/reg) + the all-reduce of K^T u (N > 1)
-+ the finalize kernel.  K (16 GiB) is far larger than the 126 MB L2, so every iteration streams from HBM.
+  config 1  ot.sinkhorn fp64 n=m=1000, reg 0.05 (the reference's own CPU-runnable case), public call
+  config 2  ot.bregman.sinkhorn_log fp32 n=m=16384, reg 0.01
+  config 3  ot.bregman.sinkhorn_knopp fp32 n=m=65536 (K = 16 GiB), rows sharded over the ranks   [DEFAULT, the metric]
+  config 4  ot.bregman.empirical_sinkhorn (online cost, log domain) n=m=262144, d=64, fp32, source points sharded
+  config 5  ot.batch.solve_batch, 4096 problems of 256x256 fp32, problems sharded, no communication
 
-value : iterations/s with K resident in HBM, CUDA events on the launch stream, max over ranks.
-e2e   : iterations/s of one whole solve of K iterations through pot_b200.host.sinkhorn_from_host with M in
-        pinned HOST memory: host->device upload of M (overlapped with the Gibbs-kernel transform), the solve,
-        and the device->host read of (u, v, err) are all inside the timed region.
---impl reference: the CPU restatement of the reference's numpy path (oracle/sinkhorn_oracle.py, same
-        np.dot / np.exp calls as ot/bregman/_sinkhorn.py:621-631) on the host cores, on a bounded row sample.
+A "step" is one Sinkhorn iteration of the whole problem (config 5: of all 4096 problems).  Every config prints ONE JSON
+line from rank 0 with the same schema:
+
+value        : iterations/s with the inputs resident in HBM, CUDA events on the launch stream, max over ranks.
+e2e          : iterations/s of one whole solve of K iterations through the public host-buffer entry point: the
+               host->device upload of the inputs from pinned memory, the solve, and the device->host read of the result
+               are all inside the timed region.
+roofline     : dominant kernel of the config, launch duration measured live with CUDA events on the launch stream.
+cpu_baseline : (N = 1, rank 0) the REFERENCE ITSELF (oracle/_ref = unmodified POT built from /root/reference by
+               oracle/build_ref.py, kind "reference"; the numpy restatement oracle/ only if that tree is missing, kind
+               "port") on the host cores, on a bounded sample of the same workload.
+reference_torch_cuda : (N = 1, informative) the reference's own torch backend on the same B200 (its only GPU path).
+--impl reference : the CPU arm alone, same config / metric / unit; BLAS threads forced to all host cores and the
+               count actually used is printed (torchrun exports OMP_NUM_THREADS=1).
 """
 
 import argparse
@@ -31,41 +39,80 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-REG = 0.05
 SEED = 0
-D = 2
+DEFAULT_STEPS = {1: 1000, 2: 100, 3: 100, 4: 10, 5: 100}
+METRIC = {1: "sinkhorn_iterations_per_sec", 2: "sinkhorn_log_iterations_per_sec",
+          3: "sinkhorn_knopp_iterations_per_sec", 4: "empirical_sinkhorn_iterations_per_sec",
+          5: "batch_sinkhorn_iterations_per_sec"}
+DTYPE = {1: "f64", 2: "f32", 3: "f32", 4: "f32", 5: "f32"}
+REG = {1: 0.05, 2: 0.01, 3: 0.05, 4: 0.1, 5: 0.1}
+
+
+def workload(cfg, n):
+    """One description per config, shared by both arms (so the driver compares like with like)."""
+    if cfg == 1:
+        return (f"ot.sinkhorn (sinkhorn_knopp) dense fp64 n=m={n}, sqeuclidean M (un-normalised), reg=0.05, uniform "
+                "weights, 2-D Gaussian clouds (seed 0), fixed iterations (stopThr=0)")
+    if cfg == 2:
+        return (f"ot.bregman.sinkhorn_log dense fp32 n=m={n} (M = {4 * n * n / 2 ** 30:.2f} GiB), M/=max, reg=0.01, "
+                "uniform weights, 2-D Gaussian clouds (seed 0), fixed iterations (stopThr=0)")
+    if cfg == 3:
+        return (f"ot.bregman.sinkhorn_knopp dense fp32 n=m={n} (K = {4 * n * n / 2 ** 30:.0f} GiB), "
+                "reg=0.05, uniform weights, 2-D Gaussian clouds (seed 0), fixed iterations (stopThr=0)")
+    if cfg == 4:
+        return (f"ot.bregman.empirical_sinkhorn isLazy (online cost, log domain) n=m={n} points, d=64, fp32, X/=sqrt(d), "
+                "reg=0.1, uniform weights, fixed iterations (stopThr=-1), M never materialised")
+    return (f"ot.batch.solve_batch {n} independent 256x256 fp32 problems (2-D Gaussian clouds per problem, M/=max), "
+            "reg=0.1, solver=log_sinkhorn, reg_type=entropy, fixed iterations (tol=0)")
+
+
+def default_n(cfg):
+    return {1: 1000, 2: 16384, 3: 65536, 4: 262144, 5: 4096}[cfg]
 
 
 # ------------------------------------------------------------------------------------------------
 def parse_args():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--config", type=int, default=3, choices=[1, 2, 3, 4, 5])
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--steps", type=int, default=None)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=65536, help="problem size n = m (default: the headline 65536)")
+    ap.add_argument("--n", type=int, default=None, help="problem size (n = m; config 5: number of problems)")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
-                    help="N > 1: per-iteration exchange of K^T u (peer = fused NVLink peer-memory exchange, "
+                    help="N > 1: per-iteration exchange (peer = fused NVLink peer-memory exchange, "
                          "nccl = torch.distributed all-reduce baseline)")
+    ap.add_argument("--operand", default="f16", choices=["f16", "tf32"],
+                    help="config 4: operand split of the tcgen05 cross term (f16 = 3xFP16 scaled split, tf32 = 3xTF32)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
-    return ap.parse_args()
+    ap.add_argument("--no-torch-ref", action="store_true")
+    a = ap.parse_args()
+    if a.steps is None:
+        a.steps = DEFAULT_STEPS[a.config]
+    if a.n is None:
+        a.n = default_n(a.config)
+    return a
 
 
 def peaks():
+    out = {"hbm_gbs": 6650.0, "bf16_tflops": 1500.0, "sm_max_mhz": 1965.0, "source": "fallback (B200_PROFILING.md)"}
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+            j = json.load(f)
+        out.update(hbm_gbs=float(j["hbm_gbs"]), bf16_tflops=float(j.get("bf16_tflops_sustained", j["bf16_tflops"])),
+                   sm_max_mhz=float(j.get("sm_max_mhz", 1965.0)), source="measured (MEASURED_PEAKS.json)")
     except Exception:
-        return 6650.0, "fallback (B200_PROFILING.md)"
+        pass
+    return out
 
 
-def point_clouds(n, m):
+def point_clouds(n, m, d=2):
     import numpy as np
 
     rng = np.random.RandomState(SEED)
-    xs = rng.randn(n, D).astype(np.float32)
-    xt = (rng.randn(m, D) + 1.0).astype(np.float32)
+    xs = rng.randn(n, d).astype(np.float32)
+    xt = (rng.randn(m, d) + 1.0).astype(np.float32)
     return xs, xt
 
 
@@ -114,52 +161,152 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
-# CPU baseline / reference arm: the oracle's numpy Sinkhorn-Knopp on a bounded row sample
+# CPU arm: the reference itself (oracle/_ref) on the host cores, bounded sample of the same workload
 # ------------------------------------------------------------------------------------------------
-def cpu_knopp_sample(n, m, rows, iters, warm):
-    """Times `iters` iterations of the reference's scaling-domain loop (K^T u GEMV, Kp v GEMV, guard test;
-    marginal check every 10th) on the sub-problem made of the first `rows` source points against all m
-    targets; returns full-problem iterations/s (per-iteration work scales with the row count)."""
-    import numpy as np
+def force_cpu_threads():
+    """All host cores for BLAS.  torchrun exports OMP_NUM_THREADS=1; OpenBLAS reads the environment when it is loaded,
+    so the variables are reset first and the pool size is then set explicitly.  Returns what is actually in use."""
+    ncpu = os.cpu_count() or 1
+    for k in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[k] = str(ncpu)
+    info = {"cpu_count": ncpu}
+    try:
+        import numpy  # noqa: F401
+        import threadpoolctl
 
-    from oracle import sinkhorn_oracle as orc
+        threadpoolctl.threadpool_limits(limits=ncpu)
+        pools = threadpoolctl.threadpool_info()
+        info["blas_threads"] = max([p.get("num_threads", 1) for p in pools if p.get("user_api") == "blas"] or [1])
+        info["blas"] = sorted({f"{p.get('internal_api')} {p.get('version')}" for p in pools if p.get("user_api") == "blas"})
+    except Exception as e:  # noqa: BLE001
+        info["blas_threads"] = None
+        info["note"] = f"threadpoolctl unavailable: {e}"
+    return info
 
-    xs, xt = point_clouds(n, m)
-    M = orc.sqeuclidean(xs[:rows], xt)
-    M = (M / M.max()).astype(np.float32)
-    a = np.full(rows, 1.0 / rows, dtype=np.float32)
-    b = np.full(m, 1.0 / m, dtype=np.float32)
+
+def load_reference():
+    """(`ot` module of the unmodified reference, "reference") or (None, "port") when oracle/_ref is not built."""
+    try:
+        from oracle.build_ref import import_ref
+
+        return import_ref(), "reference"
+    except Exception:
+        return None, "port"
+
+
+def _timed(fn):
+    t0 = time.perf_counter()
+    fn()
+    return time.perf_counter() - t0
+
+
+def _per_iteration(call, k1, k2, reps=2):
+    """Seconds per iteration from two fixed-iteration calls (setup / plan cost cancels): (t(k2) - t(k1)) / (k2 - k1)."""
+    best = None
+    for _ in range(reps):
+        t1, t2 = _timed(lambda: call(k1)), _timed(lambda: call(k2))
+        per = (t2 - t1) / (k2 - k1)
+        best = per if best is None else min(best, per)
+    return max(best, 1e-9)
+
+
+def cpu_arm(cfg, n, steps, warm):
+    """Returns the cpu_baseline object of config `cfg` (value = full-problem iterations/s on the host cores)."""
     import warnings
 
-    K = np.exp(M / (-REG))
-    Kp = (1 / a).reshape(-1, 1) * K
-    u = np.ones(rows, dtype=np.float32) / rows
-    v = np.ones(m, dtype=np.float32) / m
+    thr = force_cpu_threads()
+    import numpy as np
+
+    ot, kind = load_reference()
+    if ot is None:
+        from oracle import sinkhorn_oracle as orc
+    reg = REG[cfg]
+    k1 = max(1, min(warm, 3))
     with warnings.catch_warnings():
         warnings.simplefilter("ignore")
-        u, v, _, _ = orc.knopp_loop(K, Kp, b, u, v, max(1, warm), 0, {"err": []})
-        t0 = time.perf_counter()
-        orc.knopp_loop(K, Kp, b, u, v, iters, 0, {"err": []})
-        per_iter = (time.perf_counter() - t0) / iters
-    return (1.0 / per_iter) * (rows / n), per_iter, os.cpu_count()
+        if cfg == 1:
+            rng = np.random.RandomState(SEED)
+            x, y = rng.randn(n, 2), rng.randn(n, 2) + 1.0
+            its = 1000
+            if ot is not None:
+                M, a, b = ot.dist(x, y), ot.unif(n), ot.unif(n)
+                call = lambda: ot.sinkhorn(a, b, M, reg, numItermax=its, stopThr=0, warn=False)  # noqa: E731
+            else:
+                M, a, b = orc.sqeuclidean(x, y), np.ones(n) / n, np.ones(n) / n
+                call = lambda: orc.sinkhorn_knopp(a, b, M, reg, numItermax=its, stopThr=0, warn=False)  # noqa: E731
+            call()
+            t = statistics.median([_timed(call) for _ in range(5)])
+            value = its / t
+            sample = (f"the whole config: ot.sinkhorn(a, b, M, 0.05, numItermax=1000, stopThr=0), numpy backend, "
+                      f"1 warm-up + median of 5 calls, {t * 1e3:.1f} ms per call")
+        elif cfg in (2, 3):
+            rows = min(n, 2048 if cfg == 2 else 4096)
+            xs, xt = point_clouds(n, n)
+            if ot is not None:
+                M = ot.dist(xs[:rows].astype(np.float64), xt.astype(np.float64))
+            else:
+                M = orc.sqeuclidean(xs[:rows], xt)
+            M = (M / M.max()).astype(np.float32)
+            a = np.full(rows, 1.0 / rows, dtype=np.float32)
+            b = np.full(n, 1.0 / n, dtype=np.float32)
+            name = "sinkhorn_log" if cfg == 2 else "sinkhorn_knopp"
+            fn = getattr(ot.bregman, name) if ot is not None else getattr(orc, name)
+            call = lambda k: fn(a, b, M, reg, numItermax=k, stopThr=0, warn=False)  # noqa: E731
+            k2 = k1 + max(1, min(steps, 4 if cfg == 2 else 40))
+            per = _per_iteration(call, k1, k2)
+            value = (1.0 / per) * (rows / n)
+            sample = (f"ot.bregman.{name} (numpy backend) on the first {rows} of {n} rows (all {n} columns): "
+                      f"(t({k2} its) - t({k1} its)) / {k2 - k1} = {per * 1e3:.1f} ms per sample iteration, "
+                      f"scaled by {rows}/{n} (work per iteration is linear in the row count)")
+        elif cfg == 4:
+            ns = min(n, 8192)
+            rng = np.random.RandomState(SEED)
+            X = (rng.randn(ns, 64) / 8.0).astype(np.float32)
+            Y = (rng.randn(ns, 64) / 8.0 + 1.0 / 8.0).astype(np.float32)
+            if ot is not None:
+                call = lambda k: ot.bregman.empirical_sinkhorn(X, Y, reg, numIterMax=k, stopThr=-1.0, isLazy=True,  # noqa: E731
+                                                               warn=False)
+            else:
+                call = lambda k: orc.empirical_sinkhorn_lazy(X, Y, reg, numIterMax=k, stopThr=-1.0, warn=False)  # noqa: E731
+            k2 = k1 + max(1, min(steps, 2))
+            per = _per_iteration(call, k1, k2)
+            value = (1.0 / per) * (ns / n) ** 2
+            sample = (f"ot.bregman.empirical_sinkhorn(isLazy=True, batchSize=100 (default)), numpy backend, on "
+                      f"n=m={ns} of {n} points: (t({k2}) - t({k1})) / {k2 - k1} = {per * 1e3:.0f} ms per sample "
+                      f"iteration, scaled by ({ns}/{n})^2 (work per iteration is n*m)")
+        else:
+            Bs = min(n, 64)
+            rng = np.random.RandomState(SEED)
+            X, Y = rng.randn(Bs, 256, 2), rng.randn(Bs, 256, 2) + 1.0
+            Mb = (X ** 2).sum(-1)[:, :, None] + (Y ** 2).sum(-1)[:, None, :] - 2 * np.einsum("bid,bjd->bij", X, Y)
+            Mb = (Mb / Mb.max()).astype(np.float32)
+            if ot is not None:
+                call = lambda k: ot.batch.solve_batch(Mb, reg, max_iter=k, tol=0, solver="log_sinkhorn",  # noqa: E731
+                                                      reg_type="entropy")
+            else:
+                call = lambda k: orc.solve_batch(Mb, reg, max_iter=k, tol=0, solver="log_sinkhorn",  # noqa: E731
+                                                 reg_type="entropy")
+            k2 = k1 + max(1, min(steps, 10))
+            per = _per_iteration(call, k1, k2)
+            value = (1.0 / per) * (Bs / n)
+            sample = (f"ot.batch.solve_batch (numpy backend, log_sinkhorn) on {Bs} of {n} problems: "
+                      f"(t({k2}) - t({k1})) / {k2 - k1} = {per * 1e3:.1f} ms per sample iteration, scaled by {Bs}/{n}")
+    return {"value": value, "unit": "it/s", "cores": thr.get("blas_threads") or thr["cpu_count"], "kind": kind,
+            "sample": sample, "threads": thr}
 
 
 def reference_arm(args):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
+    if int(os.environ.get("RANK", "0")) != 0:
         return
-    n = m = args.n
-    rows = min(n, 4096)
-    its, per_iter, cores = cpu_knopp_sample(n, m, rows, max(1, args.steps), max(1, args.warmup))
+    cfg, n = args.config, args.n
+    cpu = cpu_arm(cfg, n, max(1, args.steps), max(1, args.warmup))
+    its = cpu["value"]
     line = {
-        "impl": "reference", "metric": "sinkhorn_knopp_iterations_per_sec", "value": its, "unit": "it/s",
+        "impl": "reference", "metric": METRIC[cfg], "value": its, "unit": "it/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / its,
-        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"ot.bregman.sinkhorn_knopp dense fp32 n=m={n}, reg={REG}, uniform weights, "
-                               "2-D Gaussian clouds, fixed iterations (stopThr=0)"},
-        "cpu_baseline": {"value": its, "unit": "it/s", "cores": cores, "kind": "port",
-                         "sample": f"first {rows} of {n} rows (all {m} columns), numpy/BLAS threads = all cores; "
-                                   f"measured {per_iter * 1e3:.2f} ms per sample iteration, scaled by {rows}/{n}"},
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": DTYPE[cfg], "data": "synthetic",
+        "config": {"workload": workload(cfg, n), "baseline_config": cfg},
+        "cpu_baseline": cpu,
         "e2e": {"value": its, "unit": "it/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -167,177 +314,458 @@ def reference_arm(args):
 
 
 # ------------------------------------------------------------------------------------------------
-def ours(args):
-    import torch
-    import torch.distributed as dist
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+class Ctx:
+    """Rank / device / process-group plumbing shared by the configs."""
 
-    import pot_b200
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+
+        self.torch, self.dist, self.args = torch, dist, args
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise RuntimeError("bench.py needs a CUDA device: pot_b200 has no CPU path")
+        torch.cuda.set_device(self.local_rank)
+        self.dev = torch.device("cuda", self.local_rank)
+        self.group = None
+        if self.world > 1:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("nccl", device_id=self.dev)
+            self.group = dist.group.WORLD
+        from pot_b200 import _lib
+
+        self.lib = _lib.load()
+        self._align = None
+
+    def barrier(self):
+        self.torch.cuda.synchronize(self.dev)
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize(self.dev)
+
+    def align(self):
+        """Device-side alignment of the ranks right before a timed window: one tiny peer exchange on the launch
+        stream, so no rank's ev0 is recorded (on the device) before every rank has reached this point."""
+        if self.world == 1:
+            return
+        if self.args.exchange == "peer":
+            from pot_b200.comm import get_comm
+
+            if self._align is None:
+                self._align = self.torch.zeros(8, dtype=self.torch.float32, device=self.dev)
+            get_comm(self.group, self.dev, 1 << 20).all_reduce(self._align, "sum")
+        else:
+            t = self.torch.zeros(8, dtype=self.torch.float32, device=self.dev)
+            self.dist.all_reduce(t)
+
+    def max_over_ranks(self, x):
+        t = self.torch.tensor([x], dtype=self.torch.float64, device=self.dev)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def timed(self, fn):
+        """Barrier, align, events around fn() on the current stream, barrier; seconds, max over ranks."""
+        torch = self.torch
+        self.barrier()
+        self.align()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = fn()
+        e1.record()
+        self.barrier()
+        return self.max_over_ranks(e0.elapsed_time(e1) * 1e-3), out
+
+    def finish(self):
+        if self.world > 1:
+            self.dist.destroy_process_group()
+
+
+def dense_cost_block(ctx, n, m, r0, r1, normalise=True, dtype=None):
+    """This rank's rows [r0, r1) of the squared-euclidean cost of the seed-0 clouds, built on the device in row chunks
+    with the library's own ot.dist kernel; divided by the global max when `normalise`."""
+    torch = ctx.torch
+    from pot_b200 import _dense, _lib
+
+    dtype = dtype or torch.float32
+    code = _dense.dtype_code(dtype)
+    xs, xt = point_clouds(n, m)
+    xs_d, xt_d = torch.from_numpy(xs[r0:r1]).to(ctx.dev, dtype), torch.from_numpy(xt).to(ctx.dev, dtype)
+    nloc = r1 - r0
+    M = torch.empty((nloc, m), dtype=dtype, device=ctx.dev)
+    chunk = max(1, (512 << 20) // (M.element_size() * m))
+    mx = torch.zeros((), dtype=dtype, device=ctx.dev)
+    scratch = torch.empty(ctx.lib.b2ot_dist_scratch_bytes(min(chunk, nloc), m, code), dtype=torch.uint8, device=ctx.dev)
+    for c0 in range(0, nloc, chunk):
+        c1 = min(nloc, c0 + chunk)
+        blk, xb = M[c0:c1], xs_d[c0:c1]
+        _lib.check(ctx.lib.b2ot_dist(code, xb.data_ptr(), xt_d.data_ptr(), c1 - c0, m, xb.shape[1], xb.stride(0),
+                                     xt_d.stride(0), _lib.METRIC_SQEUCLIDEAN, blk.data_ptr(), blk.stride(0),
+                                     scratch.data_ptr(), _dense.stream_ptr(ctx.dev)), "b2ot_dist")
+        mx = torch.maximum(mx, blk.max())
+    if normalise:
+        if ctx.world > 1:
+            ctx.dist.all_reduce(mx, op=ctx.dist.ReduceOp.MAX)
+        for c0 in range(0, nloc, chunk):
+            M[c0:min(nloc, c0 + chunk)].div_(mx)
+    return M
+
+
+def torch_reference_dense(ctx, cfg, n, make_M):
+    """Informative: the reference's own torch backend on this GPU (ot/backend.py:2237 torch.matmul GEMVs, one host
+    sync per iteration at ot/bregman/_sinkhorn.py:633-639; logsumexp passes for sinkhorn_log).  Seconds per iteration
+    from two fixed-iteration calls."""
+    import warnings
+
+    torch = ctx.torch
+    ot, kind = load_reference()
+    if ot is None:
+        return {"unavailable": "oracle/_ref not built on this box"}
+    try:
+        dt = torch.float64 if cfg == 1 else torch.float32
+        M = make_M()
+        a = torch.full((M.shape[0],), 1.0 / M.shape[0], dtype=dt, device=ctx.dev)
+        b = torch.full((M.shape[1],), 1.0 / M.shape[1], dtype=dt, device=ctx.dev)
+        fn = ot.bregman.sinkhorn_log if cfg == 2 else ot.bregman.sinkhorn_knopp
+
+        def call(k):
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                fn(a, b, M, REG[cfg], numItermax=k, stopThr=0, warn=False)
+            torch.cuda.synchronize(ctx.dev)
+
+        call(2)
+        k1, k2 = (5, 105) if cfg == 1 else (2, 22)
+        per = _per_iteration(call, k1, k2, reps=2)
+        del M
+        torch.cuda.empty_cache()
+        return {"value": 1.0 / per, "unit": "it/s", "ms_per_iteration": per * 1e3,
+                "what": f"ot.bregman.{fn.__name__} of the unmodified reference on torch CUDA tensors (same B200, same "
+                        f"inputs), (t({k2} its) - t({k1} its)) / {k2 - k1}, best of 2"}
+    except Exception as e:  # noqa: BLE001
+        torch.cuda.empty_cache()
+        return {"unavailable": f"{type(e).__name__}: {e}"[:300]}
+
+
+def bench_dense(ctx, cfg):
+    """Configs 1, 2, 3: dense scaling-domain (1, 3) / log-domain (2) Sinkhorn, rows sharded over the ranks."""
+    torch, args = ctx.torch, ctx.args
     from pot_b200 import _dense, _lib
     from pot_b200.host import sinkhorn_from_host
     from pot_b200.sharded import shard_rows
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise RuntimeError("bench.py needs a CUDA device: pot_b200 has no CPU path")
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    group = None
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
-        group = dist.group.WORLD
-    lib = _lib.load()
     n = m = args.n
-    r0, r1 = shard_rows(n, world, rank)
+    reg = REG[cfg]
+    mode = "log" if cfg == 2 else "knopp"
+    dt = torch.float64 if cfg == 1 else torch.float32
+    esz = 8 if cfg == 1 else 4
+    r0, r1 = shard_rows(n, ctx.world, ctx.rank)
     nloc = r1 - r0
     K_steps, W = max(1, args.steps), max(3, args.warmup)
-
-    # ---- synthetic inputs: this rank's row block of M, built on the device in row chunks ----
-    xs, xt = point_clouds(n, m)
-    xs_d, xt_d = torch.from_numpy(xs[r0:r1]).to(dev), torch.from_numpy(xt).to(dev)
-    Mdev = torch.empty((nloc, m), dtype=torch.float32, device=dev)
-    chunk = max(1, (512 << 20) // (4 * m))
-    mx = torch.zeros((), dtype=torch.float32, device=dev)
-    scratch = torch.empty(lib.b2ot_dist_scratch_bytes(min(chunk, nloc), m, _lib.F32), dtype=torch.uint8, device=dev)
-    for c0 in range(0, nloc, chunk):
-        c1 = min(nloc, c0 + chunk)
-        blk = Mdev[c0:c1]
-        xb = xs_d[c0:c1]
-        # squared-euclidean cost block straight into M (the library's own ot.dist kernel, clamped at 0)
-        _lib.check(lib.b2ot_dist(_lib.F32, xb.data_ptr(), xt_d.data_ptr(), c1 - c0, m, xb.shape[1], xb.stride(0),
-                                 xt_d.stride(0), _lib.METRIC_SQEUCLIDEAN, blk.data_ptr(), blk.stride(0),
-                                 scratch.data_ptr(), _dense.stream_ptr(dev)), "b2ot_dist")
-        mx = torch.maximum(mx, blk.max())
-    if world > 1:
-        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-    for c0 in range(0, nloc, chunk):
-        Mdev[c0:min(nloc, c0 + chunk)].div_(mx)
-    a_loc = torch.full((nloc,), 1.0 / n, dtype=torch.float32, device=dev)
-    b = torch.full((m,), 1.0 / m, dtype=torch.float32, device=dev)
-
-    def barrier():
-        torch.cuda.synchronize(dev)
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
-
-    def max_over_ranks(x):
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    # pinned host copy of M for the end-to-end leg (made before M is turned into K in place)
+    M = dense_cost_block(ctx, n, m, r0, r1, normalise=(cfg != 1), dtype=dt)
     M_host = None
     if not args.no_e2e:
-        M_host = torch.empty((nloc, m), dtype=torch.float32, pin_memory=True)
-        M_host.copy_(Mdev)
-        torch.cuda.synchronize(dev)
-
-    # ---- device-resident iterations/s ----
-    _lib.check(lib.b2ot_kexp(Mdev.data_ptr(), Mdev.data_ptr(), nloc, m, Mdev.stride(0), Mdev.stride(0), REG,
-                             _lib.F32, _dense.stream_ptr(dev)), "b2ot_kexp")
-    Kmat = Mdev
-    solver = _dense.DenseSolver("knopp", Kmat, a_loc, b, None, max_iter=10 ** 7, check_every=10, stop_thr=0.0,
-                                group=group, exchange=args.exchange)
-    u0 = torch.full((nloc,), 1.0 / n, dtype=torch.float32, device=dev)
-    v0 = torch.full((m,), 1.0 / m, dtype=torch.float32, device=dev)
+        M_host = torch.empty((nloc, m), dtype=dt, pin_memory=True)
+        M_host.copy_(M)
+        torch.cuda.synchronize(ctx.dev)
+    fn = ctx.lib.b2ot_kexp if mode == "knopp" else ctx.lib.b2ot_negscale
+    _lib.check(fn(M.data_ptr(), M.data_ptr(), nloc, m, M.stride(0), M.stride(0), reg, _dense.dtype_code(dt),
+                  _dense.stream_ptr(ctx.dev)), "cost transform")
+    a_loc = torch.full((nloc,), 1.0 / n, dtype=dt, device=ctx.dev)
+    b = torch.full((m,), 1.0 / m, dtype=dt, device=ctx.dev)
+    if mode == "knopp":
+        solver = _dense.DenseSolver("knopp", M, a_loc, b, None, max_iter=10 ** 7, check_every=10, stop_thr=0.0,
+                                    group=ctx.group, exchange=args.exchange)
+        u0, v0 = a_loc.clone(), b.clone()
+    else:
+        solver = _dense.DenseSolver("log", M, torch.log(a_loc), b, torch.log(b), max_iter=10 ** 7, check_every=10,
+                                    stop_thr=0.0, group=ctx.group, exchange=args.exchange)
+        u0, v0 = torch.zeros(nloc, dtype=dt, device=ctx.dev), torch.zeros(m, dtype=dt, device=ctx.dev)
     solver.init(u0, v0)
     solver.iterate(W)
-    barrier()
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
+    sampler = ClockSampler(ctx.local_rank)
+    if ctx.rank == 0:
         sampler.start()
-    launches0 = lib.b2ot_launch_count()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    solver.iterate(K_steps)
-    ev1.record()
-    barrier()
-    launches = lib.b2ot_launch_count() - launches0
-    clocks = sampler.stop() if rank == 0 else None
-    t_steps = max_over_ranks(ev0.elapsed_time(ev1) * 1e-3)
+    launches0 = ctx.lib.b2ot_launch_count()
+    t_steps, _ = ctx.timed(lambda: solver.iterate(K_steps))
+    launches = ctx.lib.b2ot_launch_count() - launches0
+    clocks = sampler.stop() if ctx.rank == 0 else None
     status, it_done = solver.poll()
     assert status == 0 and it_done == W + K_steps, (status, it_done)
-
-    # ---- roofline of the dominant kernel (the fused sweep), timed alone with CUDA events ----
-    sweep_ms, iter_ms = solver.profile(min(20, K_steps))
-    sweep_ms = max_over_ranks(sweep_ms)
+    sweep_ms, _ = solver.profile(min(20, K_steps))
+    sweep_ms = ctx.max_over_ranks(sweep_ms)
     u, v, errs = solver.export()
     finite = bool(torch.isfinite(u).all().item() and torch.isfinite(v).all().item())
     info = solver.info()
     solver.close()
-    del solver, Kmat, Mdev
+    del solver, M
     torch.cuda.empty_cache()
-    alg_bytes = 4.0 * nloc * m + 4.0 * (2 * nloc + 3 * m)
-    peak, peak_src = peaks()
+    alg_bytes = float(esz) * nloc * m + float(esz) * (2 * nloc + 3 * m)
+    pk = peaks()
     achieved = alg_bytes / (sweep_ms * 1e-3) / 1e9
-    traffic = None
-    try:
-        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            traffic = json.load(f).get(f"knopp_f32_{nloc}x{m}")
-    except Exception:
-        pass
+    kern = {1: "fused_sweep_kernel<double, knopp>", 2: "log_pp_sweep_kernel (fp32 log-domain ping-pong sweep)",
+            3: "fused_sweep_kernel<float, 8, knopp>"}[cfg]
+    roof = {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
+            "traffic": traffic_from_profiles(f"{mode}_{DTYPE[cfg]}_{nloc}x{m}"), "kernel": kern,
+            "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": sweep_ms, "peak_source": pk["source"],
+            "frac_of_nominal_8TBs": achieved / 8000.0}
+    if cfg == 1:
+        roof["note"] = "8 MB problem: L2-resident and launch-latency bound, the HBM fraction is not the limiter here"
 
-    # ---- e2e: whole solve from pinned host memory ----
     e2e = None
     if not args.no_e2e:
-        a_host = torch.full((nloc,), 1.0 / n, dtype=torch.float32).pin_memory()
-        b_host = torch.full((m,), 1.0 / m, dtype=torch.float32).pin_memory()
-        torch.cuda.synchronize(dev)
-        sinkhorn_from_host(a_host, b_host, M_host, REG, numItermax=min(W, 5), stopThr=0.0, device=dev, group=group,
-                           n_total=n, exchange=args.exchange)  # warm-up solve (allocator, NCCL channels, kernel images)
-        barrier()
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ev0.record()
-        res = sinkhorn_from_host(a_host, b_host, M_host, REG, numItermax=K_steps, stopThr=0.0, device=dev,
-                                 group=group, n_total=n, exchange=args.exchange)
-        ev1.record()
-        barrier()
-        t_e2e = max_over_ranks(ev0.elapsed_time(ev1) * 1e-3)
+        a_host = torch.full((nloc,), 1.0 / n, dtype=dt).pin_memory()
+        b_host = torch.full((m,), 1.0 / m, dtype=dt).pin_memory()
+        method = "sinkhorn_log" if mode == "log" else "sinkhorn"
+        kw = dict(method=method, stopThr=0.0, device=ctx.dev, group=ctx.group, n_total=n, exchange=args.exchange)
+        sinkhorn_from_host(a_host, b_host, M_host, reg, numItermax=min(W, 5), **kw)  # warm-up solve
+        t_e2e, res = ctx.timed(lambda: sinkhorn_from_host(a_host, b_host, M_host, reg, numItermax=K_steps, **kw))
         assert res["niter"] == K_steps - 1, res["niter"]
+        upload_s = res["h2d_bytes"] / 50e9
         e2e = {"value": K_steps / t_e2e, "unit": "it/s",
-               "h2d_bytes_per_step": int(res["h2d_bytes"] * world / K_steps),
-               "d2h_bytes_per_step": int(res["d2h_bytes"] * world / K_steps),
+               "h2d_bytes_per_step": int(res["h2d_bytes"] * ctx.world / K_steps),
+               "d2h_bytes_per_step": int(res["d2h_bytes"] * ctx.world / K_steps),
                "solve_seconds": t_e2e, "iterations_per_solve": K_steps,
-               "note": "one solve of `steps` iterations from pinned host M; bytes = whole-job bytes of the solve / steps"}
+               "device_resident_seconds_for_the_same_iterations": t_steps,
+               "upload_share_estimate": min(1.0, max(0.0, (t_e2e - t_steps) / t_e2e)),
+               "note": "one solve of `steps` iterations from pinned host M through pot_b200.host.sinkhorn_from_host; "
+                       "bytes = whole-job bytes of the solve / steps; the value grows with --steps because the upload "
+                       f"of M is paid once per solve (PCIe bound: ~{upload_s:.2f} s at 50 GB/s per rank)"}
         del M_host
+    tref = None
+    if ctx.rank == 0 and ctx.world == 1 and not args.no_torch_ref:
+        tref = torch_reference_dense(ctx, cfg, n, lambda: dense_cost_block(ctx, n, m, 0, n, normalise=(cfg != 1), dtype=dt))
+    extra = {"sharding": (f"rows split over {ctx.world} rank(s), one exchange of the column sums (m+1 values) per "
+                          f"iteration, exchange={args.exchange}") if ctx.world > 1 else "single GPU",
+             "l2": ("inputs larger than L2 (matrix per rank = %.2f GiB >> 126 MB): no flush needed" % (esz * nloc * m / 2 ** 30))
+             if esz * nloc * m > (256 << 20) else "8 MB problem, L2 resident by nature (the reference's own CPU-sized case)",
+             "sweep": info, "finite": finite, "last_err": errs[-1] if errs else None}
+    return dict(t_steps=t_steps, K=K_steps, W=W, launches=launches, clocks=clocks, roofline=roof, e2e=e2e, extra=extra,
+                torch_ref=tref)
 
+
+def traffic_from_profiles(key):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture of HEAD's kernel
+    (profiles/traffic.json: {key: {"bytes": ..., "commit": ..., "source": ...}}), or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            ent = json.load(f).get(key)
+        if isinstance(ent, dict):
+            return ent.get("bytes")
+        return ent
+    except Exception:
+        return None
+
+
+def bench_empirical(ctx):
+    """Config 4: online-cost log-domain empirical Sinkhorn, source points sharded over the ranks."""
+    torch, args = ctx.torch, ctx.args
+    from pot_b200.empirical import EmpiricalSolver
+    from pot_b200.sharded import empirical_sinkhorn_sharded, shard_rows
+
+    n = m = args.n
+    d, reg = 64, REG[4]
+    K_steps, W = max(1, args.steps), max(3, min(args.warmup, 5))
+    g = torch.Generator(device=ctx.dev).manual_seed(SEED)  # same seed on every rank: identical clouds
+    xs = torch.randn(n, d, device=ctx.dev, generator=g) / d ** 0.5
+    xt = torch.randn(m, d, device=ctx.dev, generator=g) / d ** 0.5 + 1.0 / d ** 0.5
+    r0, r1 = shard_rows(n, ctx.world, ctx.rank)
+    nloc = r1 - r0
+    xs_loc = xs[r0:r1].contiguous()
+    del xs
+    a_loc = torch.full((nloc,), 1.0 / n, device=ctx.dev)
+    b = torch.full((m,), 1.0 / m, device=ctx.dev)
+    s = EmpiricalSolver(xs_loc, xt, a_loc, b, reg, max_iter=10 ** 6, stop_thr=-1.0, variant="tc", group=ctx.group,
+                        exchange=args.exchange, operand=args.operand)
+    s.init(torch.zeros(nloc, device=ctx.dev), torch.zeros(m, device=ctx.dev))
+    s.iterate(W)
+    sampler = ClockSampler(ctx.local_rank)
+    if ctx.rank == 0:
+        sampler.start()
+    launches0 = ctx.lib.b2ot_launch_count()
+    t_steps, _ = ctx.timed(lambda: s.iterate(K_steps))
+    launches = ctx.lib.b2ot_launch_count() - launches0
+    clocks = sampler.stop() if ctx.rank == 0 else None
+    sweep_ms, _ = s.profile(min(5, K_steps))
+    sweep_ms = ctx.max_over_ranks(sweep_ms)
+    f, gg, errs = s.export()
+    finite = bool(torch.isfinite(f).all().item() and torch.isfinite(gg).all().item())
+    info = s.info()
+    s.close()
+    pk = peaks()
+    kind = args.operand
+    useful = 2.0 * nloc * m * d                 # one half-sweep on this rank: the -2 x.y^T cross term
+    issued = 3.0 * useful                       # 3-way split (hi*hi + hi*lo + lo*hi), fp32 accumulate
+    ex2 = float(nloc) * m
+    t = sweep_ms * 1e-3
+    sm_hz = (clocks or {}).get("sm_mhz") or pk["sm_max_mhz"]
+    mufu_peak = 148 * 16 * pk["sm_max_mhz"] * 1e6
+    roof = {"bound": "tensor", "achieved": issued / t / 1e12, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
+            "frac": issued / t / 1e12 / pk["bf16_tflops"], "traffic": None,
+            "kernel": f"emp_tc_lse_kernel (tcgen05, 3x{kind} split, online LSE epilogue), one half-sweep",
+            "launch_ms": sweep_ms, "algorithmic_flops_per_launch": useful, "issued_tensor_flops_per_launch": issued,
+            "useful_fp32_equivalent_tflops": useful / t / 1e12, "peak_source": pk["source"] + " bf16/fp16 dense sustained",
+            "mufu": {"achieved_ex2_per_s": ex2 / t, "peak_ex2_per_s": mufu_peak, "frac": ex2 / t / mufu_peak,
+                     "peak_basis": "148 SM x 16 ex2/clk x sm_max_mhz", "sm_mhz_under_load": sm_hz},
+            "note": "north_star: this path is bound by exp (MUFU) throughput and the tensor pipe, not by HBM; bytes are the "
+                    "packed clouds (L2 resident)"}
+    del s
+    torch.cuda.empty_cache()
+
+    e2e = None
+    if not args.no_e2e:
+        xs_h = xs_loc.cpu().pin_memory()
+        xt_h = xt.cpu().pin_memory()
+        del xs_loc, xt
+        torch.cuda.empty_cache()
+
+        def solve(k):
+            X, Y = xs_h.to(ctx.dev, non_blocking=True), xt_h.to(ctx.dev, non_blocking=True)
+            if ctx.world > 1:
+                fo, go = empirical_sinkhorn_sharded(X, Y, reg, numIterMax=k, stopThr=-1.0, warn=False, group=ctx.group,
+                                                    n_total=n, exchange=args.exchange, b2ot_variant="tc",
+                                                    b2ot_operand=args.operand)
+            else:
+                import pot_b200 as ot
+
+                fo, go = ot.empirical_sinkhorn(X, Y, reg, numIterMax=k, stopThr=-1.0, isLazy=True, warn=False,
+                                               b2ot_operand=args.operand)
+            return fo.cpu(), go.cpu()
+
+        solve(2)
+        t_e2e, (fo, go) = ctx.timed(lambda: solve(K_steps))
+        h2d = 4 * (nloc + m) * d
+        d2h = 4 * (nloc + m)
+        e2e = {"value": K_steps / t_e2e, "unit": "it/s", "h2d_bytes_per_step": int(h2d * ctx.world / K_steps),
+               "d2h_bytes_per_step": int(d2h * ctx.world / K_steps), "solve_seconds": t_e2e,
+               "iterations_per_solve": K_steps,
+               "note": "pinned host point clouds -> device, ot.bregman.empirical_sinkhorn(isLazy=True) "
+                       "(sharded: empirical_sinkhorn_sharded) for `steps` iterations, (f, g) read back to the host"}
+    extra = {"sharding": (f"source points split over {ctx.world} rank(s); per iteration one LSE-combine of the m column "
+                          f"partials (max + sum exchange), exchange={args.exchange}") if ctx.world > 1 else "single GPU",
+             "l2": "operands (2 x 134 MB packed clouds) exceed L2 and are re-streamed every sweep; no flush needed",
+             "operand_kind": kind, "sweep": info, "finite": finite, "last_err": errs[-1] if errs else None}
+    return dict(t_steps=t_steps, K=K_steps, W=W, launches=launches, clocks=clocks, roofline=roof, e2e=e2e, extra=extra,
+                torch_ref=None)
+
+
+def bench_batch(ctx):
+    """Config 5: ot.batch.solve_batch, whole problems sharded over the ranks, no communication."""
+    torch, args = ctx.torch, ctx.args
+    from pot_b200 import batch as otb
+    from pot_b200.sharded import shard_rows
+
+    B, bn, bm, reg = args.n, 256, 256, REG[5]
+    K_steps, W = max(1, args.steps), max(3, args.warmup)
+    p0, p1 = shard_rows(B, ctx.world, ctx.rank)
+    Bl = p1 - p0
+    g = torch.Generator(device=ctx.dev).manual_seed(100 + ctx.rank)
+    X = torch.randn(Bl, bn, 2, device=ctx.dev, generator=g)
+    Y = torch.randn(Bl, bm, 2, device=ctx.dev, generator=g) + 1.0
+    M = (X * X).sum(-1)[:, :, None] + (Y * Y).sum(-1)[:, None, :] - 2 * torch.einsum("bid,bjd->bij", X, Y)
+    mx = M.max()
+    if ctx.world > 1:
+        ctx.dist.all_reduce(mx, op=ctx.dist.ReduceOp.MAX)
+    M = (M / mx).float().contiguous()
+    a = torch.full((Bl, bn), 1.0 / bn, device=ctx.dev)
+    bb = torch.full((Bl, bm), 1.0 / bm, device=ctx.dev)
+
+    def run(mode, tr, its):
+        return otb._run(mode, M, tr, reg, M, a, bb, its, 0.0, True, False, 1, sync_n_iters=False)
+
+    for _ in range(max(1, W // 3)):
+        run("log", 2, 10)
+    sampler = ClockSampler(ctx.local_rank)
+    if ctx.rank == 0:
+        sampler.start()
+    launches0 = ctx.lib.b2ot_launch_count()
+    # the timed region: ONE solve_batch kernel pass of K iterations (load + Gibbs transform + K iterations + plan +
+    # both objective terms); it is a single launch, so its event time is the kernel's launch duration as well
+    t_steps, out = ctx.timed(lambda: run("log", 2, K_steps))
+    launches = ctx.lib.b2ot_launch_count() - launches0
+    clocks = sampler.stop() if ctx.rank == 0 else None
+    finite = bool(torch.isfinite(out["value_linear"]).all().item())
+    # per-iteration cost without load / plan: difference of two fixed-iteration solves, both solvers
+    detail = {}
+    for solver, mode, tr in (("log_sinkhorn", "log", 2), ("sinkhorn", "knopp", 1)):
+        k_lo, k_hi = 10, 10 + max(K_steps, 50)
+        t_lo = min(ctx.timed(lambda: run(mode, tr, k_lo))[0] for _ in range(3))
+        t_hi = min(ctx.timed(lambda: run(mode, tr, k_hi))[0] for _ in range(3))
+        per = (t_hi - t_lo) / (k_hi - k_lo)
+        detail[solver] = {"us_per_iteration_all_problems": per * 1e6, "problem_iterations_per_s": B / per,
+                          "ms_load_transform_plan_values": (t_lo - k_lo * per) * 1e3}
+    pk = peaks()
+    per_log = detail["log_sinkhorn"]["us_per_iteration_all_problems"] * 1e-6
+    ex2 = float(Bl) * bn * bm       # log domain: one ex2 per element per iteration (f and g half-steps share it)
+    mufu_peak = 148 * 16 * pk["sm_max_mhz"] * 1e6
+    hbm_bytes = 2.0 * 4 * Bl * bn * bm
+    roof = {"bound": "mufu", "achieved": ex2 / per_log / 1e12, "peak": mufu_peak / 1e12, "unit": "Tex2/s",
+            "frac": ex2 / per_log / mufu_peak, "traffic": None,
+            "kernel": "batch_solve_kernel<float, log> (one cluster of 2 CTAs per problem, tile register-resident)",
+            "launch_ms": t_steps * 1e3, "peak_basis": "148 SM x 16 ex2/clk x sm_max_mhz",
+            "hbm": {"bytes_per_launch": hbm_bytes, "achieved_GBps_over_whole_launch": hbm_bytes / t_steps / 1e9,
+                    "peak": pk["hbm_gbs"], "note": "M read once, plan written once; the iterations run on chip"},
+            "scaling_domain": {"fma_per_s": 2.0 * Bl * bn * bm / (detail["sinkhorn"]["us_per_iteration_all_problems"] * 1e-6),
+                               "peak_fma_per_s": 148 * 128 * pk["sm_max_mhz"] * 1e6}}
+    e2e = None
+    if not args.no_e2e:
+        import pot_b200 as ot
+
+        M_h = M.cpu().pin_memory()
+
+        def solve(k):
+            Md = M_h.to(ctx.dev, non_blocking=True)
+            res = ot.batch.solve_batch(Md, reg, max_iter=k, tol=0.0, solver="log_sinkhorn", reg_type="entropy")
+            return res.value.cpu(), res.potentials[0].cpu(), res.potentials[1].cpu()
+
+        solve(5)
+        t_e2e, _ = ctx.timed(lambda: solve(K_steps))
+        e2e = {"value": K_steps / t_e2e, "unit": "it/s", "h2d_bytes_per_step": int(4 * B * bn * bm / K_steps),
+               "d2h_bytes_per_step": int(4 * B * (1 + bn + bm) / K_steps), "solve_seconds": t_e2e,
+               "iterations_per_solve": K_steps,
+               "note": "pinned host M (B, 256, 256) -> device, ot.batch.solve_batch(max_iter=steps, tol=0), value and "
+                       "potentials read back to the host (the plan stays on the device)"}
+    extra = {"sharding": f"problems split over {ctx.world} rank(s), no communication" if ctx.world > 1 else "single GPU",
+             "l2": "inputs larger than L2 (M per rank = %.2f GiB); each solve reads M from HBM once" % (4 * Bl * bn * bm / 2 ** 30),
+             "finite": finite, "per_iteration": detail,
+             "step": "one Sinkhorn iteration of all problems inside ONE solve_batch call of `steps` iterations "
+                     "(load, Gibbs transform, plan and objective values included in the timed region)"}
+    return dict(t_steps=t_steps, K=K_steps, W=W, launches=launches, clocks=clocks, roofline=roof, e2e=e2e, extra=extra,
+                torch_ref=None)
+
+
+def ours(args):
+    import pot_b200  # noqa: F401  (raises ImportError when libb2ot.so is missing: there is no CPU path)
+
+    ctx = Ctx(args)
+    cfg = args.config
+    if cfg in (1, 2, 3):
+        r = bench_dense(ctx, cfg)
+    elif cfg == 4:
+        r = bench_empirical(ctx)
+    else:
+        r = bench_batch(ctx)
     cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu:
-        rows = min(n, 4096)
-        its, per_iter, cores = cpu_knopp_sample(n, m, rows, 30, 3)
-        cpu = {"value": its, "unit": "it/s", "cores": cores, "kind": "port",
-               "sample": f"oracle numpy sinkhorn_knopp on the first {rows} of {n} rows (all {m} columns), 30 iterations, "
-                         f"{per_iter * 1e3:.2f} ms per sample iteration, scaled by {rows}/{n}"}
-
-    if rank == 0:
+    if ctx.rank == 0 and ctx.world == 1 and not args.no_cpu:
+        cpu = cpu_arm(cfg, args.n, 20, 3)
+    if ctx.rank == 0:
+        K, t = r["K"], r["t_steps"]
+        config = {"workload": workload(cfg, args.n), "baseline_config": cfg}
+        config.update(r["extra"])
         line = {
-            "metric": "sinkhorn_knopp_iterations_per_sec", "value": K_steps / t_steps, "unit": "it/s",
-            "n_gpus": world, "steps": K_steps, "warmup": W, "ms_per_step": 1e3 * t_steps / K_steps,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"ot.bregman.sinkhorn_knopp dense fp32 n=m={n} (K = {4 * n * m / 2 ** 30:.0f} GiB), "
-                                   f"reg={REG}, uniform weights, 2-D Gaussian clouds (seed {SEED}), fixed iterations "
-                                   "(stopThr=0)",
-                       "sharding": f"rows split over {world} rank(s), one exchange of K^T u (m+1 floats) per iteration, "
-                                   f"exchange={args.exchange}"
-                                   if world > 1 else "single GPU",
-                       "l2": "inputs larger than L2 (K per rank = %.1f GiB >> 126 MB): no flush needed"
-                             % (4 * nloc * m / 2 ** 30),
-                       "sweep": info, "finite": finite, "last_err": errs[-1] if errs else None},
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "kernel": "fused_sweep_kernel<float, 8, knopp>",
-                         "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": sweep_ms, "peak_source": peak_src},
-            "cpu_baseline": cpu,
-            "e2e": e2e,
-            "gpu_launches": int(launches),
-            "clocks": clocks,
+            "metric": METRIC[cfg], "value": K / t, "unit": "it/s", "n_gpus": ctx.world, "steps": K, "warmup": r["W"],
+            "ms_per_step": 1e3 * t / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": DTYPE[cfg], "data": "synthetic", "config": config, "roofline": r["roofline"], "cpu_baseline": cpu,
+            "e2e": r["e2e"], "gpu_launches": int(r["launches"]), "clocks": r["clocks"],
         }
+        if r.get("torch_ref") is not None:
+            line["reference_torch_cuda"] = r["torch_ref"]
         print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    ctx.finish()
 
 
 if __name__ == "__main__":

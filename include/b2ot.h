@@ -212,11 +212,21 @@ int b2ot_emp_create(b2ot_emp** handle, int dtype, int64_t n, int64_t m, int d, c
                     const void* Xt, int64_t ldXt, const void* a, const void* loga, const void* logb, double reg,
                     int metric, void* workspace, size_t workspace_bytes, int max_iter, double stop_thr, int variant,
                     void* stream);
+/* operand split of the tcgen05 sweep's cross term -2 x.y^T (call before b2ot_emp_init; no effect on the SIMT sweep):
+ *   F16  (default) each fp32 coordinate = hi + lo fp16 halves under one power-of-two scale per cloud, 3 MMAs
+ *        (hi*hi + hi*lo + lo*hi), fp32 accumulate: 22 significant bits, half the operand bytes of TF32;
+ *   TF32 the 3xTF32 split (8-bit exponent: no dependence on the dynamic range inside a cloud). */
+#define B2OT_EMP_OPERAND_F16 0
+#define B2OT_EMP_OPERAND_TF32 1
+int b2ot_emp_set_operand(b2ot_emp* handle, int operand);
 int b2ot_emp_set_allreduce(b2ot_emp* handle, b2ot_allreduce_fn fn, void* ctx);
 /* enqueue: load the initial potentials f0 (n), g0 (m) and compute the squared norms */
 int b2ot_emp_init(b2ot_emp* handle, const void* f0, const void* g0);
 /* enqueue n_iters iterations (row sweep, f update + pending check, column sweep, g update); no host sync */
 int b2ot_emp_iterate(b2ot_emp* handle, int n_iters);
+/* measurement aid (as b2ot_dense_profile): CUDA events around the two sweep launches of each iteration; average
+ * duration of ONE sweep kernel and of a whole iteration, in milliseconds */
+int b2ot_emp_profile(b2ot_emp* handle, int n_iters, float* sweep_ms_avg, float* iter_ms_avg);
 int b2ot_emp_poll(b2ot_emp* handle, int* status, int* iter);
 /* what the handle resolved to: B2OT_EMP_SIMT or B2OT_EMP_TC, and the reduction splits of the two sweeps */
 int b2ot_emp_info(const b2ot_emp* handle, int* variant, int* nsplit_rows, int* nsplit_cols);

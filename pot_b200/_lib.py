@@ -74,9 +74,11 @@ PROTOTYPES = {
     "b2ot_emp_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.c_int64, C.c_int, C.c_void_p,
                                   C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double,
                                   C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_double, C.c_int, C.c_void_p]),
+    "b2ot_emp_set_operand": (C.c_int, [C.c_void_p, C.c_int]),
     "b2ot_emp_set_allreduce": (C.c_int, [C.c_void_p, ALLREDUCE_FN, C.c_void_p]),
     "b2ot_emp_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "b2ot_emp_iterate": (C.c_int, [C.c_void_p, C.c_int]),
+    "b2ot_emp_profile": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "b2ot_emp_poll": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "b2ot_emp_solve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int),
                                  C.POINTER(C.c_int), C.POINTER(C.c_int)]),
@@ -108,6 +110,7 @@ ST_COMM_TIMEOUT = 5
 IPC_HANDLE_BYTES = 64
 METRIC_SQEUCLIDEAN, METRIC_EUCLIDEAN = 0, 1
 EMP_AUTO, EMP_SIMT, EMP_TC = 0, 1, 2
+EMP_OPERAND_F16, EMP_OPERAND_TF32 = 0, 1
 
 _lib = None
 

@@ -70,7 +70,7 @@ static int launch_one(const BatchParams& p, const BatchCfg& c, cudaStream_t stre
 template <typename T>
 static int fast_trips(const BatchParams& p, const BatchCfg& c) {
   static const bool on = [] {
-    const char* e = getenv("B2OT_BATCH_REGTILE");
+    const char* e = diag_env("B2OT_BATCH_REGTILE");
     return !(e && e[0] == '0');
   }();
   if (!on || (c.cpl != 4 && c.cpl != 8)) return 0;

@@ -274,7 +274,7 @@ static int config_fused(b2ot_dense* h) {
   int stages = (int)(((OCC == 2 ? 100 : 200) * 1024) / stage_bytes);
   if (stages > SMAX) stages = SMAX;
   if (stages < 2) stages = 2;
-  const char* env = getenv("B2OT_STAGES");
+  const char* env = diag_env("B2OT_STAGES");
   if (env && atoi(env) >= 2 && atoi(env) <= SMAX && (size_t)atoi(env) * stage_bytes <= (size_t)(OCC == 2 ? 104 : 216) * 1024) stages = atoi(env);
   h->stages = stages;
   h->dyn_smem = stages * stage_bytes;
@@ -297,7 +297,7 @@ static int config_fused(b2ot_dense* h) {
   B2OT_REQUIRE(maxcl >= 1, "fused sweep: no cluster of size %d fits on this device", h->cs);
   const long long NG = (h->n + R - 1) / R;
   long long ncl = std::min<long long>(maxcl, std::max<long long>(NG, 1));
-  const char* envc = getenv("B2OT_CLUSTERS");
+  const char* envc = diag_env("B2OT_CLUSTERS");
   if (envc && atoi(envc) >= 1) ncl = std::min<long long>(ncl, atoi(envc));
   if (ncl > NPMAX) ncl = NPMAX;
   h->ncl = (int)ncl;
@@ -346,7 +346,7 @@ static int config_pp(b2ot_dense* h) {
   int stages = PP_SMAX;
   const size_t budget = OCC == 2 ? (size_t)(110 * 1024) : (size_t)(228 * 1024 - 4096);
   while (stages > 2 && pp_smem_bytes(VPT, stages) > budget) --stages;
-  const char* env = getenv("B2OT_PP_STAGES");
+  const char* env = diag_env("B2OT_PP_STAGES");
   if (env && atoi(env) >= 2 && atoi(env) <= stages) stages = atoi(env);
   h->stages = stages;
   h->dyn_smem = pp_smem_bytes(VPT, stages);
@@ -368,7 +368,7 @@ static int config_pp(b2ot_dense* h) {
   if (int rc_occ = cached_max_clusters(kern, &cfg, h->cs, &maxcl)) return rc_occ;
   B2OT_REQUIRE(maxcl >= 1, "ping-pong sweep: no cluster of size %d fits on this device", h->cs);
   long long ncl = std::min<long long>(maxcl, std::max<long long>((h->n + PP_NH - 1) / PP_NH, 1));
-  const char* envc = getenv("B2OT_CLUSTERS");
+  const char* envc = diag_env("B2OT_CLUSTERS");
   if (envc && atoi(envc) >= 1) ncl = std::min<long long>(ncl, atoi(envc));
   if (ncl > NPMAX) ncl = NPMAX;
   h->ncl = (int)ncl;
@@ -493,16 +493,16 @@ static bool plan_fused(b2ot_dense* h) {
   // CTA shape: 16 warps for the MUFU-heavy log domain, 8 warps for the scaling domain
   h->nw = 8;
   h->occ = 1;
-  const char* envw = getenv("B2OT_WARPS");
+  const char* envw = diag_env("B2OT_WARPS");
   if (envw && (atoi(envw) == 8 || atoi(envw) == 16)) h->nw = atoi(envw);
-  const char* envo = getenv("B2OT_OCC");
+  const char* envo = diag_env("B2OT_OCC");
   if (envo && (atoi(envo) == 1 || atoi(envo) == 2)) h->occ = atoi(envo);
   if (h->nw == 16) h->occ = 1;
   const int vptmax = (h->nw == 8 && h->occ == 1) ? 8 : 4;
   const long long nct = 32LL * h->nw;
   const long long wcapmax = nct * vptmax * vec;
   int max_cs = (h->occ == 2) ? 16 : 8;
-  const char* env = getenv("B2OT_MAX_CLUSTER");
+  const char* env = diag_env("B2OT_MAX_CLUSTER");
   if (env && atoi(env) >= 1 && atoi(env) <= CSMAX) max_cs = atoi(env);
   if (h->m <= wcapmax) {
     h->cs = 1;
@@ -526,21 +526,21 @@ static bool plan_fused(b2ot_dense* h) {
   }
   // K streams through L2 once per sweep: mark it evict-first only when it cannot stay resident
   h->use_hint = ((double)h->n * (double)h->ld * (double)sz > 80.0 * 1024 * 1024) ? 1 : 0;
-  const char* envh = getenv("B2OT_L2_HINT");
+  const char* envh = diag_env("B2OT_L2_HINT");
   if (envh) h->use_hint = atoi(envh) ? 1 : 0;
   // fp32 log domain: ping-pong schedule (two independent half-CTAs) when the slice is wide enough (B2OT_LOGPP=0: off)
   h->pp_vpt = 0;
   h->pp_occ = 1;
-  const char* envp = getenv("B2OT_LOGPP");
+  const char* envp = diag_env("B2OT_LOGPP");
   const bool pp_on = !(envp && envp[0] == '0');
   const bool pp_cand = pp_on && h->mode == B2OT_MODE_LOG && h->dtype == B2OT_F32 && h->nw == 8 && h->occ == 1;
   // Slice width of the ping-pong kernel.  Default: the narrowest cluster that gives slices of <= 4096 columns
   // (8 vectors per thread, 126 registers), so that TWO CTAs = four independent halves fit on an SM
   // (16384^2: 199 -> 187 us per sweep, 65536^2: 3.79 -> 3.48 ms; profiles/r01c_logpp_occ2.log).
   // B2OT_PP_OCC=1 restores one CTA per SM with the widest slices; B2OT_PP_CLUSTER forces a cluster size.
-  const char* envo2 = getenv("B2OT_PP_OCC");
+  const char* envo2 = diag_env("B2OT_PP_OCC");
   const bool want_occ2 = !(envo2 && atoi(envo2) == 1);
-  const char* envpc = getenv("B2OT_PP_CLUSTER");
+  const char* envpc = diag_env("B2OT_PP_CLUSTER");
   int force_cs = 0;
   if (envpc && atoi(envpc) >= 1 && atoi(envpc) <= CSMAX && (atoi(envpc) & (atoi(envpc) - 1)) == 0) force_cs = atoi(envpc);
   if (pp_cand && (force_cs || (want_occ2 && h->m > pp_wcap(8)))) {
@@ -817,7 +817,7 @@ static int launch_finalize(const b2ot_dense* h, int nsrc, int init, int gate_reb
   p.gate_rebuild = gate_rebuild;
   int blocks = h->tau > 0.0 ? std::min(h->fin_blocks, 512) : h->fin_blocks;  // second half of blk_err: scaled error
   static const int qsplit_env = [] {
-    const char* e = getenv("B2OT_FIN_QSPLIT");  // diagnosis: 0 = never, 1 = rule below (default), 2 = m <= 32768, 3 = m <= 4096
+    const char* e = diag_env("B2OT_FIN_QSPLIT");  // diagnosis: 0 = never, 1 = rule below (default), 2 = m <= 32768, 3 = m <= 4096
     return e ? atoi(e) : 1;
   }();
   const long long qsplit_m = (qsplit_env == 2) ? 32768 : (qsplit_env == 3 ? 4096 : ((h->mode == B2OT_MODE_LOG && h->pp_vpt > 0) ? 4096 : 32768));
@@ -983,7 +983,7 @@ static int enqueue_iterations(b2ot_dense* h, int n_iters) {
 static const int kGraphIters = 10;
 static bool graphs_enabled() {
   static const bool on = [] {
-    const char* e = getenv("B2OT_GRAPH");
+    const char* e = diag_env("B2OT_GRAPH");
     return !(e && e[0] == '0');
   }();
   return on;

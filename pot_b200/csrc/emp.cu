@@ -1,6 +1,7 @@
 // Host driver + C ABI of the online-cost (empirical) Sinkhorn solver, ot.dist and the lazy plan blocks
 // (see include/b2ot.h, emp_kernels.cuh).
 #include <algorithm>
+#include <vector>
 #include <cstring>
 #include <new>
 
@@ -158,12 +159,14 @@ int launch_tc_pass(const b2ot_emp* h, bool passA) {
   p.k2 = (float)(1.4426950408889634 / h->reg);
   p.status = &h->st->status;
   p.expect_status = ST_RUNNING;
-  if (const char* e = getenv("B2OT_EMP_DBG")) p.dbg = atoi(e);
-  if (const char* e = getenv("B2OT_EMP_TRACE")) p.trace = (long long*)strtoull(e, nullptr, 0);  // device address
+#ifdef B2OT_DIAG
+  if (const char* e = diag_env("B2OT_EMP_DBG")) p.dbg = atoi(e);
+  if (const char* e = diag_env("B2OT_EMP_TRACE")) p.trace = (long long*)strtoull(e, nullptr, 0);  // device address
+#endif
 
   // cluster along the row tiles (multicast of the column operand); B2OT_EMP_CLUSTER = 1, 2 or 4
   int cs = 1;
-  if (const char* e = getenv("B2OT_EMP_CLUSTER")) {
+  if (const char* e = diag_env("B2OT_EMP_CLUSTER")) {
     const int v = atoi(e);
     if (v == 1 || v == 2 || v == 4) cs = v;
   }
@@ -378,9 +381,8 @@ extern "C" int b2ot_emp_create(b2ot_emp** handle, int dtype, int64_t n, int64_t 
   h->pmaxB = ws + L.off_pb;
   h->psumB = ws + L.off_pb + (size_t)L.nsB * m * sz;
   h->use_tc = L.use_tc;
-  h->tc_kind = 1;
-  if (const char* e = getenv("B2OT_EMP_KIND")) h->tc_kind = (strcmp(e, "tf32") == 0) ? 0 : 1;
-  h->kc = h->tc_kind ? (d + 63) / 64 : L.kc;   // the workspace is sized for the (larger) TF32 packing
+  h->tc_kind = 1;                              // 3xFP16 scaled split; b2ot_emp_set_operand switches to 3xTF32
+  h->kc = (d + 63) / 64;                       // the workspace is sized for the (larger) TF32 packing
   h->tc_scales = (float*)((char*)(ws + L.off_xchg) + 64);
   h->packs = ws + L.off_packs;
   h->packt = ws + L.off_packt;
@@ -399,6 +401,15 @@ extern "C" int b2ot_emp_create(b2ot_emp** handle, int dtype, int64_t n, int64_t 
     return -2;
   }
   *handle = h;
+  return 0;
+}
+
+extern "C" int b2ot_emp_set_operand(b2ot_emp* h, int operand) {
+  B2OT_REQUIRE(h != nullptr, "b2ot_emp_set_operand: null handle");
+  B2OT_REQUIRE(operand == B2OT_EMP_OPERAND_F16 || operand == B2OT_EMP_OPERAND_TF32,
+               "b2ot_emp_set_operand: bad operand kind %d", operand);
+  h->tc_kind = operand == B2OT_EMP_OPERAND_TF32 ? 0 : 1;
+  h->kc = h->tc_kind ? (h->d + 63) / 64 : (h->d + TC_KCH - 1) / TC_KCH;
   return 0;
 }
 
@@ -477,6 +488,43 @@ extern "C" int b2ot_emp_init(b2ot_emp* h, const void* f0, const void* g0) {
 extern "C" int b2ot_emp_iterate(b2ot_emp* h, int n_iters) {
   B2OT_REQUIRE(h != nullptr, "b2ot_emp_iterate: null handle");
   return h->dtype == B2OT_F32 ? emp_iterate_t<float>(h, n_iters) : emp_iterate_t<double>(h, n_iters);
+}
+
+// Measurement aid: n_iters iterations with CUDA events (on the solve's stream) around each of the two sweep
+// launches of an iteration; reports the average duration of ONE sweep kernel and of a whole iteration.
+extern "C" int b2ot_emp_profile(b2ot_emp* h, int n_iters, float* sweep_ms_avg, float* iter_ms_avg) {
+  B2OT_REQUIRE(h != nullptr && n_iters >= 1 && n_iters <= 1024, "b2ot_emp_profile: bad arguments");
+  std::vector<cudaEvent_t> ev(4 * (size_t)n_iters + 1);
+  for (auto& e : ev) B2OT_CUDA(cudaEventCreate(&e));
+  const bool f32 = h->dtype == B2OT_F32;
+  int rc = 0;
+  for (int it = 0; it < n_iters && rc == 0; ++it) {
+    B2OT_CUDA(cudaEventRecord(ev[4 * it], h->stream));
+    rc = f32 ? launch_lse_pass<float>(h, true) : launch_lse_pass<double>(h, true);
+    B2OT_CUDA(cudaEventRecord(ev[4 * it + 1], h->stream));
+    if (rc == 0) rc = f32 ? launch_fin_f<float>(h) : launch_fin_f<double>(h);
+    B2OT_CUDA(cudaEventRecord(ev[4 * it + 2], h->stream));
+    if (rc == 0) rc = f32 ? launch_lse_pass<float>(h, false) : launch_lse_pass<double>(h, false);
+    B2OT_CUDA(cudaEventRecord(ev[4 * it + 3], h->stream));
+    if (rc == 0) rc = f32 ? launch_fin_g<float>(h) : launch_fin_g<double>(h);
+  }
+  if (rc == 0) {
+    B2OT_CUDA(cudaEventRecord(ev[4 * n_iters], h->stream));
+    B2OT_CUDA(cudaStreamSynchronize(h->stream));
+    double sweep = 0.0;
+    for (int it = 0; it < n_iters; ++it) {
+      float a = 0.f, b = 0.f;
+      B2OT_CUDA(cudaEventElapsedTime(&a, ev[4 * it], ev[4 * it + 1]));
+      B2OT_CUDA(cudaEventElapsedTime(&b, ev[4 * it + 2], ev[4 * it + 3]));
+      sweep += a + b;
+    }
+    float total = 0.f;
+    B2OT_CUDA(cudaEventElapsedTime(&total, ev[0], ev[4 * n_iters]));
+    if (sweep_ms_avg) *sweep_ms_avg = (float)(sweep / (2.0 * n_iters));
+    if (iter_ms_avg) *iter_ms_avg = total / n_iters;
+  }
+  for (auto& e : ev) cudaEventDestroy(e);
+  return rc;
 }
 
 extern "C" int b2ot_emp_info(const b2ot_emp* h, int* variant, int* nsplit_rows, int* nsplit_cols) {

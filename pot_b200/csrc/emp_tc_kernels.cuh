@@ -275,11 +275,19 @@ __device__ __forceinline__ void mbar_wait_guard(uint64_t* bar, uint32_t parity) 
   }
 }
 
+// Pipeline trace and experiment switches exist only in the diagnosis build (-DB2OT_DIAG, `make DIAG=1`); in the
+// product build both macros fold to nothing and the kernel carries no such branches.
+#ifdef B2OT_DIAG
 #define B2OT_TRACE(slot, t)                                                                     \
   do {                                                                                          \
     if (p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && (t) < 256)                  \
       p.trace[(t) * 8 + (slot)] = clock64();                                                    \
   } while (0)
+#define TC_DBG(bit) (p.dbg & (bit))
+#else
+#define B2OT_TRACE(slot, t) do { } while (0)
+#define TC_DBG(bit) false
+#endif
 
 struct EmpTcParams {
   const float* Apack;   // row operand, packed tiles
@@ -371,7 +379,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
           const uint32_t ph = (uint32_t)((qn / TC_NB) & 1);
           mbar_wait_guard(&b_empty[s], ph ^ 1u);
           B2OT_TRACE(0, t);
-          if ((p.dbg & 8) && qn >= TC_NB) {  // experiment: no refills (stale operands), handshake only
+          if (TC_DBG(8) && qn >= TC_NB) {  // experiment: no refills (stale operands), handshake only
             mbar_arrive(&b_full[s]);
             continue;
           }
@@ -427,7 +435,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
               const uint32_t off_lo = off_hi + TC_SUB;
               const uint64_t ah = umma_desc_sw128(a_chunk + off_hi), al = umma_desc_sw128(a_chunk + off_lo);
               const uint64_t bh = umma_desc_sw128(b_addr + off_hi), bl = umma_desc_sw128(b_addr + off_lo);
-              if (p.dbg & 4) continue;
+              if (TC_DBG(4)) continue;
               if (p.kind == 0) {
                 umma_tf32(d_tmem, al, bh, TC_IDESC, acc);  // small terms first
                 umma_tf32(d_tmem, ah, bl, TC_IDESC, 1u);
@@ -501,7 +509,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
       //   P2: online (max, sum 2^x) update.  Packed fp32x2 arithmetic throughout.
       auto phase1 = [&](uint32_t (&v)[32], int ch) -> float {
         float c0 = -CUDART_INF_F, c1 = -CUDART_INF_F;
-        if (p.dbg & 2) return c0;
+        if (TC_DBG(2)) return c0;
 #pragma unroll
         for (int g4 = 0; g4 < 8; ++g4) {
           const float4 bq = *reinterpret_cast<const float4*>(cB + ch * 32 + g4 * 4);
@@ -526,7 +534,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
         return fmaxf(c0, c1);
       };
       auto phase2 = [&](const uint32_t (&v)[32], float cmax) {
-        if (p.dbg & 2) {
+        if (TC_DBG(2)) {
           s_run += __uint_as_float(v[0]);
           return;
         }
@@ -540,7 +548,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
                 a3 = __uint_as_float(v[e + 3]);
           add2(a0, a1, nm, nm);
           add2(a2, a3, nm, nm);
-          if (!(p.dbg & 1)) {
+          if (!TC_DBG(1)) {
             a0 = ex2_ftz(a0);
             a1 = ex2_ftz(a1);
             a2 = ex2_ftz(a2);
@@ -552,7 +560,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
         s_run = (s0 + s1) + (s2 + s3);
         m_run = m_new;
       };
-      if (p.dbg & 16) {  // experiment: no TMEM reads
+      if (TC_DBG(16)) {  // experiment: no TMEM reads
         tc_fence_before();
         mbar_arrive(&acc_empty[as]);
         continue;

@@ -51,11 +51,22 @@ constexpr size_t kPinnedBlock = 1024;
 void* pinned_acquire(size_t bytes);   // nullptr on failure; bytes <= kPinnedBlock
 void pinned_release(void* p);
 
-// Programmatic dependent launch of the per-iteration kernels (B2OT_PDL=0 turns it off): the kernel may start while
+// Tuning / diagnosis switches (B2OT_STAGES, B2OT_CLUSTERS, B2OT_PDL, B2OT_EMP_DBG, ...) are read from the environment
+// ONLY in a diagnosis build (`make DIAG=1`, -DB2OT_DIAG): the product library ignores the environment altogether.
+inline const char* diag_env(const char* name) {
+#ifdef B2OT_DIAG
+  return getenv(name);
+#else
+  (void)name;
+  return nullptr;
+#endif
+}
+
+// Programmatic dependent launch of the per-iteration kernels (diagnosis build: B2OT_PDL=0 turns it off): the kernel may start while
 // the previous kernel of the stream is still finishing; it blocks in griddepcontrol.wait before touching its results.
 inline bool pdl_enabled() {
   static const bool on = [] {
-    const char* e = getenv("B2OT_PDL");
+    const char* e = diag_env("B2OT_PDL");
     return !(e && e[0] == '0');
   }();
   return on;

@@ -120,7 +120,7 @@ class EmpiricalSolver:
     """One online-cost solve (or one block of source points of a sharded solve) on the current device."""
 
     def __init__(self, X_s, X_t, a, b, reg, metric="sqeuclidean", max_iter=10000, stop_thr=1e-9, variant="auto",
-                 group=None, exchange="peer"):
+                 group=None, exchange="peer", operand="f16"):
         self.lib = _lib.load()
         self.X_s, self.X_t = X_s, X_t
         self.n, self.m, self.d = X_s.shape[0], X_t.shape[0], X_s.shape[1]
@@ -143,6 +143,12 @@ class EmpiricalSolver:
         self.h = h
         self._cb = None
         self.comm = None
+        try:
+            op = {"f16": _lib.EMP_OPERAND_F16, "tf32": _lib.EMP_OPERAND_TF32}[operand]
+        except KeyError:
+            raise ValueError(f"unknown operand split {operand!r} (f16 | tf32)") from None
+        _lib.check(self.lib.b2ot_emp_set_operand(self.h, op), "b2ot_emp_set_operand")
+        self.operand = operand
         if group is not None:
             if exchange == "peer":
                 from .comm import get_comm
@@ -190,6 +196,13 @@ class EmpiricalSolver:
         with torch.cuda.device(self.device):
             _lib.check(self.lib.b2ot_emp_iterate(self.h, int(k)), "b2ot_emp_iterate")
 
+    def profile(self, k):
+        """k iterations with CUDA events around each sweep launch -> (one-sweep ms avg, iteration ms avg)."""
+        a, b = C.c_float(), C.c_float()
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.b2ot_emp_profile(self.h, int(k), C.byref(a), C.byref(b)), "b2ot_emp_profile")
+        return a.value, b.value
+
     def poll(self):
         st, it = C.c_int(), C.c_int()
         with torch.cuda.device(self.device):
@@ -233,7 +246,8 @@ def _unif(n, like):
     return torch.full((n,), 1.0 / n, dtype=like.dtype, device=like.device)
 
 
-def _lazy_solve(X_s, X_t, reg, a, b, metric, numIterMax, stopThr, batchSize, verbose, warn, warmstart, variant="auto"):
+def _lazy_solve(X_s, X_t, reg, a, b, metric, numIterMax, stopThr, batchSize, verbose, warn, warmstart, variant="auto",
+                operand="f16"):
     if isinstance(batchSize, int):
         pass
     elif isinstance(batchSize, tuple) and len(batchSize) == 2:
@@ -246,7 +260,8 @@ def _lazy_solve(X_s, X_t, reg, a, b, metric, numIterMax, stopThr, batchSize, ver
         g0 = torch.zeros(nt, dtype=X_s.dtype, device=X_s.device)
     else:
         f0, g0 = (w.detach().to(X_s.dtype).contiguous() for w in warmstart)
-    solver = EmpiricalSolver(X_s, X_t, a, b, reg, metric, max_iter=numIterMax, stop_thr=stopThr, variant=variant)
+    solver = EmpiricalSolver(X_s, X_t, a, b, reg, metric, max_iter=numIterMax, stop_thr=stopThr, variant=variant,
+                             operand=operand)
     status, niter, _ = solver.solve(f0, g0)
     f, g, errs = solver.export()
     solver.close()
@@ -279,7 +294,8 @@ def empirical_sinkhorn(X_s, X_t, reg, a=None, b=None, metric="sqeuclidean", numI
     X_s, X_t, a, b = _prep(X_s, X_t, a, b)
     if isLazy:
         f, g, errs, niter = _lazy_solve(X_s, X_t, reg, a, b, metric, int(numIterMax), float(stopThr), batchSize,
-                                        verbose, warn, warmstart, kwargs.get("b2ot_variant", "auto"))
+                                        verbose, warn, warmstart, kwargs.get("b2ot_variant", "auto"),
+                                        kwargs.get("b2ot_operand", "f16"))
         if log:
             dict_log = {"err": [torch.tensor(e, dtype=X_s.dtype, device=X_s.device) for e in errs], "u": f, "v": g,
                         "niter": niter, "lazy_plan": get_sinkhorn_lazytensor(X_s, X_t, f, g, metric, reg)}
@@ -301,7 +317,8 @@ def empirical_sinkhorn2(X_s, X_t, reg, a=None, b=None, metric="sqeuclidean", num
     if isLazy:
         lib = _lib.load()
         f, g, errs, niter = _lazy_solve(X_s, X_t, reg, a, b, metric, int(numIterMax), float(stopThr), batchSize,
-                                        verbose, warn, warmstart, kwargs.get("b2ot_variant", "auto"))
+                                        verbose, warn, warmstart, kwargs.get("b2ot_variant", "auto"),
+                                        kwargs.get("b2ot_operand", "f16"))
         ns, nt, d = X_s.shape[0], X_t.shape[0], X_s.shape[1]
         code = _dense.dtype_code(X_s.dtype)
         out = torch.empty((), dtype=torch.float64, device=X_s.device)

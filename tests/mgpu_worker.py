@@ -26,16 +26,27 @@ from oracle import sinkhorn_oracle as orc  # noqa: E402
 from pot_b200.comm import get_comm  # noqa: E402
 from oracle import solvers_oracle as sorc  # noqa: E402
 from pot_b200.sharded import (empirical_sinkhorn_sharded, shard_rows, sinkhorn_knopp_sharded,  # noqa: E402
-                              sinkhorn_log_sharded, solve_sharded)
+                              sinkhorn_log_sharded, solve_batch_sharded, solve_sharded)
 
 
 def main():
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
+    one_device = os.environ.get("MGPU_ONE_DEVICE", "0") == "1"
+    if one_device:
+        # every rank on cuda:0 (a box with ONE GPU): NCCL refuses two ranks per device, so the process group is gloo
+        # (host plumbing + the "nccl"-hook baseline exchange staged through the host); the peer exchange maps the
+        # other process's buffer with CUDA IPC on the same device and runs exactly the multi-GPU kernels.
+        local = 0
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    dist.init_process_group("nccl", device_id=dev)
+    if one_device:
+        dist.init_process_group("gloo")
+    else:
+        dist.init_process_group("nccl", device_id=dev)
     group = dist.group.WORLD
+    long_its = 300 if one_device else 2000  # two processes time-slice one GPU: every exchange costs a context switch
+    ar_reps = 40 if one_device else 300
 
     def check(cond, msg):
         if not cond:
@@ -46,7 +57,7 @@ def main():
     comm = get_comm(group, dev, 1 << 20)
     g = torch.Generator(device=dev).manual_seed(100 + rank)
     for dt in (torch.float32, torch.float64):
-        for it in range(300):
+        for it in range(ar_reps):
             n = 1 + (it * 37) % 5000
             x = torch.randn(n, dtype=dt, device=dev, generator=g)
             ref = x.clone()
@@ -82,7 +93,7 @@ def main():
                           torch.as_tensor(b, device=dev))
             for name, fn, ofn, key in (("knopp", sinkhorn_knopp_sharded, orc.sinkhorn_knopp, "u"),
                                        ("log", sinkhorn_log_sharded, orc.sinkhorn_log, "log_u")):
-                for kw in (dict(numItermax=60, stopThr=0.0), dict(numItermax=2000, stopThr=1e-7 if dtype == np.float64 else 1e-5)):
+                for kw in (dict(numItermax=60, stopThr=0.0), dict(numItermax=long_its, stopThr=1e-7 if dtype == np.float64 else 1e-5)):
                     with warnings.catch_warnings():
                         warnings.simplefilter("ignore")
                         G, lg = fn(al, bd, Ml, 0.1, log=True, group=group, n_total=n, exchange=exchange, **kw)
@@ -132,7 +143,7 @@ def main():
     for exchange in ("peer", "nccl"):
         for dtype, tol in ((np.float64, 1e-10), (np.float32, 1e-4)):
             X, Y = xs.astype(dtype), xt.astype(dtype)
-            for kw in (dict(numIterMax=30, stopThr=-1.0), dict(numIterMax=3000, stopThr=1e-8 if dtype == np.float64 else 1e-4)):
+            for kw in (dict(numIterMax=30, stopThr=-1.0), dict(numIterMax=long_its if one_device else 3000, stopThr=1e-8 if dtype == np.float64 else 1e-4)):
                 with warnings.catch_warnings():
                     warnings.simplefilter("ignore")
                     f, gg, lg = empirical_sinkhorn_sharded(torch.as_tensor(X[r0:r1], device=dev), torch.as_tensor(Y, device=dev),
@@ -144,6 +155,34 @@ def main():
                 check(ef < tol and eg < tol, f"emp {exchange} {dtype.__name__} potentials err {ef:.2e} {eg:.2e}")
         if rank == 0:
             print(f"empirical sharded ok ({exchange})", flush=True)
+
+    # ---- 5. batched solver, whole problems sharded (no communication in the iterations) ----
+    B, bn, bm = 11, 40, 33  # 11 problems: ragged split
+    X, Y = rng.randn(B, bn, 2), rng.randn(B, bm, 2) + 1.0
+    Mb = orc.dist_sqeuclidean_batch(X, Y)
+    Mb /= Mb.max()
+    # problem-dependent conditioning, so that the shards converge at different iterations
+    Mb *= np.linspace(0.5, 2.0, B)[:, None, None]
+    p0, p1 = shard_rows(B, world, rank)
+    for dtype, tol in ((np.float64, 1e-10), (np.float32, 1e-4)):
+        Md = Mb.astype(dtype)
+        for solver in ("log_sinkhorn", "sinkhorn"):
+            for rt in ("entropy", "kl"):
+                for kw in (dict(max_iter=40, tol=0.0), dict(max_iter=500, tol=1e-6 if dtype == np.float64 else 1e-4)):
+                    ref = orc.solve_batch(Md, 0.1, solver=solver, reg_type=rt, **kw)
+                    res = solve_batch_sharded(torch.as_tensor(Md[p0:p1], device=dev), 0.1, solver=solver, reg_type=rt,
+                                              group=group, **kw)
+                    check(res.log["n_iter"] == ref["n_iter"],
+                          f"batch {solver} {rt} {dtype.__name__} n_iter {res.log['n_iter']} vs {ref['n_iter']} ({kw})")
+                    P, Pr = res.plan.cpu().numpy().astype(np.float64), ref["plan"][p0:p1].astype(np.float64)
+                    err = np.abs(P - Pr) / (np.abs(Pr) + 1e-6 * ref["plan"].max())
+                    check(err.max() < tol, f"batch {solver} {rt} {dtype.__name__} plan rel err {err.max():.3e}")
+                    for key, got in (("value", res.value), ("value_linear", res.value_linear)):
+                        rv = ref[key][p0:p1]
+                        ev = np.abs(got.cpu().numpy() - rv).max() / np.abs(ref[key]).max()
+                        check(ev < tol, f"batch {solver} {rt} {dtype.__name__} {key} err {ev:.2e}")
+    if rank == 0:
+        print("batch sharded ok", flush=True)
 
     dist.barrier()
     if rank == 0:

@@ -157,3 +157,145 @@ def test_config3_stabilized_absorbing_iterations():
     assert abs(errs[-1] - ref_err) <= 1e-3 * ref_err
     # and the plan really is close to feasible: un-scaled column violation small and decreasing over the run
     assert (col - b.double()).norm().item() < 1e-4
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Config 3: the reference loop itself, restated in chunked fp64 torch (ot/bregman/_sinkhorn.py:626-631:
+# KtransposeU = K^T u; v = b / KtransposeU; u = 1 / (Kp v)), 10 full iterations at 65536^2, compared on (u, v).
+# ------------------------------------------------------------------------------------------------------------------
+def test_config3_ten_iterations_vs_fp64_restatement(gibbs_kernel):
+    K = gibbs_kernel
+    a = torch.full((N,), 1.0 / N, device=DEV)
+    b = torch.full((N,), 1.0 / N, device=DEV)
+    its = 10
+    u1, v1, e1, n1, st1, info = _run(K, a, b, "fused", its)
+    assert st1 == _lib.ST_MAXITER and n1 == its - 1 and info["variant"] == "fused"
+    u = torch.full((N,), 1.0 / N, dtype=torch.float64, device=DEV)  # reference init (:585-590)
+    a64, b64 = a.double(), b.double()
+    err0 = None
+    for ii in range(its):
+        ktu = _matvec64(K, u, transpose=True)
+        v = b64 / ktu
+        u = a64 / _matvec64(K, v)
+        if ii == 0:  # :647-657, the check of ii % 10 == 0: tmp2 = einsum("i,ij,j->j", u, K, v)
+            err0 = (v * _matvec64(K, u, transpose=True) - b64).norm().item()
+    assert ((u1.double() - u).abs() / u.abs()).max().item() < 1e-4
+    assert ((v1.double() - v).abs() / v.abs()).max().item() < 1e-4
+    assert len(e1) == 1 and abs(e1[0] - err0) <= 1e-3 * err0 + 1e-9, (e1, err0)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Golden vectors of the UNMODIFIED reference at the BASELINE sizes (tests/golden/make_golden_fullsize.py;
+# inputs regenerated from the seeds by tests/fullsize_inputs.py).
+# ------------------------------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def gfull():
+    import os
+
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_fullsize.npz")
+    return np.load(path, allow_pickle=False)
+
+
+def _maxrel_log(x, ref):
+    x, ref = np.asarray(x, dtype=np.float64), np.asarray(ref, dtype=np.float64)
+    return np.abs(x - ref).max() / max(1.0, np.abs(ref).max())
+
+
+def test_config2_golden_16384(gfull):
+    """BASELINE config 2: ot.bregman.sinkhorn_log, n = m = 16384 fp32, reg 0.01 -- the fp32 ping-pong sweep against the
+    reference's own (log_u, log_v, err) after 20 fixed iterations, 1e-4 relative (north_star's fp32 tolerance)."""
+    import warnings
+
+    import pot_b200 as ot
+    import fullsize_inputs as fin
+
+    a, b, M = fin.config2_inputs()
+    Md = torch.from_numpy(M).to(DEV)
+    del M
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        G, lg = ot.bregman.sinkhorn_log(torch.from_numpy(a).to(DEV), torch.from_numpy(b).to(DEV), Md, fin.C2_REG,
+                                        numItermax=fin.C2_ITS, stopThr=0, log=True, warn=False)
+    assert lg["niter"] == int(gfull["c2/niter"])
+    assert _maxrel_log(lg["log_u"].cpu().numpy(), gfull["c2/log_u"]) < 1e-4
+    assert _maxrel_log(lg["log_v"].cpu().numpy(), gfull["c2/log_v"]) < 1e-4
+    e, r = np.asarray([float(x) for x in lg["err"]]), gfull["c2/err"]
+    assert e.shape == r.shape and np.all(np.abs(e - r) <= 5e-3 * r + 2e-6), (e, r)
+    # marginals of the returned plan: u was updated last, so rows are exact to fp32 round-off
+    assert float((G.sum(1) - 1.0 / fin.C2_N).abs().max()) < 1e-4 / fin.C2_N
+
+
+@pytest.mark.parametrize("operand", ["f16", "tf32"])
+def test_config4_golden_16384(gfull, operand):
+    """BASELINE config 4's path (online cost, log domain, d = 64, fp32, 128 x 128 tcgen05 tiles, several reduction
+    splits) at n = m = 16384 against the reference's own (f, g, err) after 10 fixed iterations; both operand splits."""
+    import warnings
+
+    import pot_b200 as ot
+    import fullsize_inputs as fin
+
+    X, Y = fin.config4_inputs()
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        f, g, lg = ot.empirical_sinkhorn(torch.from_numpy(X).to(DEV), torch.from_numpy(Y).to(DEV), fin.C4_REG,
+                                         numIterMax=fin.C4_ITS, stopThr=-1.0, isLazy=True, log=True, warn=False,
+                                         b2ot_variant="tc", b2ot_operand=operand)
+    assert _maxrel_log(f.cpu().numpy(), gfull["c4/f"]) < 1e-4
+    assert _maxrel_log(g.cpu().numpy(), gfull["c4/g"]) < 1e-4
+    e, r = np.asarray([float(x) for x in lg["err"]]), gfull["c4/err"]
+    assert e.shape == r.shape and np.all(np.abs(e - r) <= 5e-3 * r + 2e-5), (e, r)
+
+
+@pytest.mark.parametrize("operand", ["f16", "tf32"])
+def test_config4_65536_vs_fp64(operand):
+    """The tcgen05 sweep at n = m = 65536, d = 64 (multi-wave grid, 4-7 reduction splits) against (i) the library's
+    fp64 register-tiled sweep on the same clouds and (ii) one half-iteration restated in chunked fp64 torch
+    (ot/bregman/_empirical.py:218-233: f = -logsumexp(g - C/reg) + log a)."""
+    import warnings
+
+    import pot_b200 as ot
+
+    n, d, reg, its = 65536, 64, 0.1, 4
+    gen = torch.Generator(device=DEV).manual_seed(41)
+    X = torch.randn(n, d, device=DEV, generator=gen) / d ** 0.5
+    Y = torch.randn(n, d, device=DEV, generator=gen) / d ** 0.5 + 1.0 / d ** 0.5
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        f, g = ot.empirical_sinkhorn(X, Y, reg, numIterMax=its, stopThr=-1.0, isLazy=True, warn=False,
+                                     b2ot_variant="tc", b2ot_operand=operand)
+        f64, g64 = ot.empirical_sinkhorn(X.double(), Y.double(), reg, numIterMax=its, stopThr=-1.0, isLazy=True,
+                                         warn=False, b2ot_variant="simt")
+    assert _maxrel_log(f.cpu().numpy(), f64.cpu().numpy()) < 1e-4
+    assert _maxrel_log(g.cpu().numpy(), g64.cpu().numpy()) < 1e-4
+    # (ii) the last half-step of the solve (g from f) in chunked fp64 torch, from the fp32 f the kernel produced
+    Xd, Yd = X.double(), Y.double()
+    xx, yy = (Xd * Xd).sum(1), (Yd * Yd).sum(1)
+    logb = -np.log(n)
+    g_ref = torch.empty(n, dtype=torch.float64, device=DEV)
+    fd = f.double()
+    for j0 in range(0, n, 2048):
+        C = (yy[j0:j0 + 2048, None] + xx[None, :] - 2.0 * Yd[j0:j0 + 2048] @ Xd.t()).clamp_(min=0)
+        g_ref[j0:j0 + 2048] = logb - torch.logsumexp(fd[None, :] - C / reg, dim=1)
+    assert _maxrel_log(g.cpu().numpy(), g_ref.cpu().numpy()) < 1e-4
+
+
+@pytest.mark.parametrize("solver", ["log_sinkhorn", "sinkhorn"])
+def test_config5_golden_full(gfull, solver):
+    """BASELINE config 5 at FULL size (4096 problems of 256 x 256 fp32): ot.batch.solve_batch against the reference's own
+    values for every problem and potentials of the first 8, 20 fixed iterations."""
+    import pot_b200 as ot
+    import fullsize_inputs as fin
+
+    Mb = torch.from_numpy(fin.config5_inputs()).to(DEV)
+    res = ot.batch.solve_batch(Mb, fin.C5_REG, max_iter=fin.C5_ITS, tol=0, solver=solver, reg_type="entropy")
+    for key, got in (("value", res.value), ("value_linear", res.value_linear)):
+        ref = gfull[f"c5/{solver}/{key}"].astype(np.float64)
+        err = np.abs(got.cpu().numpy().astype(np.float64) - ref).max() / np.abs(ref).max()
+        assert err < 1e-4, (key, err)
+    fh, gh = res.potentials[0][:8].cpu().numpy(), res.potentials[1][:8].cpu().numpy()
+    rf, rg = gfull[f"c5/{solver}/f_head"].astype(np.float64), gfull[f"c5/{solver}/g_head"].astype(np.float64)
+    # same start (zeros / ones) and same update order as the reference: the potentials agree without a gauge shift
+    if solver == "log_sinkhorn":
+        assert _maxrel_log(fh, rf) < 1e-4 and _maxrel_log(gh, rg) < 1e-4
+    else:  # scalings (f, g) of bregman_projection_batch, ot/batch/_utils.py:138-160
+        assert (np.abs(fh - rf) / np.abs(rf)).max() < 1e-4 and (np.abs(gh - rg) / np.abs(rg)).max() < 1e-4

@@ -190,6 +190,28 @@ int b2ot_batch_solve(int mode, int dtype, int64_t B, int64_t n, int64_t m, const
                      double* value_linear, double* value_reg, int reg_type, int max_iter, double tol, void* workspace,
                      size_t workspace_bytes, int* n_iters, int flags, void* stream);
 
+/* ---- batched cost matrices and per-problem reductions of ot.batch ----
+ * b2ot_batch_dist replaces ot.batch.dist_batch (ot/batch/_linear.py:178-233): out[b] = dist(X[b], Y[b]) for
+ *   X (B, n, d), Y (B, m, d), out (B, n, m), all contiguous, in ONE launch (bound by the HBM write of out):
+ *   SQEUCLIDEAN |x|^2 + |y|^2 - 2 x.y and EUCLIDEAN = its square root, both WITHOUT the clamp at 0 that ot.dist
+ *   applies (dist_euclidean_batch, :54-85 -- tiny negative values / nan under the root are the reference's behaviour);
+ *   MINKOWSKI (sum_d w_d |x - y|^p)^(1/p) (dist_lp_batch with q = 1, :19-51; w may be null);
+ *   KL sum_d y log(y + eps) - sum_d y log(x + eps) (dist_kl_batch, logits_X = False, :88-120, eps 1e-10 there).
+ * b2ot_batch_reduce: out[b] = sign * sum over the (n, m) plane of A*Bm (DOT: loss_linear_batch, :123-147) or of
+ *   A*log(A + eps) (ENTROPY with sign -1: entropy_batch, ot/batch/_utils.py:4-22); `per` = n*m elements per problem,
+ *   out = B values of `dtype`; fp64 accumulation in a fixed order (deterministic); one HBM read of the operands. */
+#define B2OT_BMETRIC_SQEUCLIDEAN 0
+#define B2OT_BMETRIC_EUCLIDEAN 1
+#define B2OT_BMETRIC_MINKOWSKI 2
+#define B2OT_BMETRIC_KL 3
+#define B2OT_BREDUCE_DOT 0
+#define B2OT_BREDUCE_ENTROPY 1
+int b2ot_batch_dist(int dtype, const void* X, const void* Y, int64_t B, int64_t n, int64_t m, int d, int metric,
+                    double p, const void* w, double eps, void* out, void* stream);
+size_t b2ot_batch_reduce_scratch_bytes(int64_t B, int64_t per);
+int b2ot_batch_reduce(int dtype, int op, const void* A, const void* Bm, int64_t B, int64_t per, double eps,
+                      double sign, void* out, void* scratch_dev, void* stream);
+
 /* ---- online-cost (empirical) Sinkhorn: cost rebuilt from the point clouds, never materialised ----
  * Replaces the lazy branch of ot.bregman.empirical_sinkhorn (ot/bregman/_empirical.py:193-271): log-domain
  * updates f = log a - LSE_j(g_j - C_ij/reg), g = log b - LSE_i(f_i - C_ij/reg) (f first, :218-233) with

@@ -365,3 +365,32 @@ def solve_batch(M, reg, a=None, b=None, max_iter=1000, tol=1e-5,
         value = None
     return {"value": value, "value_linear": value_linear, "plan": T,
             "potentials": out["potentials"], "n_iter": out["n_iters"]}
+
+
+def dist_batch(X1, X2=None, metric="sqeuclidean", p=2):
+    """Batched cost matrices (ot/batch/_linear.py:178-233): sqeuclidean / euclidean without clamp (:79-85),
+    minkowski = dist_lp_batch with q = 1 (:46-51), kl = dist_kl_batch with logits_X False, eps 1e-10 (:112-120)."""
+    X2 = X1 if X2 is None else X2
+    metric = metric.lower()
+    if metric == "sqeuclidean":
+        return dist_sqeuclidean_batch(X1, X2)
+    if metric == "euclidean":
+        return np.sqrt(dist_sqeuclidean_batch(X1, X2))
+    if metric == "minkowski":
+        Mp = (np.abs(X1[:, :, None] - X2[:, None, :]) ** p).sum(axis=-1)
+        return Mp ** (1 / p) if p != 1 else Mp
+    if metric == "kl":
+        eps = 1e-10
+        entr_y = np.sum(X2 * np.log(X2 + eps), axis=-1)
+        return entr_y[:, None, :] - np.sum(X2[:, None, :] * np.log(X1 + eps)[:, :, None], axis=-1)
+    raise ValueError(f"Unknown metric: {metric}")
+
+
+def loss_linear_batch(M, T):
+    """sum_ij M_bij T_bij (ot/batch/_linear.py:147)."""
+    return np.sum(M * T, axis=(1, 2))
+
+
+def entropy_batch(T, eps=1e-16):
+    """-sum_ij T log(T + eps) (ot/batch/_utils.py:22)."""
+    return -np.sum(T * np.log(T + eps), axis=(1, 2))

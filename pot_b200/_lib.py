@@ -69,6 +69,11 @@ PROTOTYPES = {
                                    C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double,
                                    C.c_void_p, C.c_size_t, C.POINTER(C.c_int), C.c_int, C.c_void_p]),
+    "b2ot_batch_dist": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int, C.c_int,
+                                  C.c_double, C.c_void_p, C.c_double, C.c_void_p, C.c_void_p]),
+    "b2ot_batch_reduce_scratch_bytes": (C.c_size_t, [C.c_int64, C.c_int64]),
+    "b2ot_batch_reduce": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_double,
+                                    C.c_double, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b2ot_emp_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "b2ot_emp_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "b2ot_emp_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.c_int64, C.c_int, C.c_void_p,
@@ -110,6 +115,8 @@ ST_COMM_TIMEOUT = 5
 IPC_HANDLE_BYTES = 64
 METRIC_SQEUCLIDEAN, METRIC_EUCLIDEAN = 0, 1
 EMP_AUTO, EMP_SIMT, EMP_TC = 0, 1, 2
+BMETRIC = {"sqeuclidean": 0, "euclidean": 1, "minkowski": 2, "kl": 3}
+BREDUCE_DOT, BREDUCE_ENTROPY = 0, 1
 EMP_OPERAND_F16, EMP_OPERAND_TF32 = 0, 1
 
 _lib = None

@@ -18,7 +18,7 @@ import warnings
 
 import torch
 
-from . import _dense
+from . import _autograd, _dense
 
 __all__ = ["sinkhorn", "sinkhorn2", "sinkhorn_knopp", "sinkhorn_log"]
 
@@ -117,9 +117,11 @@ def sinkhorn_knopp(a, b, M, reg, numItermax=1000, stopThr=1e-9, verbose=False, l
     """
     from . import _lib
 
-    M = _require_cuda_matrix(M)
-    a = _weights(a, M.shape[0], M, "a")
-    b = _weights(b, M.shape[1], M, "b")
+    if not kwargs.get("b2ot_no_grad_warning"):
+        _autograd.warn_detached("sinkhorn_knopp", M, a, b)
+    M = _require_cuda_matrix(M).detach()
+    a = _weights(a, M.shape[0], M, "a").detach()
+    b = _weights(b, M.shape[1], M, "b").detach()
     variant = kwargs.get("b2ot_variant", "auto")
     if b.dim() > 1:
         return _multi_hist(sinkhorn_knopp, a, b, M, reg, numItermax, stopThr, verbose, log, warn, warmstart, kwargs)
@@ -147,9 +149,11 @@ def sinkhorn_log(a, b, M, reg, numItermax=1000, stopThr=1e-9, verbose=False, log
     """
     from . import _lib
 
-    M = _require_cuda_matrix(M)
-    a = _weights(a, M.shape[0], M, "a")
-    b = _weights(b, M.shape[1], M, "b")
+    if not kwargs.get("b2ot_no_grad_warning"):
+        _autograd.warn_detached("sinkhorn_log", M, a, b)
+    M = _require_cuda_matrix(M).detach()
+    a = _weights(a, M.shape[0], M, "a").detach()
+    b = _weights(b, M.shape[1], M, "b").detach()
     variant = kwargs.get("b2ot_variant", "auto")
     if b.dim() > 1:
         return _multi_hist(sinkhorn_log, a, b, M, reg, numItermax, stopThr, verbose, log, warn, warmstart, kwargs)
@@ -166,7 +170,7 @@ def sinkhorn_log(a, b, M, reg, numItermax=1000, stopThr=1e-9, verbose=False, log
     return G
 
 
-def _multi_hist(fn, a, b, M, reg, numItermax, stopThr, verbose, log, warn, warmstart, kwargs):
+def _multi_hist(fn, a, b, M, reg, numItermax, stopThr, verbose, log, warn, warmstart, kwargs, attach=None):
     """2-D ``b``: one solve per histogram, losses only (_sinkhorn.py:676-681 and :819-854).
 
     The reference's knopp runs the histograms jointly (joint stop test on the stacked error);
@@ -195,7 +199,8 @@ def _multi_hist(fn, a, b, M, reg, numItermax, stopThr, verbose, log, warn, warms
             warnings.warn(_NOCONV)
         if verbose:
             _print_table(errs, after_stop_test=not is_log, stop_thr=None if is_log else stopThr)
-        losses.append(_dense.loss(mode, Kt, Mc, u, v).to(M.dtype))
+        loss_k = _dense.loss(mode, Kt, Mc, u, v).to(M.dtype)
+        losses.append(loss_k if attach is None else attach(loss_k, Kt, u, v, k))
         us.append(u)
         vs.append(v)
     res = torch.stack(losses)
@@ -233,33 +238,55 @@ def sinkhorn2(a, b, M, reg, method="sinkhorn", numItermax=1000, stopThr=1e-9, ve
               warn=False, warmstart=None, **kwargs):
     """Drop-in for ot.sinkhorn2 (_sinkhorn.py:237-484): the loss <M, plan> (1-D b), losses per histogram (2-D b).
 
-    The loss is reduced on the device straight from (K, u, v): the plan is never materialised.
+    The loss is reduced on the device straight from (K, u, v): the plan is never materialised -- unless M, a or b
+    require grad: then the plan is formed once and the loss carries the envelope gradient (plan, reg (f - mean f),
+    reg (g - mean g)) of ot/solvers.py:485-494 (pot_b200/_autograd.py; a UserWarning says that this replaces the
+    reference's unrolled autodiff).
     """
     from . import _lib
 
-    M = _require_cuda_matrix(M)
-    a = _weights(a, M.shape[0], M, "a")
-    b = _weights(b, M.shape[1], M, "b")
+    M0, a0, b0 = M, a, b
+    wants_grad = _autograd.any_requires_grad(M0, a0, b0)
+    M = _require_cuda_matrix(M).detach()
+    a = _weights(a, M.shape[0], M, "a").detach()
+    b = _weights(b, M.shape[1], M, "b").detach()
     name = method.lower()
     if name == "sinkhorn_stabilized":  # :420-432: loss of the stabilized plan
         from . import stabilized
 
+        _autograd.warn_detached("sinkhorn2(method='sinkhorn_stabilized')", M0, a0, b0)
         return stabilized.sinkhorn_stabilized(a, b, M, reg, numItermax=numItermax, stopThr=stopThr,
                                               warmstart=warmstart, verbose=verbose, log=log, warn=warn,
                                               b2ot_loss=True, **kwargs)
     if name not in ("sinkhorn", "sinkhorn_log"):
         raise ValueError("Unknown method '%s'." % method)
-    if b.dim() > 1:
-        return sinkhorn(a, b, M, reg, method=method, numItermax=numItermax, stopThr=stopThr, verbose=verbose,
-                        log=log, warn=warn, warmstart=warmstart, **kwargs)
     mode = "knopp" if name == "sinkhorn" else "log"
+    if wants_grad:
+        warnings.warn(_autograd.ENVELOPE_NOTE)
+    ain = a0 if isinstance(a0, torch.Tensor) and a0.numel() else a
+    bin_ = b0 if isinstance(b0, torch.Tensor) and b0.numel() else b
+
+    def attach(value, Kt, u, v, b_in):
+        if not wants_grad:
+            return value
+        lu, lv = (torch.log(u), torch.log(v)) if mode == "knopp" else (u, v)
+        return _autograd.set_gradients(value, (M0, ain, b_in),
+                                       _autograd.envelope_grads(_dense.plan(mode, Kt, u, v), lu, lv, reg))
+
+    if b.dim() > 1:
+        if not wants_grad:
+            return sinkhorn(a, b, M, reg, method=method, numItermax=numItermax, stopThr=stopThr, verbose=verbose,
+                            log=log, warn=warn, warmstart=warmstart, b2ot_no_grad_warning=True, **kwargs)
+        return _multi_hist(sinkhorn_knopp if mode == "knopp" else sinkhorn_log, a, b, M, reg, numItermax, stopThr,
+                           verbose, log, warn, warmstart, kwargs,
+                           attach=lambda value, Kt, u, v, k: attach(value, Kt, u, v, bin_[:, k]))
     Kt, u, v, errs, niter, status = _solve_dense(mode, a, b, M, reg, int(numItermax), float(stopThr), warmstart,
                                                  kwargs.get("b2ot_variant", "auto"))
     if status == _lib.ST_NUMERR:
         warnings.warn("Warning: numerical errors at iteration %d" % niter)
     elif status == _lib.ST_MAXITER and warn:
         warnings.warn(_NOCONV)
-    value = _dense.loss(mode, Kt, _rowmajor(M), u, v).to(M.dtype)
+    value = attach(_dense.loss(mode, Kt, _rowmajor(M), u, v).to(M.dtype), Kt, u, v, bin_)
     if not log:
         return value
     errl = [torch.tensor(e, dtype=M.dtype, device=M.device) for e in errs]

@@ -30,6 +30,7 @@ struct b2ot_emp {
   int tc_kind;             // 0 = 3xTF32, 1 = 3xFP16 (scaled split)
   float* tc_scales;        // 3xFP16: [s_x, s_y, 1 / (s_x s_y)] followed by the two abs-max words (device)
   void *packs, *packt;
+  float* tc_centre;        // common centre of the clouds (TC_MAX_D floats) followed by the partial sums of its reduction
   b2ot_allreduce_fn ar;
   void* ar_ctx;
   b2ot_comm* comm;  // NVLink peer-memory exchange (takes precedence over the hook)
@@ -87,8 +88,8 @@ int pick_nsplit_tc(long long rows, long long cols) {
 }
 
 struct EmpWs {
-  size_t off_state, off_blk, off_err, off_xchg, off_f, off_g, off_xx, off_yy, off_c, off_pa, off_pb, off_packs,
-      off_packt, total;
+  size_t off_state, off_blk, off_err, off_xchg, off_f, off_g, off_xx, off_yy, off_c, off_pa, off_pb, off_centre,
+      off_packs, off_packt, total;
   int err_cap, nsA, nsB, use_tc, kc;
 };
 EmpWs emp_ws(long long n, long long m, int d, int dtype, int metric, int variant, int max_iter) {
@@ -111,6 +112,8 @@ EmpWs emp_ws(long long n, long long m, int d, int dtype, int metric, int variant
   L.off_c = o;      o = align_up(o + 3 * (size_t)m * sz, 256);
   L.off_pa = o;     o = align_up(o + 2 * (size_t)L.nsA * n * sz, 256);
   L.off_pb = o;     o = align_up(o + 2 * (size_t)L.nsB * m * sz, 256);
+  L.off_centre = o;  // tensor-core path: centre (TC_MAX_D floats) + per-block partial sums (doubles)
+  o += L.use_tc ? 256 + (size_t)TC_CENTRE_BLOCKS * TC_MAX_D * sizeof(double) : 0;
   o = align_up(o, 1024);
   L.off_packs = o;  o += L.use_tc ? tc_pack_bytes(n, L.kc) : 0;
   L.off_packt = o;  o += L.use_tc ? tc_pack_bytes(m, L.kc) : 0;
@@ -386,6 +389,7 @@ extern "C" int b2ot_emp_create(b2ot_emp** handle, int dtype, int64_t n, int64_t 
   h->tc_scales = (float*)((char*)(ws + L.off_xchg) + 64);
   h->packs = ws + L.off_packs;
   h->packt = ws + L.off_packt;
+  h->tc_centre = (float*)(ws + L.off_centre);
   if (h->use_tc) {
     B2OT_CUDA(cudaFuncSetAttribute(emp_tc_lse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)tc_smem_bytes(2)));
@@ -444,39 +448,55 @@ extern "C" int b2ot_emp_init(b2ot_emp* h, const void* f0, const void* g0) {
   B2OT_CUDA(cudaMemsetAsync(h->st, 0, 256, h->stream));
   B2OT_CUDA(cudaMemcpyAsync(h->fring, f0, (size_t)h->n * sz, cudaMemcpyDeviceToDevice, h->stream));
   B2OT_CUDA(cudaMemcpyAsync(h->g, g0, (size_t)h->m * sz, cudaMemcpyDeviceToDevice, h->stream));
-  if (h->dtype == B2OT_F32) {
+  if (h->dtype == B2OT_F32 && !h->use_tc) {
     int rc = launch_sqnorm<float>(h->Xs, h->n, h->d, h->ldxs, h->xx, h->stream);
     if (rc) return rc;
-    rc = launch_sqnorm<float>(h->Xt, h->m, h->d, h->ldxt, h->yy, h->stream);
-    if (rc || !h->use_tc) return rc;
-    // tensor-core sweep: split (hi, lo) + pre-swizzle both clouds once per solve
+    return launch_sqnorm<float>(h->Xt, h->m, h->d, h->ldxt, h->yy, h->stream);
+  }
+  if (h->dtype == B2OT_F32) {
+    // tensor-core sweep: centre both clouds on the mean of the target cloud, then norms, split (hi, lo) and
+    // pre-swizzle of the centred coordinates, once per solve
+    const float* Xs = (const float*)h->Xs;
+    const float* Xt = (const float*)h->Xt;
+    float* centre = h->tc_centre;
+    double* cpart = (double*)((char*)centre + 256);
+    emp_centre_partial_kernel<<<TC_CENTRE_BLOCKS, 256, 0, h->stream>>>(Xt, h->m, h->d, h->ldxt, cpart);
+    B2OT_CHECK_LAUNCH();
+    emp_centre_final_kernel<<<1, TC_MAX_D, 0, h->stream>>>(cpart, TC_CENTRE_BLOCKS, h->m, h->d, centre);
+    B2OT_CHECK_LAUNCH();
+    emp_sqnorm_centred_kernel<<<(unsigned)((h->n + 7) / 8), 256, 0, h->stream>>>(Xs, h->n, h->d, h->ldxs, centre,
+                                                                               (float*)h->xx);
+    B2OT_CHECK_LAUNCH();
+    emp_sqnorm_centred_kernel<<<(unsigned)((h->m + 7) / 8), 256, 0, h->stream>>>(Xt, h->m, h->d, h->ldxt, centre,
+                                                                               (float*)h->yy);
+    B2OT_CHECK_LAUNCH();
     const long long us = (h->n + TC_BM - 1) / TC_BM * TC_BM * h->kc * 8;
     const long long ut = (h->m + TC_BM - 1) / TC_BM * TC_BM * h->kc * 8;
     if (h->tc_kind == 0) {
-      emp_tc_pack_kernel<<<(unsigned)((us + 255) / 256), 256, 0, h->stream>>>((const float*)h->Xs, h->n, h->d, h->ldxs,
-                                                                             h->kc, (float*)h->packs);
+      emp_tc_pack_kernel<<<(unsigned)((us + 255) / 256), 256, 0, h->stream>>>(Xs, h->n, h->d, h->ldxs, h->kc, centre,
+                                                                             (float*)h->packs);
       B2OT_CHECK_LAUNCH();
-      emp_tc_pack_kernel<<<(unsigned)((ut + 255) / 256), 256, 0, h->stream>>>((const float*)h->Xt, h->m, h->d, h->ldxt,
-                                                                             h->kc, (float*)h->packt);
+      emp_tc_pack_kernel<<<(unsigned)((ut + 255) / 256), 256, 0, h->stream>>>(Xt, h->m, h->d, h->ldxt, h->kc, centre,
+                                                                             (float*)h->packt);
       B2OT_CHECK_LAUNCH();
       return 0;
     }
-    // 3xFP16: one power-of-two scale per cloud from its largest |coordinate|, then the scaled split
+    // 3xFP16: one power-of-two scale per cloud from its largest |centred coordinate|, then the scaled split
     unsigned int* maxbits = (unsigned int*)(h->tc_scales + 4);
     B2OT_CUDA(cudaMemsetAsync(maxbits, 0, 2 * sizeof(unsigned int), h->stream));
     const unsigned gs = (unsigned)std::min<long long>((h->n * h->d + 255) / 256, 1184);
     const unsigned gt = (unsigned)std::min<long long>((h->m * h->d + 255) / 256, 1184);
-    emp_absmax_kernel<<<gs, 256, 0, h->stream>>>((const float*)h->Xs, h->n, h->d, h->ldxs, maxbits);
+    emp_absmax_kernel<<<gs, 256, 0, h->stream>>>(Xs, h->n, h->d, h->ldxs, centre, maxbits);
     B2OT_CHECK_LAUNCH();
-    emp_absmax_kernel<<<gt, 256, 0, h->stream>>>((const float*)h->Xt, h->m, h->d, h->ldxt, maxbits + 1);
+    emp_absmax_kernel<<<gt, 256, 0, h->stream>>>(Xt, h->m, h->d, h->ldxt, centre, maxbits + 1);
     B2OT_CHECK_LAUNCH();
     emp_tc_scale_kernel<<<1, 32, 0, h->stream>>>(maxbits, h->tc_scales);
     B2OT_CHECK_LAUNCH();
     emp_tc_pack_f16_kernel<<<(unsigned)((us + 255) / 256), 256, 0, h->stream>>>(
-        (const float*)h->Xs, h->n, h->d, h->ldxs, h->kc, h->tc_scales, (unsigned char*)h->packs);
+        Xs, h->n, h->d, h->ldxs, h->kc, centre, h->tc_scales, (unsigned char*)h->packs);
     B2OT_CHECK_LAUNCH();
     emp_tc_pack_f16_kernel<<<(unsigned)((ut + 255) / 256), 256, 0, h->stream>>>(
-        (const float*)h->Xt, h->m, h->d, h->ldxt, h->kc, h->tc_scales + 1, (unsigned char*)h->packt);
+        Xt, h->m, h->d, h->ldxt, h->kc, centre, h->tc_scales + 1, (unsigned char*)h->packt);
     B2OT_CHECK_LAUNCH();
     return 0;
   }

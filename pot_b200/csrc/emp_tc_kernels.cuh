@@ -59,10 +59,56 @@ __device__ __forceinline__ float to_tf32(float x) {
   return __uint_as_float(r);
 }
 
+// ---- common centre of the two clouds ----
+// C_ij = |x_i - y_j|^2 does not change when both clouds are shifted by the same vector, but its expansion
+// |x|^2 + |y|^2 - 2 x.y cancels log2(|x|^2 / C) bits, and the (hi, lo) operand split carries 22 significant bits, two
+// fewer than fp32: for a cloud 30 standard deviations off the origin the 3xFP16 sweep missed the 1e-4 parity target
+// (1.3e-4, tests/test_empirical_gpu.py::test_tc_wide_dynamic_range[offcentre]).  The tensor-core path therefore works
+// on centred coordinates: c = mean of the TARGET cloud (replicated on every rank of a sharded solve, so all ranks
+// use the same centre), subtracted in fp32 before the norms, the scale search and the split.  Deterministic: per-block
+// partial sums in double, combined in a fixed order.
+constexpr int TC_CENTRE_BLOCKS = 128;
+__global__ void __launch_bounds__(256) emp_centre_partial_kernel(const float* __restrict__ X, long long n, int d,
+                                                                 long long ld, double* __restrict__ partial) {
+  __shared__ double red[4][TC_MAX_D];
+  const int k = threadIdx.x & 63, sub = threadIdx.x >> 6;
+  double s = 0.0;
+  if (k < d)
+    for (long long i = (long long)blockIdx.x * 4 + sub; i < n; i += (long long)gridDim.x * 4) s += (double)X[i * ld + k];
+  red[sub][k] = s;
+  __syncthreads();
+  if (sub == 0) partial[(size_t)blockIdx.x * TC_MAX_D + k] = (red[0][k] + red[1][k]) + (red[2][k] + red[3][k]);
+}
+__global__ void emp_centre_final_kernel(const double* __restrict__ partial, int nblocks, long long n, int d,
+                                        float* __restrict__ centre) {
+  const int k = threadIdx.x;
+  if (k >= TC_MAX_D) return;
+  double s = 0.0;
+  for (int b = 0; b < nblocks; ++b) s += partial[(size_t)b * TC_MAX_D + k];
+  const float c = (k < d && n > 0) ? (float)(s / (double)n) : 0.f;
+  centre[k] = (fabsf(c) < CUDART_INF_F) ? c : 0.f;  // nan / inf coordinates: no shift (the solve reports them itself)
+}
+// squared norms of the centred rows (one warp per row)
+__global__ void __launch_bounds__(256) emp_sqnorm_centred_kernel(const float* __restrict__ X, long long n, int d,
+                                                                 long long ld, const float* __restrict__ centre,
+                                                                 float* __restrict__ out) {
+  const long long i = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (i >= n) return;
+  float s = 0.f;
+  for (int k = lane; k < d; k += 32) {
+    const float x = X[i * ld + k] - centre[k];
+    s = fmaf(x, x, s);
+  }
+  s = warp_sum(s);
+  if (lane == 0) out[i] = s;
+}
+
 // Split + pre-swizzle: packed[tile][chunk c][hi|lo][group g of 8 rows][row r][16-byte unit (j ^ r)][4 floats].
 // One thread per (row, 16-byte unit).
 __global__ void __launch_bounds__(256) emp_tc_pack_kernel(const float* __restrict__ X, long long n, int d, long long ld,
-                                                          int kc, float* __restrict__ packed) {
+                                                          int kc, const float* __restrict__ centre,
+                                                          float* __restrict__ packed) {
   const long long rows_pad = (n + TC_BM - 1) / TC_BM * TC_BM;
   const int units = kc * 8;  // 16-byte units per row
   const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
@@ -74,10 +120,10 @@ __global__ void __launch_bounds__(256) emp_tc_pack_kernel(const float* __restric
   if (row < n) {
     const int k0 = c * TC_KCH + j * 4;
     const float* src = X + row * ld + k0;
-    if (k0 + 0 < d) v.x = src[0];
-    if (k0 + 1 < d) v.y = src[1];
-    if (k0 + 2 < d) v.z = src[2];
-    if (k0 + 3 < d) v.w = src[3];
+    if (k0 + 0 < d) v.x = src[0] - centre[k0 + 0];
+    if (k0 + 1 < d) v.y = src[1] - centre[k0 + 1];
+    if (k0 + 2 < d) v.z = src[2] - centre[k0 + 2];
+    if (k0 + 3 < d) v.w = src[3] - centre[k0 + 3];
   }
   float4 hi, lo;
   hi.x = to_tf32(v.x);  lo.x = to_tf32(v.x - hi.x);
@@ -101,11 +147,12 @@ __global__ void __launch_bounds__(256) emp_tc_pack_kernel(const float* __restric
 // one for the same 8 KB of shared-memory operand traffic -- which is what bounds this kernel (UMMA operand reads +
 // TMA fills share the 128 B/clk of shared-memory bandwidth).
 __global__ void __launch_bounds__(256) emp_absmax_kernel(const float* __restrict__ X, long long n, int d, long long ld,
+                                                         const float* __restrict__ centre,
                                                          unsigned int* __restrict__ out_bits) {
   float mx = 0.f;
   const long long total = n * d;
   for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
-    const float v = fabsf(X[(i / d) * ld + (i % d)]);
+    const float v = fabsf(X[(i / d) * ld + (i % d)] - centre[i % d]);
     if (v < CUDART_INF_F) mx = fmaxf(mx, v);  // nan / inf coordinates poison the result anyway
   }
   mx = warp_max(mx);
@@ -127,7 +174,8 @@ __global__ void emp_tc_scale_kernel(const unsigned int* __restrict__ maxbits, fl
 }
 // packed[tile][chunk c of 64 coordinates][hi|lo][group g of 8 rows][row r][16-byte unit (j ^ r)][8 halves]
 __global__ void __launch_bounds__(256) emp_tc_pack_f16_kernel(const float* __restrict__ X, long long n, int d, long long ld,
-                                                              int kc, const float* __restrict__ scale,
+                                                              int kc, const float* __restrict__ centre,
+                                                              const float* __restrict__ scale,
                                                               unsigned char* __restrict__ packed) {
   const long long rows_pad = (n + TC_BM - 1) / TC_BM * TC_BM;
   const int units = kc * 8;
@@ -141,7 +189,7 @@ __global__ void __launch_bounds__(256) emp_tc_pack_f16_kernel(const float* __res
 #pragma unroll
   for (int e = 0; e < 8; ++e) {
     const int k = c * 64 + j * 8 + e;
-    const float v = (row < n && k < d) ? X[row * ld + k] * sc : 0.f;
+    const float v = (row < n && k < d) ? (X[row * ld + k] - centre[k]) * sc : 0.f;
     hi[e] = __float2half_rn(v);
     lo[e] = __float2half_rn(v - __half2float(hi[e]));
   }

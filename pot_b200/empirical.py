@@ -20,7 +20,7 @@ import warnings
 
 import torch
 
-from . import _dense, _lib
+from . import _autograd, _dense, _lib
 from .bregman import _NOCONV, sinkhorn, sinkhorn2
 from .utils import LazyTensor
 
@@ -54,15 +54,32 @@ def _points(X, name):
     return X if X.stride(1) == 1 and X.stride(0) >= X.shape[1] else X.contiguous()
 
 
-def dist(x1, x2=None, metric="sqeuclidean"):
-    """Pairwise cost matrix; drop-in for ot.dist with metric "sqeuclidean" (default) or "euclidean".
+def dist(x1, x2=None, metric="sqeuclidean", p=2, w=None, backend="auto", nx=None, use_tensor=False):
+    """Pairwise cost matrix; drop-in for ot.dist (ot/utils.py:400-526, same signature) with metric "sqeuclidean"
+    (default) or "euclidean".
 
-    C = |x|^2 + |y|^2 - 2 x.y^T clamped at 0 (ot/utils.py:292-299); with x2 None the diagonal is zeroed like the
-    reference does when X is Y (:304-305).
+    C = |x|^2 + |y|^2 - 2 x.y^T clamped at 0 (ot/utils.py:292-299); with x2 None (or x2 is x1) the diagonal is zeroed
+    like the reference does when X is Y (:304-305).  `p`, `w` and `use_tensor` do not enter these two metrics in the
+    reference either (:465-468); `nx` is accepted and ignored (there is one backend here); `backend="scipy"` (the
+    host cdist path, :457-464) and every other metric raise NotImplementedError: they are outside the hot path.
     """
+    if backend == "scipy":
+        raise NotImplementedError("pot_b200: backend='scipy' (host cdist) is outside the accelerated hot path")
+    same = x2 is None or x2 is x1
+    if _autograd.any_requires_grad(x1, x2):
+        _metric_code(metric)
+        _points(x1, "x1")  # type / device checks before entering autograd
+        if not same:
+            _points(x2, "x2")
+        return _autograd.DistFunction.apply(x1, x1 if same else x2, metric, same, _dist_kernel)
+    return _dist_kernel(x1, None if same else x2, metric)
+
+
+def _dist_kernel(x1, x2, metric):
+    """One launch of the dist kernel on detached inputs; x2 None = the X-is-Y case (diagonal zeroed)."""
     lib = _lib.load()
     X = _points(x1, "x1")
-    same = x2 is None or x2 is x1
+    same = x2 is None
     Y = X if same else _points(x2, "x2")
     if Y.dtype != X.dtype or Y.device != X.device or Y.shape[1] != X.shape[1]:
         raise ValueError("pot_b200: x1 and x2 must share dtype, device and dimension")
@@ -276,7 +293,11 @@ def _lazy_solve(X_s, X_t, reg, a, b, metric, numIterMax, stopThr, batchSize, ver
 
 
 def _prep(X_s, X_t, a, b):
-    X_s, X_t = _points(X_s, "X_s"), _points(X_t, "X_t")
+    # identity is decided BEFORE detaching: the reference's `dist` zeroes the diagonal iff `X is Y` (ot/utils.py:304),
+    # and list_to_array keeps the caller's objects, so empirical_sinkhorn(X, X, isLazy=False) takes that branch
+    same = X_t is X_s
+    X_s = _points(X_s, "X_s")
+    X_t = X_s if same else _points(X_t, "X_t")
     if X_t.dtype != X_s.dtype or X_t.device != X_s.device or X_t.shape[1] != X_s.shape[1]:
         raise ValueError("pot_b200: X_s and X_t must share dtype, device and dimension")
     a = _unif(X_s.shape[0], X_s) if a is None else a.detach().to(X_s.dtype).contiguous()
@@ -291,6 +312,7 @@ def empirical_sinkhorn(X_s, X_t, reg, a=None, b=None, metric="sqeuclidean", numI
     isLazy=True : returns the log-scalings (f, g) [+ dict_log {"err", "u": f, "v": g, "niter", "lazy_plan"}];
     isLazy=False: M = dist(X_s, X_t), then sinkhorn(a, b, M, reg, ...) -> plan [+ log].
     """
+    _autograd.warn_detached("empirical_sinkhorn", X_s, X_t, a, b)
     X_s, X_t, a, b = _prep(X_s, X_t, a, b)
     if isLazy:
         f, g, errs, niter = _lazy_solve(X_s, X_t, reg, a, b, metric, int(numIterMax), float(stopThr), batchSize,
@@ -312,7 +334,13 @@ def empirical_sinkhorn2(X_s, X_t, reg, a=None, b=None, metric="sqeuclidean", num
     """Drop-in for ot.bregman.empirical_sinkhorn2 (ot/bregman/_empirical.py:305-517): the loss <C, plan>.
 
     Lazy mode reduces sum_ij C_ij exp(f_i + g_j - C_ij/reg) in one sweep from the point clouds (:466-483).
+
+    When X_s, X_t, a or b require grad the loss carries the envelope gradient (pot_b200/_autograd.py): the lazy path
+    rebuilds the plan block by block in backward; the dense path goes through the differentiable `dist` and
+    `sinkhorn2`.
     """
+    X_s0, X_t0, a0, b0 = X_s, X_t, a, b
+    wants_grad = _autograd.any_requires_grad(X_s0, X_t0, a0, b0)
     X_s, X_t, a, b = _prep(X_s, X_t, a, b)
     if isLazy:
         lib = _lib.load()
@@ -329,12 +357,22 @@ def empirical_sinkhorn2(X_s, X_t, reg, a=None, b=None, metric="sqeuclidean", num
                                          out.data_ptr(), scratch.data_ptr(), _dense.stream_ptr(X_s.device)),
                        "b2ot_emp_loss")
         loss = out.to(X_s.dtype)
+        if wants_grad:
+            warnings.warn(_autograd.ENVELOPE_NOTE)
+            block = batchSize[0] if isinstance(batchSize, tuple) else batchSize
+            loss = _autograd.LazyLossFunction.apply(
+                loss, X_s0, X_t0, a0 if isinstance(a0, torch.Tensor) else a, b0 if isinstance(b0, torch.Tensor) else b,
+                f, g, float(reg), metric, _plan_block, max(int(block), 1024))
         if log:
             dict_log = {"err": [torch.tensor(e, dtype=X_s.dtype, device=X_s.device) for e in errs], "u": f, "v": g,
                         "niter": niter, "lazy_plan": get_sinkhorn_lazytensor(X_s, X_t, f, g, metric, reg)}
             return loss, dict_log
         return loss
-    M = dist(X_s, X_t, metric=metric)
+    if wants_grad:
+        M = dist(X_s0, X_t0, metric=metric)  # differentiable wrt the clouds; keeps the X-is-Y identity
+        a, b = (a0 if isinstance(a0, torch.Tensor) else a), (b0 if isinstance(b0, torch.Tensor) else b)
+    else:
+        M = dist(X_s, X_t, metric=metric)
     return sinkhorn2(a, b, M, reg, numItermax=numIterMax, stopThr=stopThr, verbose=verbose, log=log, warn=warn,
                      warmstart=warmstart, **kwargs)
 

@@ -26,34 +26,15 @@ import warnings
 
 import torch
 
-from . import _dense, _lib
+from . import _autograd, _dense, _lib
 from .bregman import _NOCONV, _print_table, _require_cuda_matrix, _rowmajor, _solve_dense, _weights
 from .utils import OTResult
 
 __all__ = ["solve", "solve_sample"]
 
 
-class _ValFunction(torch.autograd.Function):
-    """value with prescribed gradients (the role of nx.set_gradients, ot/backend.py:2140-2145)."""
-
-    @staticmethod
-    def forward(ctx, val, grads, *inputs):
-        ctx.grads = grads
-        ctx.needs = [isinstance(t, torch.Tensor) and t.requires_grad for t in inputs]
-        return val.clone()
-
-    @staticmethod
-    def backward(ctx, grad_output):
-        out = tuple((g * grad_output) if need else None for g, need in zip(ctx.grads, ctx.needs))
-        return (None, None) + out
-
-
-def _set_gradients(val, inputs, grads):
-    return _ValFunction.apply(val, grads, *inputs)
-
-
-def _any_requires_grad(*ts):
-    return any(isinstance(t, torch.Tensor) and t.requires_grad for t in ts)
+_set_gradients = _autograd.set_gradients
+_any_requires_grad = _autograd.any_requires_grad
 
 
 def solve(M, a=None, b=None, reg=None, c=None, reg_type="KL", unbalanced=None, unbalanced_type="KL", method=None,
@@ -183,12 +164,9 @@ def solve_sample(X_a, X_b, a=None, b=None, metric="sqeuclidean", reg=None, c=Non
             f"pot_b200: method={method!r} (1d / gaussian / factored / lowrank / geomloss / nystroem) is outside the "
             "accelerated Sinkhorn path")
     if not lazy:
-        Xa = X_a.detach() if isinstance(X_a, torch.Tensor) else X_a
-        Xb = X_b.detach() if isinstance(X_b, torch.Tensor) else X_b
-        if _any_requires_grad(X_a, X_b):
-            warnings.warn("pot_b200: solve_sample does not differentiate through the point clouds (forward-only "
-                          "kernels); the cost matrix is detached")
-        M = dist(Xa, Xb, metric)
+        # `dist` is differentiable wrt the clouds (pot_b200/_autograd.py::DistFunction), so the gradient `solve`
+        # attaches to `value` wrt M reaches X_a / X_b, as in the reference (:1727-1755)
+        M = dist(X_a, X_b, metric)
         return solve(M, a, b, reg, c, reg_type, unbalanced, unbalanced_type, method, n_threads, max_iter, plan_init,
                      potentials_init, tol, verbose, grad)
     if reg is None or reg == 0:

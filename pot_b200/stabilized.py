@@ -24,7 +24,7 @@ import warnings
 
 import torch
 
-from . import _dense, _lib
+from . import _autograd, _dense, _lib
 from .bregman import _NOCONV, POLL_EVERY, _require_cuda_matrix, _rowmajor, _weights
 
 __all__ = ["sinkhorn_stabilized", "sinkhorn_epsilon_scaling"]
@@ -64,10 +64,12 @@ def sinkhorn_stabilized(a, b, M, reg, numItermax=1000, tau=1e3, stopThr=1e-9, wa
 
     Returns the plan; with ``log=True`` also {"err", "n_iter", "logu", "logv", "alpha", "beta", "warmstart"} (:1332-1340).
     """
+    if not kwargs.get("b2ot_loss", False):
+        _autograd.warn_detached("sinkhorn_stabilized", M, a, b)
     M = _require_cuda_matrix(M)
     Mc = _rowmajor(M.detach())
-    a = _weights(a, Mc.shape[0], Mc, "a")
-    b = _weights(b, Mc.shape[1], Mc, "b")
+    a = _weights(a, Mc.shape[0], Mc, "a").detach()
+    b = _weights(b, Mc.shape[1], Mc, "b").detach()
     if b.dim() > 1:
         raise NotImplementedError("pot_b200: sinkhorn_stabilized with several target histograms (2-D b) is outside "
                                   "the accelerated hot path")

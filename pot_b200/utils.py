@@ -13,33 +13,29 @@ import torch
 __all__ = ["OTResult", "LazyTensor"]
 
 
-class LazyTensor(object):
-    """A tensor that is not stored: `getitem(i, j, **kwargs)` computes the requested block on demand."""
+class LazyTensor:
+    """A tensor that is never stored: indexing evaluates `getitem(*index, **kwargs)` for the requested block.
+
+    Behaviour follows ot.utils.LazyTensor (ot/utils.py:1425-1492): `shape` / `ndim`, every keyword argument is also
+    an attribute, an index shorter than `ndim` is completed with full slices, anything but int / slice / tuple
+    indices raises NotImplementedError, and the repr lists the attribute names.
+    """
 
     def __init__(self, shape, getitem, **kwargs):
-        self._getitem = getitem
-        self.shape = shape
-        self.ndim = len(shape)
-        self.kwargs = kwargs
-        for key, value in kwargs.items():
-            setattr(self, key, value)
+        self.shape, self.ndim = shape, len(shape)
+        self._getitem, self.kwargs = getitem, kwargs
+        self.__dict__.update(kwargs)
 
     def __getitem__(self, key):
-        k = []
-        if isinstance(key, int) or isinstance(key, slice):
-            k.append(key)
-            for _ in range(self.ndim - 1):
-                k.append(slice(None))
-        elif isinstance(key, tuple):
-            k = list(key)
-            for _ in range(self.ndim - len(key)):
-                k.append(slice(None))
-        else:
+        if isinstance(key, (int, slice)):
+            key = (key,)
+        elif not isinstance(key, tuple):
             raise NotImplementedError("Only integer, slice, and tuple indexing is supported")
-        return self._getitem(*k, **self.kwargs)
+        index = key + (slice(None),) * (self.ndim - len(key))
+        return self._getitem(*index, **self.kwargs)
 
     def __repr__(self):
-        return "LazyTensor(shape={},attributes=({}))".format(self.shape, ",".join(self.kwargs.keys()))
+        return f"LazyTensor(shape={self.shape},attributes=({','.join(self.kwargs)}))"
 
 
 class OTResult:

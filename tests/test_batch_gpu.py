@@ -162,8 +162,9 @@ def test_log_exact_column_pass(dtype, shape):
     B, n, m = shape
     M, a, b = _problem(B, n, m, dtype, seed=9)
     ref = orc.solve_batch(M, 0.05, a, b, max_iter=15, tol=0, solver="log_sinkhorn")
-    r = ot.solve_batch(dev(M), 0.05, dev(a), dev(b), max_iter=15, tol=0, solver="log_sinkhorn",
-                       b2ot_flags=_lib.BATCH_FORCE_EXACT)
+    from pot_b200 import batch as pbatch
+    with pbatch._solver_flags(_lib.BATCH_FORCE_EXACT):
+        r = ot.solve_batch(dev(M), 0.05, dev(a), dev(b), max_iter=15, tol=0, solver="log_sinkhorn")
     close(r.plan, ref["plan"], tol_of(dtype), "plan (exact column pass)")
 
 

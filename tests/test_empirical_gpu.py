@@ -197,22 +197,24 @@ def test_lazy_equals_dense_log_solver():
 # ------------------------------------------------------------------------------------------------
 # tensor-core sweep (tcgen05, 3xTF32): fp32, sqeuclidean, d <= 64
 # ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("operand", ["f16", "tf32"])
 @pytest.mark.parametrize("case", [c for c in EMP if "_f32_" in c])
-def test_tc_golden(golden, case):
+def test_tc_golden(golden, case, operand):
     xs, xt, a, b = (golden(case, k) for k in ("xs", "xt", "a", "b"))
     reg, its = float(golden(case, "reg")), int(golden(case, "its"))
     with warnings.catch_warnings():
         warnings.simplefilter("ignore")
         f, g, lg = ot.empirical_sinkhorn(dev(xs), dev(xt), reg, dev(a), dev(b), numIterMax=its, stopThr=-1, isLazy=True,
-                                         log=True, b2ot_variant="tc")
+                                         log=True, b2ot_variant="tc", b2ot_operand=operand)
     logclose(f, golden(case, "f"), 1e-4, "f (tc)")
     logclose(g, golden(case, "g"), 1e-4, "g (tc)")
     assert lg["niter"] == its - 1
     errs_close(lg["err"], golden(case, "err"), "f32")
 
 
+@pytest.mark.parametrize("operand", ["f16", "tf32"])
 @pytest.mark.parametrize("shape", [(1, 9, 2), (130, 127, 3), (200, 333, 16), (513, 190, 64), (257, 1030, 33), (1500, 900, 64)])
-def test_tc_vs_oracle(shape):
+def test_tc_vs_oracle(shape, operand):
     """The tcgen05 sweep against the fp64 oracle: ragged tiles, 1 and 2 K-chunks, reduction splits, weights,
     warm start.  Also the auto variant and the register-tiled sweep must agree with it."""
     n, m, d = shape
@@ -232,13 +234,59 @@ def test_tc_vs_oracle(shape):
         for variant in ("tc", "simt", "auto"):
             f, g, lg = ot.empirical_sinkhorn(dev(xs), dev(xt), 0.5, dev(a), dev(b), numIterMax=20, stopThr=-1,
                                              isLazy=True, log=True, warmstart=(dev(ws[0]), dev(ws[1])),
-                                             b2ot_variant=variant)
+                                             b2ot_variant=variant, b2ot_operand=operand)
             logclose(f, fr, 1e-4, f"f ({variant})")
             logclose(g, gr, 1e-4, f"g ({variant})")
             assert lg["niter"] == 19 and len(lg["err"]) == 2
             out[variant] = (f, g)
     # the two sweeps differ only by round-off (3xTF32 keeps the dot product at fp32 level)
     assert float(torch.abs(out["tc"][0] - out["simt"][0]).max()) < 2e-5 * max(1.0, float(np.abs(fr).max()))
+
+
+@pytest.mark.parametrize("operand", ["f16", "tf32"])
+@pytest.mark.parametrize("kind", ["outliers", "tiny_coords", "offcentre"])
+def test_tc_wide_dynamic_range(kind, operand):
+    """Clouds the operand split could be sensitive to (the 3xFP16 split has one power-of-two scale per cloud, so its
+    low halves lose bits for coordinates far below the cloud maximum; 3xTF32 has an 8-bit exponent):
+      outliers    : a few points at 2^10 x the typical norm;
+      tiny_coords : some coordinates at 2^-12 x the typical size;
+      offcentre   : the whole cloud shifted by 30 standard deviations (|x|^2 + |y|^2 - 2 x.y cancels 3 digits).
+    Checked against the fp64 oracle on the same fp32 inputs at the fp32 tolerance, and against the fp32 SIMT sweep."""
+    n, m, d = 700, 520, 48
+    rng = np.random.RandomState(97)
+    xs = (rng.randn(n, d) / np.sqrt(d)).astype(np.float32)
+    xt = (rng.randn(m, d) / np.sqrt(d) + 0.2).astype(np.float32)
+    if kind == "outliers":
+        xs[::97] *= 1024.0
+        xt[5::131] *= 1024.0
+    elif kind == "tiny_coords":
+        xs[:, ::5] *= 2.0 ** -12
+        xt[:, 1::7] *= 2.0 ** -12
+        xs[3::11] *= 2.0 ** -12
+    else:
+        xs += 30.0 / np.sqrt(d)
+        xt += 30.0 / np.sqrt(d)
+    reg = 0.5
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        fr, gr = orc.empirical_sinkhorn_lazy(xs.astype(np.float64), xt.astype(np.float64), reg, numIterMax=20,
+                                             stopThr=-1, batchSize=256)
+        f, g = ot.empirical_sinkhorn(dev(xs), dev(xt), reg, numIterMax=20, stopThr=-1, isLazy=True,
+                                     b2ot_variant="tc", b2ot_operand=operand)
+        fs, gs = ot.empirical_sinkhorn(dev(xs), dev(xt), reg, numIterMax=20, stopThr=-1, isLazy=True,
+                                       b2ot_variant="simt")
+    assert torch.isfinite(f).all() and torch.isfinite(g).all()
+    logclose(f, fr, 1e-4, f"f ({kind}, {operand})")
+    logclose(g, gr, 1e-4, f"g ({kind}, {operand})")
+    # the typical points must be right too, not only the outlier-dominated maximum: compare where |ref| is moderate
+    fn, gn = f.cpu().numpy().astype(np.float64), g.cpu().numpy().astype(np.float64)
+    for x, r, nm in ((fn, fr, "f"), (gn, gr, "g")):
+        typ = np.abs(r) <= 10 * np.median(np.abs(r)) + 1.0
+        scale = max(1.0, np.abs(r[typ]).max())
+        # fp32 inputs: the cost itself carries eps * (|x|^2 + |y|^2) / reg of rounding; allow the SIMT sweep's own error
+        simt = (fs if nm == "f" else gs).cpu().numpy().astype(np.float64)
+        allow = max(1e-4 * scale, 4.0 * np.abs(simt[typ] - r[typ]).max())
+        assert np.abs(x[typ] - r[typ]).max() <= allow, (nm, kind, operand, np.abs(x[typ] - r[typ]).max(), allow)
 
 
 def test_tc_rejects_ineligible():

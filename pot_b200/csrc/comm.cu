@@ -89,7 +89,8 @@ static int allreduce_t(b2ot_comm* c, void* buf, long long count, int op, int* er
   B2OT_REQUIRE((size_t)count * sizeof(T) <= c->view.slot_bytes, "peer all-reduce: %lld elements exceed the slot (%llu B)",
                count, c->view.slot_bytes);
   const unsigned long long seq = ++c->seq;
-  const unsigned grid = (unsigned)std::max<long long>(1, std::min<long long>((count + 255) / 256, 296));
+  const long long vn = 16 / (long long)sizeof(T);
+  const unsigned grid = (unsigned)std::max<long long>(1, std::min<long long>((count / vn + 1 + 255) / 256, 148));
   comm_put_kernel<T><<<grid, 256, 0, s>>>(c->view, (const T*)buf, 0, 1, count, nullptr, nullptr, 0, seq);
   B2OT_CHECK_LAUNCH();
   comm_take_kernel<T><<<grid, 256, 0, s>>>(c->view, (T*)buf, count, op, nullptr, 0, err_status, seq);

@@ -14,7 +14,9 @@
 //          until all ranks have published s (ld.acquire.sys), then sums the nranks slots in rank order -- the
 //          same order on every rank, so all ranks see bit-identical totals and take identical stop decisions.
 // Two parities suffice: a rank can only start the put of s + 2 after it consumed s + 1, which needs every
-// peer's put of s + 1, which those peers issue after they consumed s.
+// peer's put of s + 1, which those peers issue after they consumed s.  The argument needs EVERY sequence number to be
+// put and waited for by every rank: a solver that has stopped still publishes the flag (without data) and its
+// consumer still waits for the peers' flags (comm_put_kernel / finalize_kernel), so the chain has no gaps.
 // The per-iteration traffic is one m-vector per peer (256 KiB at m = 65536): latency-bound, no NCCL launch,
 // no separate reduce kernel on the hot path.
 #pragma once
@@ -74,27 +76,48 @@ __device__ __forceinline__ bool comm_wait(const CommView& c, unsigned long long 
 }
 
 // put: dst_q[j] = sum over nsrc local rows of src[row * ld + j] for j < count; optional extra element at index
-// `count` carrying (*flag_src != 0).  No-op unless *status == expect_status (status may be null).
+// `count` carrying (*flag_src != 0).  The DATA is written only while *status == expect_status (status may be null);
+// the FLAG of `seq` is published in every case: the two-parity reuse argument in the header needs every sequence
+// number to be exchanged by every rank, also after the solve has stopped (all ranks stop at the same iteration, but
+// the host keeps enqueueing no-op iterations until its next poll; a gap in the sequence would let the first put
+// after the gap land in a slot a slower peer is still reading).
+// 16-byte path: one thread sums a 16-byte column vector over the local rows and stores it to every peer with one
+// 16-byte NVLink store per peer (the scalar version issued 4-byte peer stores).
 template <typename T>
 __global__ void __launch_bounds__(256) comm_put_kernel(const CommView c, const T* __restrict__ src, long long ld, int nsrc,
                                                        long long count, const int* flag_src, const int* status,
                                                        int expect_status, unsigned long long seq) {
+  using V = typename Vec<T>::type;
+  constexpr int VN = Vec<T>::N;
   griddep_wait();
   griddep_launch_dependents();
   __shared__ int s_last;
-  if (status != nullptr && *status != expect_status) return;
+  const bool live = (status == nullptr || *status == expect_status);
   const int par = (int)(seq & 1ull);
-  const long long total = count + (flag_src != nullptr ? 1 : 0);
-  for (long long j = (long long)blockIdx.x * 256 + threadIdx.x; j < total; j += (long long)gridDim.x * 256) {
-    T s = (T)0;
-    if (j < count) {
-      for (int q = 0; q < nsrc; ++q) s += src[(long long)q * ld + j];
-    } else {
-      s = (T)(atomicOr(const_cast<int*>(flag_src), 0) ? 1 : 0);
+  if (live) {
+    const bool vec_ok = (nsrc == 1 || ld % VN == 0) && (reinterpret_cast<uintptr_t>(src) % 16 == 0);
+    const long long nvec = vec_ok ? count / VN : 0;
+    for (long long jv = (long long)blockIdx.x * 256 + threadIdx.x; jv < nvec; jv += (long long)gridDim.x * 256) {
+      V acc = __ldcg(reinterpret_cast<const V*>(src) + jv);
+      for (int q = 1; q < nsrc; ++q) {
+        const V x = __ldcg(reinterpret_cast<const V*>(src + (long long)q * ld) + jv);
+#pragma unroll
+        for (int e = 0; e < VN; ++e) elem(acc, e) += elem(x, e);
+      }
+      for (int q = 0; q < c.nranks; ++q) reinterpret_cast<V*>(comm_slot<T>(c, q, par, c.rank))[jv] = acc;
     }
-    for (int q = 0; q < c.nranks; ++q) comm_slot<T>(c, q, par, c.rank)[j] = s;
+    const long long total = count + (flag_src != nullptr ? 1 : 0);
+    for (long long j = nvec * VN + (long long)blockIdx.x * 256 + threadIdx.x; j < total; j += (long long)gridDim.x * 256) {
+      T s = (T)0;
+      if (j < count) {
+        for (int q = 0; q < nsrc; ++q) s += __ldcg(&src[(long long)q * ld + j]);
+      } else {
+        s = (T)(atomicOr(const_cast<int*>(flag_src), 0) ? 1 : 0);
+      }
+      for (int q = 0; q < c.nranks; ++q) comm_slot<T>(c, q, par, c.rank)[j] = s;
+    }
+    __threadfence_system();
   }
-  __threadfence_system();
   __syncthreads();
   if (threadIdx.x == 0) {
     const unsigned int t = atomicAdd(c.ticket, 1u);

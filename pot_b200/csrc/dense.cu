@@ -766,7 +766,9 @@ static int launch_finalize(const b2ot_dense* h, int nsrc, int init, int gate_reb
     // kernel below is the "take" (waits on the flags, sums the slots in rank order)
     b2ot_comm* c = h->comm;
     const unsigned long long seq = ++c->seq;
-    const unsigned g = (unsigned)std::min<long long>((h->m + 1 + 255) / 256, 296);
+    // one 16-byte column vector per thread (comm_put_kernel): 64 blocks at m = 65536 fp32
+    const long long vn = 16 / (long long)sizeof(T);
+    const unsigned g = (unsigned)std::max<long long>(1, std::min<long long>((h->m / vn + 1 + 255) / 256, 148));
     B2OT_CUDA(launch_pdl(comm_put_kernel<T>, dim3(g), dim3(256), 0, h->stream, c->view, (const T*)h->partials,
                          (long long)h->mp, nsrc, (long long)h->m, (const int*)&h->st->uflag,
                          (const int*)&h->st->status, (int)ST_RUNNING, seq));

@@ -703,13 +703,16 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
   SolveState* st = p.st;
   griddep_wait();               // column partials of the sweep (or the peer put) are complete and visible
   griddep_launch_dependents();  // let the next sweep start its prologue (barriers, first K tiles) under this kernel
-  if (st->status != ST_RUNNING) return;
-  if (STAB && p.gate_rebuild && st->rebuild == 0) return;
+  const int status_in = st->status;
   const int tid = threadIdx.x;
-  if (p.use_comm && !comm_wait(p.comm, p.seq)) {  // fused "take" of the NVLink exchange
+  // fused "take" of the NVLink exchange.  The wait is NOT gated on the solver status: every sequence number is
+  // waited for (comm.cuh), also by the no-op iterations enqueued after the solve stopped -- except after a timeout.
+  if (p.use_comm && status_in != ST_COMM_TIMEOUT && !comm_wait(p.comm, p.seq)) {
     if (tid == 0) st->status = ST_COMM_TIMEOUT;
     return;
   }
+  if (status_in != ST_RUNNING) return;
+  if (STAB && p.gate_rebuild && st->rebuild == 0) return;
   const int sel_v = st->sel_v;
   const int nxt = (sel_v + 1) % 3;
   const T* vcur = reinterpret_cast<const T*>(p.vring) + (long long)sel_v * p.mp;

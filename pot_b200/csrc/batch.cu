@@ -5,6 +5,7 @@
 
 #include "../../include/b2ot.h"
 #include "batch_kernels.cuh"
+#include "batch_hyb_kernels.cuh"
 #include "host_util.h"
 
 using namespace b2ot;
@@ -103,7 +104,36 @@ static int launch_cpl(const BatchParams& p, const BatchCfg& c, cudaStream_t s) {
   return -1;
 }
 
+// One whole 256-column fp32 problem per CTA, half in registers, half in shared memory (batch_hyb_kernels.cuh).
+// B2OT_BATCH_HYB=0 (diagnosis build) falls back to the cluster kernel.
+static bool hyb_enabled() {
+  static const bool on = [] {
+    const char* e = diag_env("B2OT_BATCH_HYB");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+template <int MODE, int NS>
+static int launch_hyb_one(const BatchParams& p, cudaStream_t stream) {
+  auto kern = batch_hyb_kernel<MODE, NS>;
+  const size_t smem = hyb_smem_bytes(128 + 64 * NS);
+  static thread_local bool configured = false;
+  if (!configured) {
+    B2OT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  kern<<<(unsigned)p.B, HYB_NT, smem, stream>>>(p);
+  B2OT_CHECK_LAUNCH();
+  return 0;
+}
+static int launch_hyb(int mode, const BatchParams& p, cudaStream_t s) {
+  if (p.n == 256)
+    return mode == B2OT_MODE_KNOPP ? launch_hyb_one<MODE_KNOPP, 2>(p, s) : launch_hyb_one<MODE_LOG, 2>(p, s);
+  return mode == B2OT_MODE_KNOPP ? launch_hyb_one<MODE_KNOPP, 1>(p, s) : launch_hyb_one<MODE_LOG, 1>(p, s);
+}
+
 static int launch(int mode, int dtype, const BatchParams& p, const BatchCfg& c, cudaStream_t s) {
+  if (hyb_enabled() && hyb_eligible(dtype == B2OT_F32, p.n, p.m) && p.B < (1ll << 31)) return launch_hyb(mode, p, s);
   if (dtype == B2OT_F32)
     return mode == B2OT_MODE_KNOPP ? launch_cpl<float, MODE_KNOPP>(p, c, s) : launch_cpl<float, MODE_LOG>(p, c, s);
   return mode == B2OT_MODE_KNOPP ? launch_cpl<double, MODE_KNOPP>(p, c, s) : launch_cpl<double, MODE_LOG>(p, c, s);

@@ -263,3 +263,58 @@ def test_fast_path_converged_and_kl(dtype, solver):
         tol = 1e-3 if r.log["n_iter"] != ref["n_iter"] else tol_of(dtype)
     close(r.plan, ref["plan"], tol, "plan")
     close(r.value, ref["value"], 10 * tol, "value")
+
+
+# ------------------------------------------------------------------------------------------------
+# one-problem-per-CTA kernel (batch_hyb_kernels.cuh): fp32, m = 256, n = 192 / 256 (BASELINE config 5's shape)
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n", [192, 256])
+def test_hybrid_exact_column_pass_and_underflow(n):
+    """The two-pass exact column log-sum-exp of the hybrid kernel: forced (test hook) it must reproduce the fast
+    row-frame update; with a far-away target point the row-frame column totals underflow and it runs for real."""
+    B, m = 3, 256
+    M, a, b = _problem(B, n, m, np.float32, seed=21)
+    ref = orc.solve_batch(M, 0.05, a, b, max_iter=15, tol=0, solver="log_sinkhorn")
+    with otb._solver_flags(_lib.BATCH_FORCE_EXACT):
+        r = ot.solve_batch(dev(M), 0.05, dev(a), dev(b), max_iter=15, tol=0, solver="log_sinkhorn")
+    close(r.plan, ref["plan"], 1e-4, "plan (exact column pass, hybrid)")
+    rng = np.random.RandomState(5)
+    X, Y = rng.randn(B, n, 2), rng.randn(B, m, 2)
+    Y[:, 0, :] += 40.0
+    M = orc.dist_sqeuclidean_batch(X, Y).astype(np.float32)
+    ref64 = orc.solve_batch(M.astype(np.float64), 1.0, a.astype(np.float64), b.astype(np.float64), max_iter=20, tol=0,
+                            solver="log_sinkhorn")
+    r = ot.solve_batch(dev(M), 1.0, dev(a), dev(b), max_iter=20, tol=0, solver="log_sinkhorn")
+    assert torch.isfinite(r.plan).all() and torch.isfinite(r.potentials[1]).all()
+    logclose(r.potentials[1], ref64["potentials"][1], 1e-4, "v (underflow fallback, hybrid)")
+    close(r.plan, ref64["plan"], 5e-3, "plan (underflow fallback, hybrid)")
+
+
+@pytest.mark.parametrize("solver", ["log_sinkhorn", "sinkhorn"])
+def test_hybrid_stale_reference_survives_a_jump(solver):
+    """The log-domain hot loop uses last iteration's row log-sum-exp as the exponent reference.  A warm start far from
+    the fixed point (v jumps by hundreds between the first iterations) must take the exact-maximum redo, not overflow:
+    bregman_*_projection_batch on a badly scaled kernel, against the oracle; also an unaligned problem pointer (the
+    cooperative load path) and the log-plan output."""
+    B, n, m = 2, 256, 256
+    M, a, b = _problem(B, n, m, np.float32, seed=31)
+    M = (M * 400.0).astype(np.float32)  # K = -M / reg spans 0 .. -4000: e^-4000 underflows every row frame at first
+    if solver == "log_sinkhorn":
+        K = (-M / 0.1).astype(np.float32)
+        ref = orc.bregman_log_projection_batch(K.astype(np.float64), a.astype(np.float64), b.astype(np.float64),
+                                               max_iter=12, tol=0)
+        buf = torch.zeros(B * n * m + 1, dtype=torch.float32, device=DEV)
+        Kd = buf[1:].view(B, n, m)  # 4-byte aligned only
+        Kd.copy_(dev(K))
+        out = otb.bregman_log_projection_batch(Kd, dev(a), dev(b), max_iter=12, tol=0)
+        assert torch.isfinite(out["potentials"][0]).all()
+        logclose(out["potentials"][0], ref["potentials"][0], 1e-4, "u")
+        logclose(out["potentials"][1], ref["potentials"][1], 1e-4, "v")
+        logclose(out["log_T"], ref["log_T"], 1e-4, "log T")
+    else:
+        K = np.exp(-(M / 400.0) / 0.1).astype(np.float32)
+        ref = orc.bregman_projection_batch(K.astype(np.float64), a.astype(np.float64), b.astype(np.float64),
+                                           max_iter=12, tol=0)
+        out = otb.bregman_projection_batch(dev(K), dev(a), dev(b), max_iter=12, tol=0)
+        close(out["T"], ref["T"], 1e-4, "T")
+        close(out["potentials"][0], ref["potentials"][0], 1e-4, "f")

@@ -34,7 +34,30 @@ constexpr int TC_KCH = 32;        // K elements per swizzle chunk (32 x 4 B = 12
 constexpr int TC_SUB = 16384;     // bytes of one (chunk, hi|lo) sub-tile: 128 rows x 128 B
 constexpr int TC_NB = 4;          // shared-memory stages of the column operand, one K chunk (hi + lo) each
 constexpr int TC_STAGE = 2 * TC_SUB;  // bytes of a stage
+// Build-time variants of the sweep (A/B'd as separate builds of the library, scripts/build_variants.sh):
+//   B2OT_TC_EPI_SINGLE  1: one pass per 32-column chunk against a lagging per-row reference exponent (default)
+//                       0: two phases per chunk (exact chunk maximum first, then the exponentials)
+//   B2OT_TC_POLY        1: a quarter of the exponentials on the FMA pipe (Cody-Waite + degree-4 polynomial)
+//   B2OT_TC_ATMEM       1: 3xFP16 row operand resident in tensor memory (written once per CTA with tcgen05.st),
+//                          3 accumulator stages of 128 columns + 64 operand columns
+#ifndef B2OT_TC_EPI_SINGLE
+#define B2OT_TC_EPI_SINGLE 1
+#endif
+#ifndef B2OT_TC_POLY
+#define B2OT_TC_POLY 0
+#endif
+#ifndef B2OT_TC_CLAMP
+#define B2OT_TC_CLAMP 1   // 0 (measurement only): without the clamp C >= 0
+#endif
+#ifndef B2OT_TC_ATMEM
+#define B2OT_TC_ATMEM 0
+#endif
+#if B2OT_TC_ATMEM
+constexpr int TC_NACC = 3;        // accumulator stages in tensor memory (the row operand takes the last 64 columns)
+#else
 constexpr int TC_NACC = 4;        // accumulator stages in tensor memory
+#endif
+constexpr uint32_t TC_ATMEM_COL = 384;  // first tensor-memory column of the resident row operand (hi: 32 columns, lo: 32)
 #ifndef B2OT_TC_EPI_WARPS
 #define B2OT_TC_EPI_WARPS 12
 #endif
@@ -241,6 +264,17 @@ __device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint6
       ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// row operand read from tensor memory (lane = row, one 32-bit column = two consecutive K elements), column operand
+// from shared memory
+__device__ __forceinline__ void umma_f16_ta(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "elect.sync _|q, 0xFFFFFFFF;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // NOTE: the tcgen05.mma / tcgen05.commit wrappers are WARP-level calls: every lane of the converged MMA warp executes
 // them with identical (warp-uniform) operands and one lane is elected inside the asm block.  ptxas then keeps the
 // descriptors in uniform registers and emits back-to-back UTCHMMA; issuing from `if (lane == 0)` instead costs an
@@ -303,6 +337,49 @@ constexpr uint32_t TC_IDESC = (1u << 4) /*D = f32*/ | (2u << 7) /*A = tf32*/ | (
                :                                                                                                       \
                : "memory")
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// registers -> tensor memory, 32 lanes x 32 columns (thread i of the warp writes lane base + i, register k column k)
+#define B2OT_TMEM_ST32(taddr, v)                                                                                       \
+  asm volatile(                                                                                                        \
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "                                                                  \
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "                                       \
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"                               \
+      :                                                                                                                \
+      : "r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), \
+        "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]),     \
+        "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]),    \
+        "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])                                                     \
+      : "memory")
+// shared-memory read the compiler may neither hoist nor merge (keeps its place between the other volatile statements)
+__device__ __forceinline__ float4 lds128_volatile(uint32_t addr) {
+  float4 r;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(addr));
+  return r;
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// 2^t for a PAIR of arguments on the FMA / ALU pipes (no MUFU): t clamped to >= -126, n = round(t) peeled off with the
+// 1.5 * 2^23 trick, 2^f on f in [-0.5, 0.5] by a degree-4 minimax polynomial (relative error 2.7e-6: the terms it
+// serves are a quarter of a sum of hundreds, and the potentials see reg * that error), n added into the exponent
+// field.  Exactly-zero terms (t = -inf: padding, zero weights) come out as 2^-126 instead of 0.
+__device__ __forceinline__ void ex2_poly2(float& t0, float& t1) {
+  const float MAGIC = 12582912.f;
+  t0 = fmaxf(t0, -126.f);
+  t1 = fmaxf(t1, -126.f);
+  float j0 = t0, j1 = t1;
+  add2(j0, j1, MAGIC, MAGIC);
+  float n0 = j0, n1 = j1;
+  add2(n0, n1, -MAGIC, -MAGIC);
+  float f0, f1;
+  fma2(f0, f1, n0, n1, -1.f, -1.f, t0, t1);
+  float p0, p1;
+  const float C4 = 9.5733143e-3f, C3 = 5.5920169e-2f, C2 = 2.4024625e-1f, C1 = 6.9312131e-1f, C0 = 0.99999928f;
+  fma2(p0, p1, f0, f1, C4, C4, C3, C3);
+  fma2(p0, p1, p0, p1, f0, f1, C2, C2);
+  fma2(p0, p1, p0, p1, f0, f1, C1, C1);
+  fma2(p0, p1, p0, p1, f0, f1, C0, C0);
+  t0 = __int_as_float(__float_as_int(p0) + (__float_as_int(j0) << 23));
+  t1 = __int_as_float(__float_as_int(p1) + (__float_as_int(j1) << 23));
+}
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -362,6 +439,7 @@ struct EmpTcParams {
 __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcParams p) {
   extern __shared__ unsigned char tc_smem_raw[];
   __shared__ __align__(8) uint64_t a_full;
+  __shared__ __align__(8) uint64_t a_tmem_full;  // B2OT_TC_ATMEM: row operand written to tensor memory (128 arrivals)
   __shared__ __align__(8) uint64_t b_full[TC_NB], b_empty[TC_NB];
   __shared__ __align__(8) uint64_t acc_full[TC_NACC], acc_empty[TC_NACC];
   __shared__ uint32_t tmem_holder;
@@ -390,9 +468,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
   const uint16_t cmask = (uint16_t)((1u << cs) - 1u);
   const long long row_tiles = (p.nx + TC_BM - 1) / TC_BM;
   const long long row_tile_ld = row_tile < row_tiles ? row_tile : row_tiles - 1;  // padding CTA of the last cluster
+  // row operand resident in tensor memory: 3xFP16 with one K chunk (d <= 64) = 2 x 32 columns
+  const bool atm = (B2OT_TC_ATMEM != 0) && p.kind == 1 && p.kc == 1;
 
   if (tid == 0) {
     mbar_init(&a_full, 1);
+    mbar_init(&a_tmem_full, 128);
     for (int s = 0; s < TC_NB; ++s) {
       mbar_init(&b_full[s], 1);
       mbar_init(&b_empty[s], cs);
@@ -453,6 +534,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
     const int mw = (warp == 1) ? 0 : 1;
     if (ntiles > 0) {
       mbar_wait_guard(&a_full, 0);
+      if (atm) {
+        mbar_wait_guard(&a_tmem_full, 0);
+        tc_fence_after();
+      }
       const uint32_t a_addr = smem_u32(As);
       // The CTA owns all 512 TMEM columns, so the allocation starts at column 0 / lane 0: using the literal 0 keeps
       // the accumulator address in a uniform register (an address loaded from shared memory would force a
@@ -484,7 +569,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
               const uint64_t ah = umma_desc_sw128(a_chunk + off_hi), al = umma_desc_sw128(a_chunk + off_lo);
               const uint64_t bh = umma_desc_sw128(b_addr + off_hi), bl = umma_desc_sw128(b_addr + off_lo);
               if (TC_DBG(4)) continue;
-              if (p.kind == 0) {
+              if (atm) {
+                const uint32_t tah = TC_ATMEM_COL + (uint32_t)(ks * 8), tal = tah + 32u;
+                umma_f16_ta(d_tmem, tal, bh, TC_IDESC_F16, acc);
+                umma_f16_ta(d_tmem, tah, bl, TC_IDESC_F16, 1u);
+                umma_f16_ta(d_tmem, tah, bh, TC_IDESC_F16, 1u);
+              } else if (p.kind == 0) {
                 umma_tf32(d_tmem, al, bh, TC_IDESC, acc);  // small terms first
                 umma_tf32(d_tmem, ah, bl, TC_IDESC, 1u);
                 umma_tf32(d_tmem, ah, bh, TC_IDESC, 1u);
@@ -531,6 +621,29 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
       py = ok ? p.yy[j] : 0.f;
     };
     fetch(wg);
+    if (atm && wg == 0 && ntiles > 0) {
+      // this thread's row of the (hi, lo) fp16 operand: shared memory (swizzled 16-byte units) -> registers -> tensor
+      // memory lane rloc, 32 + 32 columns (column c = coordinates 2c, 2c + 1)
+      mbar_wait_guard(&a_full, 0);
+      const unsigned char* rowp = As + (rloc >> 3) * 1024 + (rloc & 7) * 128;
+      const uint32_t ta = tmem_base + ((uint32_t)(q * 32) << 16) + TC_ATMEM_COL;
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        uint32_t w[32];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint4 u = *reinterpret_cast<const uint4*>(rowp + half * TC_SUB + ((j ^ (rloc & 7)) << 4));
+          w[4 * j + 0] = u.x;
+          w[4 * j + 1] = u.y;
+          w[4 * j + 2] = u.z;
+          w[4 * j + 3] = u.w;
+        }
+        B2OT_TMEM_ST32(ta + (uint32_t)(half * 32), w);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      mbar_arrive(&a_tmem_full);
+    }
     for (long long t = wg; t < ntiles; t += TC_NWG) {
       const int as = (int)(t % TC_NACC);
       const uint32_t aph = (uint32_t)((t / TC_NACC) & 1);
@@ -555,6 +668,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
       //   P1: (pot_j - C_ij / reg) log2e = min(2 k2 x.y + B_j - k2 |x|^2, G_j)   [clamp C >= 0, ot/utils.py:299],
       //       written back in place, and the chunk maximum;
       //   P2: online (max, sum 2^x) update.  Packed fp32x2 arithmetic throughout.
+#if !B2OT_TC_EPI_SINGLE
       auto phase1 = [&](uint32_t (&v)[32], int ch) -> float {
         float c0 = -CUDART_INF_F, c1 = -CUDART_INF_F;
         if (TC_DBG(2)) return c0;
@@ -608,6 +722,86 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
         s_run = (s0 + s1) + (s2 + s3);
         m_run = m_new;
       };
+#endif
+      // One pass per chunk against a LAGGING reference exponent (B2OT_TC_EPI_SINGLE): m_run is a value this row
+      // attained in an earlier chunk (or 0 when the first values lie within 2^+-64 of it), so t = r - m_run needs no
+      // chunk maximum before the exponentials: cost, clamp, 2^t and the sums are independent per element - the
+      // instruction-level parallelism the two-phase form lacks (there every pipe sat near 50 % and the rest was
+      // dependency latency, profiles/r01d_emp_limiters.log).  The chunk maximum of t is tracked on the side: a chunk
+      // that rises more than 64 above the reference (2^t could overflow), or a first chunk far from 0, moves the
+      // reference to its own maximum, rescales the running sum and is redone.  Terms more than 126 below the reference
+      // flush to zero: they are below 2^-62 of a term that is present in the sum.
+      auto chunk = [&](uint32_t (&v)[32], int ch) {
+#if B2OT_TC_EPI_SINGLE
+        const uint32_t cb_addr = smem_u32(cB) + (uint32_t)(ch * 32 * sizeof(float));
+        for (;;) {
+          const bool unset = (m_run == -CUDART_INF_F);
+          const float base = unset ? 0.f : m_run;
+          const float c1 = nxk - base;
+          float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f, x0 = -CUDART_INF_F, x1 = -CUDART_INF_F;
+          // the column vectors are read two groups ahead with volatile loads: the compiler otherwise hoists all 16
+          // LDS.128 of a chunk (and keeps them live across the redo loop), 64 registers that spill
+          float4 bq[3];
+          bq[0] = lds128_volatile(cb_addr);
+          bq[1] = lds128_volatile(cb_addr + 16u);
+#if B2OT_TC_CLAMP
+          const float ng = -base;
+          float4 gq[3];
+          gq[0] = lds128_volatile(cb_addr + (uint32_t)(TC_BN * sizeof(float)));
+          gq[1] = lds128_volatile(cb_addr + (uint32_t)(TC_BN * sizeof(float)) + 16u);
+#endif
+#pragma unroll
+          for (int g4 = 0; g4 < 8; ++g4) {
+            if (g4 + 2 < 8) {
+              bq[(g4 + 2) % 3] = lds128_volatile(cb_addr + (uint32_t)((g4 + 2) * 16));
+#if B2OT_TC_CLAMP
+              gq[(g4 + 2) % 3] = lds128_volatile(cb_addr + (uint32_t)(TC_BN * sizeof(float)) + (uint32_t)((g4 + 2) * 16));
+#endif
+            }
+            float z0 = bq[g4 % 3].x, z1 = bq[g4 % 3].y, z2 = bq[g4 % 3].z, z3 = bq[g4 % 3].w;
+            add2(z0, z1, c1, c1);
+            add2(z2, z3, c1, c1);
+            float t0, t1, t2, t3;
+            fma2(t0, t1, __uint_as_float(v[g4 * 4 + 0]), __uint_as_float(v[g4 * 4 + 1]), k22, k22, z0, z1);
+            fma2(t2, t3, __uint_as_float(v[g4 * 4 + 2]), __uint_as_float(v[g4 * 4 + 3]), k22, k22, z2, z3);
+#if B2OT_TC_CLAMP
+            float h0 = gq[g4 % 3].x, h1 = gq[g4 % 3].y, h2 = gq[g4 % 3].z, h3 = gq[g4 % 3].w;
+            add2(h0, h1, ng, ng);
+            add2(h2, h3, ng, ng);
+            t0 = fminf(t0, h0);
+            t1 = fminf(t1, h1);
+            t2 = fminf(t2, h2);
+            t3 = fminf(t3, h3);
+#endif
+            x0 = max3(x0, t0, t1);
+            x1 = max3(x1, t2, t3);
+            t0 = ex2_ftz(t0);
+            t1 = ex2_ftz(t1);
+#if B2OT_TC_POLY
+            if (g4 & 1) {
+              ex2_poly2(t2, t3);
+            } else
+#endif
+            {
+              t2 = ex2_ftz(t2);
+              t3 = ex2_ftz(t3);
+            }
+            add2(s0, s1, t0, t1);
+            add2(s2, s3, t2, t3);
+          }
+          const float cm = fmaxf(x0, x1);
+          if (cm <= 64.f && (!unset || cm >= -64.f || cm == -CUDART_INF_F)) {
+            s_run += (s0 + s1) + (s2 + s3);
+            if (unset && cm != -CUDART_INF_F) m_run = 0.f;
+            break;
+          }
+          s_run = unset ? 0.f : s_run * ex2_ftz(-cm);
+          m_run = base + cm;
+        }
+#else
+        phase2(v, phase1(v, ch));
+#endif
+      };
       if (TC_DBG(16)) {  // experiment: no TMEM reads
         tc_fence_before();
         mbar_arrive(&acc_empty[as]);
@@ -617,17 +811,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) emp_tc_lse_kernel(const EmpTcPa
       B2OT_TMEM_LD32(taddr, b0);
       B2OT_TMEM_WAIT32(b0);
       B2OT_TMEM_LD32(taddr + 32u, b1);
-      phase2(b0, phase1(b0, 0));
+      chunk(b0, 0);
       B2OT_TMEM_WAIT32(b1);
       B2OT_TMEM_LD32(taddr + 64u, b0);
-      phase2(b1, phase1(b1, 1));
+      chunk(b1, 1);
       B2OT_TMEM_WAIT32(b0);
       B2OT_TMEM_LD32(taddr + 96u, b1);
-      phase2(b0, phase1(b0, 2));
+      chunk(b0, 2);
       B2OT_TMEM_WAIT32(b1);
       tc_fence_before();
       mbar_arrive(&acc_empty[as]);  // accumulator stage drained: the MMA warp may overwrite it
-      phase2(b1, phase1(b1, 3));
+      chunk(b1, 3);
       if (et == 0) B2OT_TRACE(7, t);
     }
     // merge the warpgroups' running (max, sum) of each row

@@ -41,7 +41,7 @@ def run(n, m, d, variant, iters):
 if __name__ == "__main__":
     sizes = [int(x) for x in os.environ.get("SIZES", "8192,32768,65536").split(",")]
     for n in sizes:
-        for variant in ("tc", "simt"):
+        for variant in os.environ.get("VARIANTS", "tc,simt").split(","):
             if variant == "simt" and n > 32768:
                 continue
             iters = max(2, min(20, int(2e11 / (n * n * (1 if variant == "tc" else 8)))))

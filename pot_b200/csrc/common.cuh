@@ -119,6 +119,11 @@ __device__ __forceinline__ float warp_max_redux(float x) {
   asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(x));
   return r;
 }
+__device__ __forceinline__ float warp_min_redux(float x) {
+  float r;
+  asm volatile("redux.sync.min.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(x));
+  return r;
+}
 __device__ __forceinline__ float lg2_ftz(float x) {
   float y;
   asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));

@@ -289,6 +289,62 @@ def test_tc_wide_dynamic_range(kind, operand):
         assert np.abs(x[typ] - r[typ]).max() <= allow, (nm, kind, operand, np.abs(x[typ] - r[typ]).max(), allow)
 
 
+@pytest.mark.parametrize("operand", ["f16", "tf32"])
+@pytest.mark.parametrize("reg", [0.5, 0.02])
+def test_tc_coincident_points(reg, operand):
+    """The tensor-core sweep leaves out the reference's clamp C >= 0 (ot/utils.py:299; emp_tc_kernels.cuh header): it
+    matters only where the computed cost is negative, i.e. for (near-)coincident points.  Worst case on purpose: the
+    target cloud IS the source cloud (every row has an exact zero of the cost on the diagonal) plus duplicated points,
+    small reg so that the diagonal term dominates each log-sum-exp.  Reference: the fp64 oracle, which clamps."""
+    n, d = 900, 64
+    rng = np.random.RandomState(5)
+    xs = (rng.randn(n, d) / np.sqrt(d)).astype(np.float32)
+    xs[1::50] = xs[::50][: len(xs[1::50])]  # duplicates off the diagonal too
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        fr, gr = orc.empirical_sinkhorn_lazy(xs.astype(np.float64), xs.astype(np.float64), reg, numIterMax=20,
+                                             stopThr=-1, batchSize=256)
+        X = dev(xs)
+        f, g = ot.empirical_sinkhorn(X, X, reg, numIterMax=20, stopThr=-1, isLazy=True, b2ot_variant="tc",
+                                     b2ot_operand=operand)
+    assert torch.isfinite(f).all() and torch.isfinite(g).all()
+    logclose(f, fr, 1e-4, f"f (coincident, reg {reg}, {operand})")
+    logclose(g, gr, 1e-4, f"g (coincident, reg {reg}, {operand})")
+
+
+@pytest.mark.parametrize("n", [16384])
+def test_tc_multiwave_vs_fp64(n):
+    """Config-4 shaped sweep at a size with several waves of CTAs and reduction splits (16384^2 x 64: 128 row tiles x
+    splits over 148 SMs): 3 iterations of the tensor-core solver against a chunked fp64 torch restatement of the same
+    recursion (_empirical.py:218-233: f = log a - LSE_j(g_j - C_ij/reg), then g = log b - LSE_i(f_i - C_ij/reg)), 1e-4."""
+    d, reg, its = 64, 0.1, 3
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    xs = torch.randn(n, d, device="cuda", generator=gen) / d ** 0.5
+    xt = torch.randn(n, d, device="cuda", generator=gen) / d ** 0.5 + 1.0 / d ** 0.5
+    f, g = ot.empirical_sinkhorn(xs, xt, reg, numIterMax=its, stopThr=-1, isLazy=True, warn=False, b2ot_variant="tc")
+    X, Y = xs.double(), xt.double()
+    la = torch.full((n,), -np.log(n), dtype=torch.float64, device="cuda")
+    fr = torch.zeros(n, dtype=torch.float64, device="cuda")
+    gr = torch.zeros(n, dtype=torch.float64, device="cuda")
+
+    def half(P, Q, pot):  # log(1/n) - LSE_j(pot_j - |P_i - Q_j|^2 / reg), row chunks of 2048
+        out = torch.empty(P.shape[0], dtype=torch.float64, device="cuda")
+        qq = (Q * Q).sum(1)
+        for c0 in range(0, P.shape[0], 2048):
+            Pc = P[c0:c0 + 2048]
+            C = ((Pc * Pc).sum(1)[:, None] + qq[None, :] - 2.0 * Pc @ Q.T).clamp_min_(0.0)
+            out[c0:c0 + 2048] = -torch.logsumexp(pot[None, :] - C / reg, dim=1)
+        return out + la
+
+    for _ in range(its):
+        fr = half(X, Y, gr)
+        gr = half(Y, X, fr)
+    for got, ref, nm in ((f, fr, "f"), (g, gr, "g")):
+        err = float((got.double() - ref).abs().max())
+        scale = max(1.0, float(ref.abs().max()))
+        assert err <= 1e-4 * scale, (nm, err, scale)
+
+
 def test_tc_rejects_ineligible():
     rng = np.random.RandomState(0)
     xs, xt = dev(rng.randn(20, 70).astype(np.float32)), dev(rng.randn(30, 70).astype(np.float32))

@@ -509,12 +509,16 @@ def bench_dense(ctx, cfg):
     achieved = alg_bytes / (sweep_ms * 1e-3) / 1e9
     kern = {1: "fused_sweep_kernel<double, knopp>", 2: "log_pp_sweep_kernel (fp32 log-domain ping-pong sweep)",
             3: "fused_sweep_kernel<float, 8, knopp>"}[cfg]
+    if info.get("variant") == "resident":
+        kern = ("resident_knopp_kernel<%s> (K in the grid's shared memory, one cooperative launch per chunk of iterations; "
+                "launch_ms = per iteration)" % ("double" if cfg == 1 else "float"))
     roof = {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
             "traffic": traffic_from_profiles(f"{mode}_{DTYPE[cfg]}_{nloc}x{m}"), "kernel": kern,
             "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": sweep_ms, "peak_source": pk["source"],
             "frac_of_nominal_8TBs": achieved / 8000.0}
     if cfg == 1:
-        roof["note"] = "8 MB problem: L2-resident and launch-latency bound, the HBM fraction is not the limiter here"
+        roof["note"] = ("8 MB problem: K stays on chip; an iteration is bound by two grid barriers and the L2 round trips of the "
+                        "column partials, the HBM fraction is not the limiter here")
 
     e2e = None
     if not args.no_e2e:

@@ -60,7 +60,8 @@ class DenseSolver:
         code = dtype_code(K.dtype)
         nbytes = self.lib.b2ot_dense_workspace_bytes(self.n, self.m, code, self.max_iter, int(check_every))
         self.ws = torch.empty(nbytes, dtype=torch.uint8, device=K.device)
-        var = {"auto": _lib.VARIANT_AUTO, "fused": _lib.VARIANT_FUSED, "split": _lib.VARIANT_SPLIT}[variant]
+        var = {"auto": _lib.VARIANT_AUTO, "fused": _lib.VARIANT_FUSED, "split": _lib.VARIANT_SPLIT,
+               "resident": _lib.VARIANT_RESIDENT}[variant]
         h = C.c_void_p()
         with torch.cuda.device(self.device):
             _lib.check(self.lib.b2ot_dense_create(
@@ -108,7 +109,10 @@ class DenseSolver:
         _lib.check(self.lib.b2ot_dense_info(self.h, *[C.byref(x) for x in v]), "b2ot_dense_info")
         names = ("variant", "cluster_size", "n_clusters", "stages", "vecs_per_thread")
         out = dict(zip(names, (x.value for x in v)))
-        out["variant"] = {1: "fused", 2: "split"}.get(out["variant"], "?")
+        out["variant"] = {1: "fused", 2: "split", 3: "resident"}.get(out["variant"], "?")
+        if out["variant"] == "resident":  # K in the grid's shared memory: CTAs and rows per CTA
+            out = {"variant": "resident", "ctas": out["n_clusters"], "rows_per_cta": out["stages"]}
+            return out
         if out["vecs_per_thread"] >= 100:  # fp32 log domain: two independent half-CTAs (dense_logpp_kernels.cuh)
             out["vecs_per_thread"] -= 100
             out["schedule"] = "ping-pong"

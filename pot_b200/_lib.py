@@ -14,7 +14,7 @@ LIB_PATH = os.environ.get("B2OT_LIB") or os.path.join(_HERE, "libb2ot.so")
 F32, F64 = 0, 1
 MODE_KNOPP, MODE_LOG = 0, 1
 ST_RUNNING, ST_CONVERGED, ST_NUMERR, ST_MAXITER = 0, 1, 2, 3
-VARIANT_AUTO, VARIANT_FUSED, VARIANT_SPLIT = 0, 1, 2
+VARIANT_AUTO, VARIANT_FUSED, VARIANT_SPLIT, VARIANT_RESIDENT = 0, 1, 2, 3
 OP_SUM, OP_MAX = 0, 1
 BATCH_FORCE_EXACT = 1
 VALUE_LINEAR, VALUE_ENTROPY, VALUE_KL, VALUE_KMULQ = 1, 2, 4, 8

@@ -12,6 +12,7 @@
 #include "../../include/b2ot.h"
 #include "comm_host.h"
 #include "dense_kernels.cuh"
+#include "dense_resident_kernels.cuh"
 #include "dense_logpp_kernels.cuh"
 #include "host_util.h"
 
@@ -117,6 +118,13 @@ struct b2ot_dense {
   const void* stab_mr;  // Mr = -M/reg (n x m, leading dimension stab_ld), source of the K rebuilds
   long long stab_ld;
   void *stab_alpha, *stab_beta;  // caller-owned alpha/reg (n), beta/reg (m) as DOUBLES, updated by the absorptions
+  // resident solver of small problems (dense_resident_kernels.cuh): K lives in the grid's shared memory
+  int res_ok;        // shape fits and the variant allows it
+  int res_rows;      // rows per CTA
+  int res_cols;      // columns per CTA
+  int res_rep;       // copies of the exchange area
+  int res_grid;      // CTAs (<= SM count: the launch is cooperative)
+  size_t res_smem;
 };
 
 static void drop_graph(b2ot_dense* h);
@@ -563,12 +571,90 @@ static bool plan_fused(b2ot_dense* h) {
   return true;
 }
 
+// Resident solver: eligible when the grid's shared memory holds K twice (a block of rows and a block of columns per
+// CTA, at most one CTA per SM).  Scaling domain only.
+static bool plan_resident(b2ot_dense* h, int sm_count) {
+  h->res_ok = 0;
+  if (h->mode != B2OT_MODE_KNOPP) return false;
+  if (const char* e = diag_env("B2OT_RESIDENT"))
+    if (e[0] == '0') return false;
+  if (sm_count > RES_MAXG) sm_count = RES_MAXG;
+  const long long grid = std::min<long long>(sm_count, std::max(h->n, h->m));
+  const long long rows = (h->n + grid - 1) / grid, cols = (h->m + grid - 1) / grid;
+  const size_t sz = esize(h->dtype);
+  const size_t smem = ((size_t)rows * h->m + (size_t)cols * h->n + 2 * h->m + h->n + 2 * (rows + cols) + 64) * sz + 64;
+  if (smem > 200 * 1024) return false;
+  // the exchange words live in the partial-sum scratch of the streaming solver (unused on this path): as many copies
+  // as fit, at most 8
+  int rep = 2;  // measured at n = m = 1000 fp64: 1 / 2 / 4 / 8 copies = 8.5 / 7.5 / 8.7 / 9.0 us per iteration
+  while (rep > 1 && res_xbuf_bytes(h->n, h->m, (int)(sz / 4), rep) > (size_t)NPMAX * h->mp * sz) rep >>= 1;
+  if (res_xbuf_bytes(h->n, h->m, (int)(sz / 4), rep) > (size_t)NPMAX * h->mp * sz) return false;
+  if (const char* e = diag_env("B2OT_RES_REPLICAS")) rep = std::max(1, std::min(rep, atoi(e)));
+  h->res_rep = rep;
+  int coop = 0, dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+  if (!coop) return false;
+  const void* fn = h->dtype == B2OT_F32 ? (const void*)resident_knopp_kernel<float> : (const void*)resident_knopp_kernel<double>;
+  if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, RES_THREADS, smem) != cudaSuccess || per_sm < 1) {
+    cudaGetLastError();
+    return false;
+  }
+  h->res_rows = (int)rows;
+  h->res_cols = (int)cols;
+  h->res_grid = (int)grid;
+  h->res_smem = smem;
+  h->res_ok = 1;
+  return true;
+}
+// the resident path serves the plain balanced scaling iteration on one device
+static inline bool resident_active(const b2ot_dense* h) {
+  return h->res_ok && !h->unbal && h->tau <= 0.0 && h->ar == nullptr && h->comm == nullptr;
+}
+template <typename T>
+static int launch_resident(b2ot_dense* h, int n_iters) {
+  if (n_iters <= 0) return 0;
+  ResParams p;
+  memset(&p, 0, sizeof(p));
+  p.K = h->K;  p.ld = h->ld;  p.n = h->n;  p.m = h->m;  p.mp = h->mp;
+  p.a = h->a;  p.b = h->b;
+  p.uring = h->uring;  p.vring = h->vring;  p.cbuf = h->cbuf;  p.xbuf = h->partials;
+  p.st = h->st;  p.err_hist = h->err_hist;
+  p.max_iter = h->max_iter;  p.check_every = h->check_every;  p.stop_thr = h->stop_thr;
+  p.n_iters = n_iters;
+  p.rows_per_cta = h->res_rows;
+  p.cols_per_cta = h->res_cols;
+  p.replicas = h->res_rep;
+#ifdef B2OT_DIAG
+  if (diag_env("B2OT_RES_TRACE")) p.trace = (long long*)h->blk_err;  // 64 iterations x 8 stamps = the 512 leading doubles' bytes... (4 KB of the 8 KB block)
+#endif
+  void* args[] = {(void*)&p};
+  const cudaError_t e = cudaLaunchCooperativeKernel((const void*)resident_knopp_kernel<T>, dim3((unsigned)h->res_grid),
+                                                    dim3(RES_THREADS), args, h->res_smem, h->stream);
+  if (e == cudaErrorCooperativeLaunchTooLarge || e == cudaErrorLaunchOutOfResources) {
+    // the grid cannot be co-resident right now (SMs taken away by MPS / a partitioned device): the streaming solver
+    // continues the same solve from the same state
+    cudaGetLastError();
+    h->res_ok = 0;
+    return 1;
+  }
+  B2OT_CUDA(e);
+  count_launch();
+  return 0;
+}
+
 extern "C" int b2ot_dense_create(b2ot_dense** handle, int mode, int dtype, int64_t n, int64_t m, int64_t ld,
                                  const void* K, const void* a, const void* b, const void* logb, void* workspace,
                                  size_t workspace_bytes, int max_iter, int check_every, double stop_thr, int variant,
                                  void* stream) {
   B2OT_REQUIRE(handle != nullptr, "b2ot_dense_create: null handle pointer");
   B2OT_REQUIRE(mode == B2OT_MODE_KNOPP || mode == B2OT_MODE_LOG, "b2ot_dense_create: bad mode %d", mode);
+  B2OT_REQUIRE(variant >= B2OT_VARIANT_AUTO && variant <= B2OT_VARIANT_RESIDENT, "b2ot_dense_create: bad variant %d", variant);
   B2OT_REQUIRE(dtype == B2OT_F32 || dtype == B2OT_F64, "b2ot_dense_create: bad dtype %d", dtype);
   B2OT_REQUIRE(n >= 1 && m >= 1 && ld >= m, "b2ot_dense_create: bad shape n=%lld m=%lld ld=%lld", (long long)n,
                (long long)m, (long long)ld);
@@ -621,6 +707,16 @@ extern "C" int b2ot_dense_create(b2ot_dense** handle, int mode, int dtype, int64
   h->nsplit_lse = (int)ns;
   h->fin_blocks = (int)std::min<long long>(colblocks, 1024);
 
+  if (variant == B2OT_VARIANT_AUTO || variant == B2OT_VARIANT_RESIDENT) plan_resident(h, sm);
+  if (variant == B2OT_VARIANT_RESIDENT) {
+    if (!h->res_ok) {
+      delete h;
+      set_error("b2ot_dense_create: the resident solver needs the scaling domain and K twice within the grid's shared "
+                "memory (a row block and a column block per CTA, <= 200 KB), got n=%lld m=%lld", (long long)n, (long long)m);
+      return -1;
+    }
+    variant = B2OT_VARIANT_AUTO;  // the streaming fallback behind it (unbalanced / stabilized / sharded use)
+  }
   bool fused_ok = plan_fused(h);
   if (variant == B2OT_VARIANT_FUSED && !fused_ok) {
     delete h;
@@ -689,6 +785,14 @@ extern "C" int b2ot_dense_set_comm(b2ot_dense* h, b2ot_comm* comm) {
 extern "C" int b2ot_dense_info(const b2ot_dense* h, int* variant, int* cluster_size, int* n_clusters, int* stages,
                                int* vecs_per_thread) {
   B2OT_REQUIRE(h != nullptr, "b2ot_dense_info: null handle");
+  if (resident_active(h)) {  // K in the grid's shared memory: n_clusters = CTAs, stages = rows per CTA
+    if (variant) *variant = B2OT_VARIANT_RESIDENT;
+    if (cluster_size) *cluster_size = 1;
+    if (n_clusters) *n_clusters = h->res_grid;
+    if (stages) *stages = h->res_rows;
+    if (vecs_per_thread) *vecs_per_thread = 0;
+    return 0;
+  }
   if (variant) *variant = h->variant;
   if (cluster_size) *cluster_size = h->variant == B2OT_VARIANT_FUSED ? h->cs : 0;
   if (n_clusters) *n_clusters = h->variant == B2OT_VARIANT_FUSED ? h->ncl : h->nsplit;
@@ -911,6 +1015,8 @@ static int launch_exact_cols(const b2ot_dense* h, int expect_status, int advance
 template <typename T>
 static int dense_init_t(b2ot_dense* h, const void* u0, const void* v0) {
   B2OT_CUDA(cudaMemsetAsync(h->st, 0, 256, h->stream));
+  if (h->res_ok)  // exchange words of the resident solver: epoch 0 everywhere
+    B2OT_CUDA(cudaMemsetAsync(h->partials, 0, res_xbuf_bytes(h->n, h->m, (int)(sizeof(T) / 4), h->res_rep), h->stream));
   B2OT_CUDA(cudaMemcpyAsync(h->uring, u0, (size_t)h->n * sizeof(T), cudaMemcpyDeviceToDevice, h->stream));
   B2OT_CUDA(cudaMemcpyAsync(h->vring, v0, (size_t)h->m * sizeof(T), cudaMemcpyDeviceToDevice, h->stream));
   if (h->unbal) return 0;  // u-then-v order: the first sweep starts from v0, no seeding pass
@@ -1029,6 +1135,10 @@ static void build_graph(b2ot_dense* h) {
 
 template <typename T>
 static int dense_iterate_t(b2ot_dense* h, int n_iters) {
+  if (resident_active(h)) {
+    const int rc = launch_resident<T>(h, n_iters);
+    if (rc <= 0) return rc;  // 1: not launchable, go on with the streaming solver
+  }
   if (graphs_enabled() && h->ar == nullptr && h->comm == nullptr && n_iters >= kGraphIters) {
     if (h->graph_state == 0) build_graph<T>(h);
     while (h->graph_state == 1 && n_iters >= kGraphIters) {
@@ -1054,6 +1164,29 @@ extern "C" int b2ot_dense_iterate(b2ot_dense* h, int n_iters) {
 // launch stream).  Reports the average duration of the sweep kernel(s) alone and of a whole iteration.
 extern "C" int b2ot_dense_profile(b2ot_dense* h, int n_iters, float* sweep_ms_avg, float* iter_ms_avg) {
   B2OT_REQUIRE(h != nullptr && n_iters >= 1 && n_iters <= 4096, "b2ot_dense_profile: bad arguments");
+  if (resident_active(h)) {  // one launch runs all n_iters iterations: sweep and iteration time coincide
+    cudaEvent_t e0, e1;
+    B2OT_CUDA(cudaEventCreate(&e0));
+    B2OT_CUDA(cudaEventCreate(&e1));
+    B2OT_CUDA(cudaEventRecord(e0, h->stream));
+    int rc = h->dtype == B2OT_F32 ? launch_resident<float>(h, n_iters) : launch_resident<double>(h, n_iters);
+    if (rc > 0) {
+      cudaEventDestroy(e0);
+      cudaEventDestroy(e1);
+      return b2ot_dense_profile(h, n_iters, sweep_ms_avg, iter_ms_avg);  // streaming path from here on
+    }
+    if (rc == 0) {
+      B2OT_CUDA(cudaEventRecord(e1, h->stream));
+      B2OT_CUDA(cudaStreamSynchronize(h->stream));
+      float ms = 0.f;
+      B2OT_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+      if (sweep_ms_avg) *sweep_ms_avg = ms / n_iters;
+      if (iter_ms_avg) *iter_ms_avg = ms / n_iters;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return rc;
+  }
   std::vector<cudaEvent_t> ev(2 * (size_t)n_iters + 1);
   for (auto& e : ev) B2OT_CUDA(cudaEventCreate(&e));
   int rc = 0;

@@ -59,7 +59,7 @@ def assert_errs(errs, ref, dtype):
     assert np.all(np.abs(e - r) <= 1e-3 * r + floor), (e, r)
 
 
-@pytest.mark.parametrize("variant", ["fused", "split"])
+@pytest.mark.parametrize("variant", ["fused", "split", "resident"])
 @pytest.mark.parametrize("case", DENSE)
 def test_knopp_golden_fixed(golden, case, variant):
     a, b, M = golden(case, "a"), golden(case, "b"), golden(case, "M")
@@ -157,7 +157,7 @@ def test_numerical_guard_reverts_like_reference(golden):
     (ot/bregman/_sinkhorn.py:633-645).  The device-side guard must stop at the same iteration."""
     a, b, M = golden("guard", "a"), golden("guard", "b"), golden("guard", "M")
     at, bt, Mt = to_dev(a, b, M)
-    for variant in ("fused", "split"):
+    for variant in ("fused", "split", "resident"):
         with warnings.catch_warnings(record=True) as w:
             warnings.simplefilter("always")
             G, lg = ot.bregman.sinkhorn_knopp(at, bt, Mt, 1e-3, numItermax=50, stopThr=0, log=True,
@@ -259,6 +259,83 @@ def test_oracle_parity_shapes(mode, shape, dtype):
     assert_errs(lg["err"], lgr["err"], dtype)
 
 
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("shape", [(1, 1), (3, 4), (7, 1), (148, 256), (149, 257), (257, 1031), (1000, 1000), (2000, 999),
+                                   (4000, 1500), (300, 4096)])
+def test_resident_solver(shape, dtype):
+    """Small problems on the resident solver (K in the grid's shared memory, one cooperative launch per chunk of
+    iterations, dense_resident_kernels.cuh): ragged row / column splits over the CTAs against the oracle and against the
+    streaming sweep; convergence stop at the reference's iteration; chunked iterate calls; what does not fit is refused."""
+    n, m = shape
+    rng = np.random.RandomState(n * 5 + m)
+    xs, xt = rng.randn(n, 2), rng.randn(m, 2) + 1.0
+    M = orc.sqeuclidean(xs, xt)
+    M = (M / M.max()).astype(dtype)
+    a = rng.rand(n) + 0.1
+    b = rng.rand(m) + 0.1
+    a, b = (a / a.sum()).astype(dtype), (b / b.sum()).astype(dtype)
+    at, bt, Mt = to_dev(a, b, M)
+    tol = tol_of(dtype)
+    grid = min(148, max(n, m))  # plan_resident (dense.cu): a row block and a column block of K per CTA, <= 200 KB
+    R_, Q_ = -(-n // grid), -(-m // grid)
+    fits = (R_ * m + Q_ * n + 2 * m + n + 2 * (R_ + Q_) + 64) * M.itemsize + 64 <= 200 * 1024
+    if not fits:
+        with pytest.raises(_lib.B2otError, match="resident solver needs"):
+            ot.bregman.sinkhorn_knopp(at, bt, Mt, 0.1, numItermax=5, stopThr=0, warn=False, b2ot_variant="resident")
+        return
+    G, lg = ot.bregman.sinkhorn_knopp(at, bt, Mt, 0.1, numItermax=23, stopThr=0, log=True, warn=False,
+                                      b2ot_variant="resident")
+    Gr, lgr = orc.sinkhorn_knopp(a, b, M, 0.1, numItermax=23, stopThr=0, log=True, warn=False)
+    assert lg["niter"] == lgr["niter"] == 22
+    assert_plan(G, Gr, tol)
+    assert_scaling(lg["u"], lgr["u"], tol)
+    assert_scaling(lg["v"], lgr["v"], tol)
+    assert_errs(lg["err"], lgr["err"], dtype)
+    Gs, lgs = ot.bregman.sinkhorn_knopp(at, bt, Mt, 0.1, numItermax=23, stopThr=0, log=True, warn=False,
+                                        b2ot_variant="split")
+    assert_scaling(lg["u"], lgs["u"].cpu().numpy(), 1e-12 if dtype == np.float64 else 1e-5)
+    # the default picks it, and a converging solve stops where the reference stops
+    Gc, lgc = ot.bregman.sinkhorn_knopp(at, bt, Mt, 0.1, numItermax=3000, stopThr=1e-6, log=True, warn=False)
+    Grc, lgrc = orc.sinkhorn_knopp(a, b, M, 0.1, numItermax=3000, stopThr=1e-6, log=True, warn=False)
+    if dtype == np.float64:
+        assert lgc["niter"] == lgrc["niter"]
+    else:
+        assert abs(lgc["niter"] - lgrc["niter"]) <= 10
+    assert len(lgc["err"]) == len(lgrc["err"]) or dtype == np.float32
+
+
+def test_resident_handle_chunks_and_info():
+    """The handle API on the resident path: info reports it, iterate calls of any size continue the same solve (state
+    written back by the kernel), sinkhorn_log refuses the variant."""
+    from pot_b200 import _dense
+    n, m = 500, 640
+    rng = np.random.RandomState(2)
+    K = torch.as_tensor(np.exp(-rng.rand(n, m) / 0.3), device=DEV)
+    a = torch.full((n,), 1.0 / n, dtype=torch.float64, device=DEV)
+    b = torch.full((m,), 1.0 / m, dtype=torch.float64, device=DEV)
+    outs = []
+    for variant, chunks in (("resident", (1, 2, 7, 10, 17)), ("resident", (37,)), ("fused", (37,))):
+        s = _dense.DenseSolver("knopp", K, a, b, None, max_iter=1000, check_every=10, stop_thr=0.0, variant=variant)
+        assert s.info()["variant"] == variant
+        s.init(a.clone(), b.clone())
+        for c in chunks:
+            s.iterate(c)
+        st, it = s.poll()
+        assert st == 0 and it == 37
+        u, v, errs = s.export()
+        outs.append((u, v, errs))
+        s.close()
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])  # chunking changes nothing
+    assert outs[0][2] == outs[1][2] and len(outs[0][2]) == 4
+    np.testing.assert_allclose(outs[0][0].cpu().numpy(), outs[2][0].cpu().numpy(), rtol=1e-12)
+    np.testing.assert_allclose(outs[0][2], outs[2][2], rtol=1e-6, atol=1e-15)
+    s = _dense.DenseSolver("knopp", K, a, b, None, max_iter=1000, check_every=10, stop_thr=0.0)
+    assert s.info()["variant"] == "resident"   # what "auto" resolves to at this size
+    s.close()
+    with pytest.raises(_lib.B2otError, match="resident solver needs"):
+        _dense.DenseSolver("log", K.log(), a.log(), b, b.log(), max_iter=10, check_every=10, stop_thr=0.0, variant="resident")
+
+
 def test_noncontiguous_and_strided_inputs():
     rng = np.random.RandomState(3)
     n, m = 96, 128
@@ -335,7 +412,7 @@ def test_launch_counter_and_variant_info():
     K = torch.rand(256, 512, device=DEV)
     a = torch.full((256,), 1 / 256, device=DEV)
     b = torch.full((512,), 1 / 512, device=DEV)
-    s = _dense.DenseSolver("knopp", K, a, b, None, max_iter=100)
+    s = _dense.DenseSolver("knopp", K, a, b, None, max_iter=100, variant="fused")
     assert s.info()["variant"] == "fused"
     c0 = lib.b2ot_launch_count()
     s.init(a.clone(), b.clone())
@@ -343,4 +420,12 @@ def test_launch_counter_and_variant_info():
     st, it = s.poll()
     assert (st, it) == (0, 10)
     assert lib.b2ot_launch_count() - c0 == 2 + 2 * 10
+    s.close()
+    s = _dense.DenseSolver("knopp", K, a, b, None, max_iter=100)   # small problem: one launch per iterate call
+    assert s.info()["variant"] == "resident"
+    c0 = lib.b2ot_launch_count()
+    s.init(a.clone(), b.clone())
+    s.iterate(10)
+    assert s.poll() == (0, 10)
+    assert lib.b2ot_launch_count() - c0 == 2 + 1
     s.close()

@@ -214,6 +214,18 @@ size_t b2ot_batch_reduce_scratch_bytes(int64_t B, int64_t per);
 int b2ot_batch_reduce(int dtype, int op, const void* A, const void* Bm, int64_t B, int64_t per, double eps,
                       double sign, void* out, void* scratch_dev, void* stream);
 
+/* ---- Gromov-Wasserstein contraction: strided, batched matrix product ----
+ * C[b, f](i, j) = beta * C0[b](i, j) + alpha * sum_{s < Sf} sum_k A[b, f + s](i, k) * B[b, f + s](k, j)
+ * for b < Zb, f < Zf; every operand addressed by ELEMENT strides (batch, feature, row, column; C0 and C have unit
+ * column stride; C0 may be null, and may alias C), so transposes and the interleaved feature axis of (B, n, n, d)
+ * structure tensors need no copies.  Replaces `-nx.dot(nx.dot(hC1, T), hC2.T)` of tensor_product
+ * (ot/gromov/_utils.py:244-280) and the two einsums + feature sum of tensor_product_batch
+ * (ot/batch/_quadratic.py:535-572).  Own register-tiled FMA kernel (gemm_kernels.cuh), deterministic. */
+int b2ot_strided_gemm(int dtype, int64_t Zb, int64_t Zf, int64_t Sf, int64_t M, int64_t N, int64_t K, const void* A,
+                      int64_t sAb, int64_t sAf, int64_t sAi, int64_t sAk, const void* B, int64_t sBb, int64_t sBf,
+                      int64_t sBk, int64_t sBj, const void* C0, int64_t sC0b, int64_t sC0i, void* C, int64_t sCb,
+                      int64_t sCf, int64_t sCi, double alpha, double beta, void* stream);
+
 /* ---- online-cost (empirical) Sinkhorn: cost rebuilt from the point clouds, never materialised ----
  * Replaces the lazy branch of ot.bregman.empirical_sinkhorn (ot/bregman/_empirical.py:193-271): log-domain
  * updates f = log a - LSE_j(g_j - C_ij/reg), g = log b - LSE_i(f_i - C_ij/reg) (f first, :218-233) with

@@ -74,6 +74,9 @@ PROTOTYPES = {
     "b2ot_batch_reduce_scratch_bytes": (C.c_size_t, [C.c_int64, C.c_int64]),
     "b2ot_batch_reduce": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_double,
                                     C.c_double, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b2ot_strided_gemm": (C.c_int, [C.c_int] + [C.c_int64] * 6 + [C.c_void_p] + [C.c_int64] * 4 + [C.c_void_p] +
+                          [C.c_int64] * 4 + [C.c_void_p] + [C.c_int64] * 2 + [C.c_void_p] + [C.c_int64] * 3 +
+                          [C.c_double, C.c_double, C.c_void_p]),
     "b2ot_emp_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "b2ot_emp_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "b2ot_emp_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.c_int64, C.c_int, C.c_void_p,

@@ -9,8 +9,10 @@ Mirrors (same names, argument meaning, return values and errors):
 
 The outer loop (:456-470) is: cost of the current plan `Mk = (1 - alpha) M + 2 alpha L x T`, then a log-domain Bregman
 projection of `K = -Mk/reg + log T` onto the marginals.  The projection is `pot_b200.batch.bregman_log_projection_batch`
-(one thread-block cluster per problem, the whole inner solve in shared memory); the tensor product `L x T` is batched
-GEMM work (`einsum`, :551-562) and goes to cuBLAS through torch, as do the small reductions of the stop test.
+(one thread-block cluster per problem, the whole inner solve in shared memory); the tensor product `L x T` (`einsum`, :551-562) runs on the
+library's own strided, batched matrix-product kernel (`b2ot_strided_gemm`, pot_b200/_gemm.py: the feature axis and the
+transposes are strides, the `const -` and the feature sum are fused); only the one differentiable evaluation of the
+envelope value goes through torch autograd.
 Inputs must be torch CUDA tensors; there is no CPU path.
 """
 
@@ -18,6 +20,7 @@ import warnings
 
 import torch
 
+from . import _gemm
 from .batch import _check3, _weights, bregman_log_projection_batch
 from .utils import OTResult
 
@@ -64,6 +67,10 @@ def tensor_product_batch(L, T, nx=None, recompute_const=False, symmetric=True):
     else:
         const = L["constC"]
     hC1, hC2 = L["hC1"], L["hC2"]
+    if not (torch.is_grad_enabled() and any(t.requires_grad for t in (hC1, hC2, T, const))):
+        # the solver's loop: the library's own strided matrix-product kernel (forward-only; b2ot_strided_gemm)
+        return _gemm.contract_batch(const, hC1, T, hC2, symmetric=symmetric)
+    # differentiable evaluation (the envelope value of solve_gromov_batch, once per solve): torch autograd
     dot = torch.einsum("bijd,bjk->bikd", hC1, T)
     dot = torch.einsum("bikd,bjkd->bijd", dot, hC2)
     dot = torch.sum(dot, dim=-1)

@@ -8,9 +8,10 @@ Mirrors (same names, argument meaning, return values, warnings and errors):
 Every outer iteration (projected gradient or proximal point, :197-244) is a gradient of the GW energy followed by one
 entropic OT solve on it.  The solve is `pot_b200.bregman.sinkhorn_knopp` (Gibbs kernel, fused sweep, device-side
 stopping, plan kernel: libb2ot.so); it is the repeated Sinkhorn consumer this row is about.  The gradient
-`constC - hC1 T hC2^T` (ot/gromov/_utils.py:244-280) is two plain dense GEMMs and goes to cuBLAS through `torch.mm`; the
-rest (`init_matrix`, the `- epsilon log T` term of PPA, the error every 10th outer iteration) is n x m elementwise glue
-on the device.  Inputs must be torch CUDA tensors; there is no CPU path.
+`constC - hC1 T hC2^T` (ot/gromov/_utils.py:244-280) runs on the library's own strided matrix-product kernel
+(`b2ot_strided_gemm`, pot_b200/_gemm.py: two launches, the second fuses the `constC -`); the rest (`init_matrix` - matrix
+times vector and outer products -, the `- epsilon log T` term of PPA, the error every 10th outer iteration) is n x m
+elementwise glue on the device.  Inputs must be torch CUDA tensors; there is no CPU path.
 """
 
 import math
@@ -18,6 +19,7 @@ import warnings
 
 import torch
 
+from . import _gemm
 from .bregman import _require_cuda_matrix, _weights, sinkhorn
 
 __all__ = ["entropic_gromov_wasserstein", "entropic_gromov_wasserstein2"]
@@ -40,9 +42,9 @@ def _init_matrix(C1, C2, p, q, loss_fun):
 
 
 def _tensor_product(constC, hC1, hC2, T):
-    """constC - hC1 T hC2^T (ot/gromov/_utils.py:244-280): two cuBLAS GEMMs."""
-    A = -torch.mm(torch.mm(hC1, T), hC2.t())
-    return constC + A
+    """constC - hC1 T hC2^T (ot/gromov/_utils.py:244-280) on the library's own strided matrix-product kernel
+    (b2ot_strided_gemm, two launches; the second one fuses the `constC -`)."""
+    return _gemm.contract(constC, hC1, T, hC2)
 
 
 def entropic_gromov_wasserstein(C1, C2, p=None, q=None, loss_fun="square_loss", epsilon=0.1, symmetric=None, G0=None,

@@ -9,19 +9,21 @@
 //     when the structures are asymmetric)
 // which were torch.mm / torch.einsum (cuBLAS) until round 2.
 //
-// Register-tiled FMA kernel on the FP32 / FP64 pipes: a block of 256 threads owns a 64 x 64 output tile, a thread a 4 x 4
-// micro-tile; K advances in chunks of 16 through shared memory (the next chunk is fetched into registers while the current
-// one is multiplied).  The global-load mapping of each operand follows its unit stride (coalesced along k or along the
-// row / column, whichever is contiguous).  Fixed summation order: deterministic.  fp64 is what the Gromov solvers run in
-// (parity target 1e-10); the tensor pipe has no fp64 path, and fp32 on tcgen05 with the operand split of
-// emp_tc_kernels.cuh is the listed next step.
+// Register-tiled FMA kernel on the FP32 / FP64 pipes: a block of 256 threads owns a (16 TM) x (16 TN) output tile, a
+// thread a TM x TN micro-tile (fp32: 8 x 8 on a 128 x 128 tile, fp64: 8 x 4 on 128 x 64; micro-tile rows / columns come
+// in groups of four, 64 apart, so the shared-memory reads are conflict-free 16-byte vectors); K advances in chunks of 16
+// through shared memory (the next chunk is fetched into registers while the current one is multiplied).  A first
+// version with 4 x 4 micro-tiles read 8 shared-memory values per 16 FMA and sat at the shared-memory bound (50 % of the
+// FMA peak in fp32, 32 % in fp64: scripts/bench_gemm.py).  The global-load mapping of each operand follows its unit
+// stride (coalesced along k or along the row / column, whichever is contiguous).  Fixed summation order:
+// deterministic.  fp64 is what the Gromov solvers run in (parity target 1e-10); the tensor pipe has no fp64 path, and
+// fp32 on tcgen05 with the operand split of emp_tc_kernels.cuh is the listed next step.
 #pragma once
 
 #include "common.cuh"
 
 namespace b2ot {
 
-constexpr int GM_T = 64;    // output tile edge
 constexpr int GM_K = 16;    // K chunk
 constexpr int GM_PAD = 4;
 
@@ -39,24 +41,31 @@ struct GemmParams {
   double alpha, beta;
 };
 
-template <typename T>
+// offset of micro-tile entry r (0..TX-1) of thread t (0..15) inside a tile edge of 16 * TX: groups of four, 64 apart
+template <int TX>
+__device__ __forceinline__ int gm_off(int t, int r) {
+  return TX == 8 ? ((r >> 2) * 64 + t * 4 + (r & 3)) : (t * TX + r);
+}
+
+template <typename T, int TM, int TN>
 __global__ void __launch_bounds__(256) strided_gemm_kernel(const GemmParams p) {
-  __shared__ T As[GM_K][GM_T + GM_PAD];
-  __shared__ T Bs[GM_K][GM_T + GM_PAD];
+  constexpr int BM = 16 * TM, BN = 16 * TN;
+  __shared__ __align__(16) T As[GM_K][BM + GM_PAD];
+  __shared__ __align__(16) T Bs[GM_K][BN + GM_PAD];
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const long long z = blockIdx.z, b = z / p.Zf, f = z % p.Zf;
-  const long long i0 = (long long)blockIdx.y * GM_T, j0 = (long long)blockIdx.x * GM_T;
-  // global -> register staging: 4 elements of each operand per thread and chunk.  Mapping by contiguity:
+  const long long i0 = (long long)blockIdx.y * BM, j0 = (long long)blockIdx.x * BN;
+  // global -> register staging: TM (TN) elements of A (B) per thread and chunk.  Mapping by contiguity:
   //   A: k fastest across threads when A is contiguous along k (sAk == 1), rows fastest otherwise;
   //   B: columns fastest when B is contiguous along j (sBj == 1), k fastest otherwise.
   const bool a_kfast = (p.sAk == 1) || (p.sAi != 1);
   const bool b_jfast = (p.sBj == 1) || (p.sBk != 1);
-  T ra[4], rb[4];
-  T acc[4][4];
+  T ra[TM], rb[TN];
+  T acc[TM][TN];
 #pragma unroll
-  for (int r = 0; r < 4; ++r)
+  for (int r = 0; r < TM; ++r)
 #pragma unroll
-    for (int c = 0; c < 4; ++c) acc[r][c] = (T)0;
+    for (int c = 0; c < TN; ++c) acc[r][c] = (T)0;
 
   const long long nchunk = (p.K + GM_K - 1) / GM_K;
   const long long steps = p.Sf * nchunk;
@@ -66,23 +75,31 @@ __global__ void __launch_bounds__(256) strided_gemm_kernel(const GemmParams p) {
     const T* Ab = reinterpret_cast<const T*>(p.A) + b * p.sAb + (f + s) * p.sAf;
     const T* Bb = reinterpret_cast<const T*>(p.B) + b * p.sBb + (f + s) * p.sBf;
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int e = tid + q * 256;  // 0..1023
-      const int ak = a_kfast ? (e & 15) : (e >> 6), ai = a_kfast ? (e >> 4) : (e & 63);
+    for (int q = 0; q < TM; ++q) {
+      const int e = tid + q * 256;  // 0 .. 16 BM - 1
+      const int ak = a_kfast ? (e & 15) : (e / BM), ai = a_kfast ? (e >> 4) : (e % BM);
       const long long gi = i0 + ai, gk = k0 + ak;
       ra[q] = (gi < p.M && gk < p.K) ? Ab[gi * p.sAi + gk * p.sAk] : (T)0;
-      const int bk = b_jfast ? (e >> 6) : (e & 15), bj = b_jfast ? (e & 63) : (e >> 4);
-      const long long gj = j0 + bj, gk2 = k0 + bk;
-      rb[q] = (gj < p.N && gk2 < p.K) ? Bb[gk2 * p.sBk + gj * p.sBj] : (T)0;
+    }
+#pragma unroll
+    for (int q = 0; q < TN; ++q) {
+      const int e = tid + q * 256;
+      const int bk = b_jfast ? (e / BN) : (e & 15), bj = b_jfast ? (e % BN) : (e >> 4);
+      const long long gj = j0 + bj, gk = k0 + bk;
+      rb[q] = (gj < p.N && gk < p.K) ? Bb[gk * p.sBk + gj * p.sBj] : (T)0;
     }
   };
   auto stage = [&]() {
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
+    for (int q = 0; q < TM; ++q) {
       const int e = tid + q * 256;
-      const int ak = a_kfast ? (e & 15) : (e >> 6), ai = a_kfast ? (e >> 4) : (e & 63);
+      const int ak = a_kfast ? (e & 15) : (e / BM), ai = a_kfast ? (e >> 4) : (e % BM);
       As[ak][ai] = ra[q];
-      const int bk = b_jfast ? (e >> 6) : (e & 15), bj = b_jfast ? (e & 63) : (e >> 4);
+    }
+#pragma unroll
+    for (int q = 0; q < TN; ++q) {
+      const int e = tid + q * 256;
+      const int bk = b_jfast ? (e / BN) : (e & 15), bj = b_jfast ? (e % BN) : (e >> 4);
       Bs[bk][bj] = rb[q];
     }
   };
@@ -95,15 +112,15 @@ __global__ void __launch_bounds__(256) strided_gemm_kernel(const GemmParams p) {
     if (step + 1 < steps) fetch(step + 1);
 #pragma unroll
     for (int kk = 0; kk < GM_K; ++kk) {
-      T a[4], bb[4];
+      T a[TM], bb[TN];
 #pragma unroll
-      for (int r = 0; r < 4; ++r) a[r] = As[kk][ty * 4 + r];
+      for (int r = 0; r < TM; ++r) a[r] = As[kk][gm_off<TM>(ty, r)];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) bb[c] = Bs[kk][tx * 4 + c];
+      for (int c = 0; c < TN; ++c) bb[c] = Bs[kk][gm_off<TN>(tx, c)];
 #pragma unroll
-      for (int r = 0; r < 4; ++r)
+      for (int r = 0; r < TM; ++r)
 #pragma unroll
-        for (int c = 0; c < 4; ++c) acc[r][c] += a[r] * bb[c];
+        for (int c = 0; c < TN; ++c) acc[r][c] += a[r] * bb[c];
     }
   }
 
@@ -111,12 +128,12 @@ __global__ void __launch_bounds__(256) strided_gemm_kernel(const GemmParams p) {
   T* Cb = reinterpret_cast<T*>(p.C) + b * p.sCb + f * p.sCf;
   const T* C0b = p.C0 != nullptr ? reinterpret_cast<const T*>(p.C0) + b * p.sC0b : nullptr;
 #pragma unroll
-  for (int r = 0; r < 4; ++r) {
-    const long long gi = i0 + ty * 4 + r;
+  for (int r = 0; r < TM; ++r) {
+    const long long gi = i0 + gm_off<TM>(ty, r);
     if (gi >= p.M) continue;
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      const long long gj = j0 + tx * 4 + c;
+    for (int c = 0; c < TN; ++c) {
+      const long long gj = j0 + gm_off<TN>(tx, c);
       if (gj >= p.N) continue;
       T v = alpha * acc[r][c];
       if (C0b != nullptr) v += beta * C0b[gi * p.sC0i + gj];

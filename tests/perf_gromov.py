@@ -1,6 +1,6 @@
 """entropic_gromov_wasserstein (PGD, square loss) on one B200 next to the numpy oracle on the host cores:
 n = m = N points, `outer` projected-gradient iterations of `inner` fixed Sinkhorn iterations each (fp64).
-The GPU call is the public pot_b200.gromov entry (inner solves in libb2ot.so, the two gradient GEMMs in cuBLAS).
+The GPU call is the public pot_b200.gromov entry (inner solves in libb2ot.so, the two gradient products on b2ot_strided_gemm).
 Prints one JSON line."""
 import json
 import os

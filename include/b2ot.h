@@ -46,6 +46,8 @@ extern "C" {
 
 /* ---- library ---- */
 int b2ot_version(void);
+/* "src=<first 16 hex digits of sha256 over pot_b200/csrc sources + headers, Makefile order> built=<date time>" */
+const char* b2ot_build_info(void);
 const char* b2ot_last_error(void);
 int b2ot_device_info(int device, int* sm_count, int* cc_major, int* cc_minor);
 /* number of kernels this library has launched in this process (bench.py's "gpu_launches") */

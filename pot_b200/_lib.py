@@ -24,6 +24,7 @@ ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c
 # name -> (restype, argtypes); every symbol include/b2ot.h declares
 PROTOTYPES = {
     "b2ot_version": (C.c_int, []),
+    "b2ot_build_info": (C.c_char_p, []),
     "b2ot_last_error": (C.c_char_p, []),
     "b2ot_device_info": (C.c_int, [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "b2ot_launch_count": (C.c_ulonglong, []),
@@ -153,3 +154,23 @@ def check(rc, what=""):
     if rc != 0:
         msg = load().b2ot_last_error()
         raise B2otError(f"{what} failed (code {rc}): {msg.decode() if msg else '?'}")
+
+
+def source_hash():
+    """sha256 prefix over the kernel sources in the tree, in the Makefile's order (what b2ot_build_info() reports as src=)."""
+    import hashlib
+    import re
+
+    d = os.path.join(_HERE, "csrc")
+    mk = open(os.path.join(d, "Makefile")).read()
+    names = re.search(r"^SRCS\s*:=\s*(.*)$", mk, re.M).group(1).split() + re.search(r"^HDRS\s*:=\s*(.*)$", mk, re.M).group(1).split()
+    h = hashlib.sha256()
+    for n in names:
+        with open(os.path.join(d, n), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:16]
+
+
+def build_matches_sources():
+    info = load().b2ot_build_info().decode()
+    return ("src=" + source_hash()) in info, info

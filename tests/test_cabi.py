@@ -40,6 +40,9 @@ def test_every_declared_symbol_is_exported(lib):
 
 def test_version_and_error_reporting(lib):
     assert lib.b2ot_version() >= 100
+    from pot_b200 import _lib
+    ok, info = _lib.build_matches_sources()
+    assert ok, f"stale library: {info}, sources hash {_lib.source_hash()}"
     h = ctypes.c_void_p()
     rc = lib.b2ot_dense_create(ctypes.byref(h), 7, 0, 4, 4, 4, None, None, None, None, None, 0, 10, 10, 0.0, 0, None)
     assert rc < 0

@@ -79,7 +79,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n", type=int, default=None, help="problem size (n = m; config 5: number of problems)")
-    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+    ap.add_argument("--exchange", default="peer", choices=["peer", "peer_ll", "nccl"],
                     help="N > 1: per-iteration exchange (peer = fused NVLink peer-memory exchange, "
                          "nccl = torch.distributed all-reduce baseline)")
     ap.add_argument("--operand", default="f16", choices=["f16", "tf32"],
@@ -352,7 +352,7 @@ class Ctx:
         stream, so no rank's ev0 is recorded (on the device) before every rank has reached this point."""
         if self.world == 1:
             return
-        if self.args.exchange == "peer":
+        if self.args.exchange in ("peer", "peer_ll"):
             from pot_b200.comm import get_comm
 
             if self._align is None:

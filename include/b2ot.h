@@ -314,6 +314,10 @@ size_t b2ot_comm_slot_bytes(const b2ot_comm* comm);
 int b2ot_comm_allreduce(b2ot_comm* comm, void* buf_dev, int64_t count, int dtype, int op, void* stream);
 /* attach to a solver handle (replaces the all-reduce hook); the communicator must outlive the handle */
 int b2ot_dense_set_comm(b2ot_dense* handle, b2ot_comm* comm);
+/* on = 1: the per-iteration column sums travel as tagged 8-byte words {value bits, sequence} stored straight into the
+ * peers' slots and polled inside the finalize kernel (no put kernel, no flags, no system-scope fences); needs
+ * slot_bytes >= roundup64(8 (m + 1)) + 2 (m + 1) sizeof(dtype).  Default off (put kernel + sequence flags). */
+int b2ot_dense_set_comm_ll(b2ot_dense* h, int on);
 int b2ot_emp_set_comm(b2ot_emp* handle, b2ot_comm* comm);
 
 #ifdef __cplusplus

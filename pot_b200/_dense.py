@@ -72,15 +72,22 @@ class DenseSolver:
         self._cb = None
         self.comm = None
         if group is not None:
-            if exchange == "peer":  # NVLink peer-memory exchange fused into the put / finalize kernels
+            if exchange in ("peer", "peer_ll"):
+                # NVLink peer-memory exchange.  "peer": put kernel + sequence flags, the finalize kernel is the take
+                # (csrc/comm.cuh).  "peer_ll": slots with room for the tagged-word region - the column sums then travel
+                # as {value, sequence} words inside the finalize kernel, no put kernel, no flags (b2ot_dense_set_comm
+                # decides by slot size).  Measured equal on 2 and 8 GPUs (profiles/r02ll_exchange_ab.md), so the protocol
+                # with two rounds of multi-GPU runs behind it stays the default.
                 from .comm import get_comm
 
-                self.comm = get_comm(group, self.device, (self.m + 1) * 8)
+                self.comm = get_comm(group, self.device, (self.m + 1) * (24 if exchange == "peer_ll" else 8) + 128)
                 _lib.check(self.lib.b2ot_dense_set_comm(self.h, self.comm.h), "b2ot_dense_set_comm")
+                if exchange == "peer_ll":
+                    _lib.check(self.lib.b2ot_dense_set_comm_ll(self.h, 1), "b2ot_dense_set_comm_ll")
             elif exchange == "nccl":  # baseline: one NCCL all-reduce per iteration through torch.distributed
                 self._install_allreduce(group)
             else:
-                raise ValueError(f"unknown exchange {exchange!r} (peer | nccl)")
+                raise ValueError(f"unknown exchange {exchange!r} (peer | peer_ll | nccl)")
 
     # ---- baseline exchange: the per-iteration column-sum all-reduce goes through torch.distributed ----
     def _install_allreduce(self, group):

@@ -112,6 +112,7 @@ PROTOTYPES = {
     "b2ot_comm_slot_bytes": (C.c_size_t, [C.c_void_p]),
     "b2ot_comm_allreduce": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p]),
     "b2ot_dense_set_comm": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "b2ot_dense_set_comm_ll": (C.c_int, [C.c_void_p, C.c_int]),
     "b2ot_emp_set_comm": (C.c_int, [C.c_void_p, C.c_void_p]),
 }
 

@@ -75,6 +75,77 @@ __device__ __forceinline__ bool comm_wait(const CommView& c, unsigned long long 
   return s_ok != 0;
 }
 
+// ---- tagged-word exchange (the dense solver's finalize kernel, dense_kernels.cuh) ----
+// A value travels as 8-byte words {32 data bits, 32-bit sequence tag} (fp32: one word, fp64: two), stored straight into
+// the peers' slots with single 8-byte stores (single-copy atomic, also over NVLink - the NCCL LL idea) and polled by the
+// consumer until the tag equals the sequence number: no flag word, no system-scope fence, no block ticket on the hot path.
+// The words live in their own region of a slot (offset ll_off), so the flag protocol above can share the buffer.
+__device__ __forceinline__ void llw_store(unsigned long long* p, unsigned int bits, unsigned int tag) {
+  asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(bits), "r"(tag) : "memory");
+}
+__device__ __forceinline__ bool llw_poll(const unsigned long long* p, unsigned int tag, unsigned int& bits) {
+  unsigned int t;
+  asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(bits), "=r"(t) : "l"(p) : "memory");
+  return t == tag;
+}
+template <typename T> struct LLWords;
+template <> struct LLWords<float> {
+  static constexpr int N = 1;
+  static __device__ __forceinline__ void put(unsigned long long* base, long long i, float x, unsigned int tag) {
+    llw_store(base + i, __float_as_uint(x), tag);
+  }
+  static __device__ __forceinline__ bool poll(const unsigned long long* base, long long i, unsigned int tag, float& x) {
+    unsigned int b;
+    const bool ok = llw_poll(base + i, tag, b);
+    x = __uint_as_float(b);
+    return ok;
+  }
+};
+template <> struct LLWords<double> {
+  static constexpr int N = 2;
+  static __device__ __forceinline__ void put(unsigned long long* base, long long i, double x, unsigned int tag) {
+    const unsigned long long b = (unsigned long long)__double_as_longlong(x);
+    llw_store(base + 2 * i, (unsigned int)b, tag);
+    llw_store(base + 2 * i + 1, (unsigned int)(b >> 32), tag);
+  }
+  static __device__ __forceinline__ bool poll(const unsigned long long* base, long long i, unsigned int tag, double& x) {
+    unsigned int lo, hi;
+    const bool ok0 = llw_poll(base + 2 * i, tag, lo);
+    const bool ok1 = llw_poll(base + 2 * i + 1, tag, hi);
+    x = __longlong_as_double((long long)(((unsigned long long)hi << 32) | lo));
+    return ok0 && ok1;
+  }
+};
+__device__ __forceinline__ unsigned long long* comm_ll_slot(const CommView& c, int owner, int parity, int src_rank,
+                                                            unsigned long long ll_off) {
+  return reinterpret_cast<unsigned long long*>(c.data[owner] + (size_t)(parity * c.nranks + src_rank) * c.slot_bytes + ll_off);
+}
+// value of element i from every rank, summed in rank order (identical on all ranks); false on timeout (20 s)
+template <typename T>
+__device__ __forceinline__ bool comm_ll_take(const CommView& c, int parity, unsigned long long ll_off, long long i,
+                                             unsigned int tag, T& total) {
+  T x[COMM_MAX_RANKS];
+  unsigned int done = 0;
+  const unsigned int all = (1u << c.nranks) - 1u;
+  unsigned long long t0 = 0;
+  for (unsigned int spins = 0; done != all; ++spins) {
+#pragma unroll
+    for (int q = 0; q < COMM_MAX_RANKS; ++q)
+      if (q < c.nranks && !(done & (1u << q)) && LLWords<T>::poll(comm_ll_slot(c, c.rank, parity, q, ll_off), i, tag, x[q]))
+        done |= 1u << q;
+    if ((spins & 0x3FFFu) == 0x3FFFu) {
+      const unsigned long long now = global_timer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 20000000000ull) return false;
+    }
+  }
+  total = x[0];
+#pragma unroll
+  for (int q = 1; q < COMM_MAX_RANKS; ++q)
+    if (q < c.nranks) total += x[q];
+  return true;
+}
+
 // put: dst_q[j] = sum over nsrc local rows of src[row * ld + j] for j < count; optional extra element at index
 // `count` carrying (*flag_src != 0).  The DATA is written only while *status == expect_status (status may be null);
 // the FLAG of `seq` is published in every case: the two-parity reuse argument in the header needs every sequence

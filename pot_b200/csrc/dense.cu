@@ -108,6 +108,8 @@ struct b2ot_dense {
   b2ot_allreduce_fn ar;
   void* ar_ctx;
   b2ot_comm* comm;  // NVLink peer-memory exchange (takes precedence over the hook)
+  int comm_ll;      // 1: the column sums travel as tagged words inside the finalize kernel (slots large enough)
+  unsigned long long comm_ll_off;  // byte offset of the tagged-word region inside a slot
   SolveState* h_state;  // pinned host mirror for polls
   cudaGraphExec_t gexec;  // graph of kGraphIters iterations (single-device solves), built at the first iterate call
   int graph_state;        // 0 not built, 1 ready, -1 unavailable
@@ -779,6 +781,26 @@ extern "C" int b2ot_dense_set_comm(b2ot_dense* h, b2ot_comm* comm) {
                  comm->view.slot_bytes, need);
   }
   h->comm = comm;
+  h->comm_ll = 0;
+  return 0;
+}
+
+// Tagged-word exchange (comm.cuh) instead of put kernel + flags: the column sums travel as {value, sequence} words
+// inside the finalize kernel.  Needs slots with room for the word region behind the plain one:
+// slot_bytes >= roundup64(8 (m + 1)) + 2 (m + 1) sizeof(T).
+extern "C" int b2ot_dense_set_comm_ll(b2ot_dense* h, int on) {
+  B2OT_REQUIRE(h != nullptr, "b2ot_dense_set_comm_ll: null handle");
+  if (!on) {
+    h->comm_ll = 0;
+    return 0;
+  }
+  B2OT_REQUIRE(h->comm != nullptr, "b2ot_dense_set_comm_ll: no communicator set");
+  const size_t off = ((size_t)(h->m + 1) * 8 + 63) / 64 * 64;
+  const size_t need_ll = off + (size_t)(h->m + 1) * 2 * esize(h->dtype);
+  B2OT_REQUIRE(h->comm->view.slot_bytes >= need_ll, "b2ot_dense_set_comm_ll: exchange slots hold %llu bytes, %zu needed",
+               h->comm->view.slot_bytes, need_ll);
+  h->comm_ll = 1;
+  h->comm_ll_off = off;
   return 0;
 }
 
@@ -870,6 +892,18 @@ static int launch_finalize(const b2ot_dense* h, int nsrc, int init, int gate_reb
     // kernel below is the "take" (waits on the flags, sums the slots in rank order)
     b2ot_comm* c = h->comm;
     const unsigned long long seq = ++c->seq;
+    if (h->comm_ll && !(h->tau > 0.0)) {
+      // tagged-word exchange inside the finalize kernel: no put kernel, no flags (comm.cuh, dense_kernels.cuh)
+      p.use_comm = 2;
+      p.seq = seq;
+      p.comm = c->view;
+      p.lsrc = h->partials;
+      p.lsrc_ld = h->mp;
+      p.lnsrc = nsrc;
+      p.uflag_src = &h->st->uflag;
+      p.ll_off = h->comm_ll_off;
+      p.nsrc = c->view.nranks;
+    } else {
     // one 16-byte column vector per thread (comm_put_kernel): 64 blocks at m = 65536 fp32
     const long long vn = 16 / (long long)sizeof(T);
     const unsigned g = (unsigned)std::max<long long>(1, std::min<long long>((h->m / vn + 1 + 255) / 256, 148));
@@ -886,6 +920,7 @@ static int launch_finalize(const b2ot_dense* h, int nsrc, int init, int gate_reb
     p.use_comm = 1;
     p.seq = seq;
     p.comm = c->view;
+    }
   } else if (multi) {
     const unsigned g = (unsigned)((h->m + 1 + 255) / 256);
     reduce_partials_kernel<T><<<g, 256, 0, h->stream>>>(h->partials, h->mp, nsrc, h->cbuf, h->m, h->st, ST_RUNNING);
@@ -933,6 +968,10 @@ static int launch_finalize(const b2ot_dense* h, int nsrc, int init, int gate_reb
   }
   if (h->mode == B2OT_MODE_KNOPP && h->tau > 0.0)
     B2OT_CUDA(launch_pdl(finalize_kernel<T, MODE_KNOPP, true>, dim3(blocks), dim3(256), 0, h->stream, p));
+  else if (p.use_comm == 2 && h->mode == B2OT_MODE_KNOPP)
+    B2OT_CUDA(launch_pdl(finalize_ll_kernel<T, MODE_KNOPP>, dim3(blocks), dim3(256), 0, h->stream, p));
+  else if (p.use_comm == 2)
+    B2OT_CUDA(launch_pdl(finalize_ll_kernel<T, MODE_LOG>, dim3(blocks), dim3(256), 0, h->stream, p));
   else if (h->mode == B2OT_MODE_KNOPP)
     B2OT_CUDA(launch_pdl(finalize_kernel<T, MODE_KNOPP>, dim3(blocks), dim3(256), 0, h->stream, p));
   else

@@ -665,8 +665,15 @@ struct FinParams {
   long long extra_flag_ld; // ... flag_n values, extra_flag_ld elements apart
   int extra_flag_n;
   int use_comm;            // 1: `src` are the peer-exchange slots of sequence `seq`: wait for all ranks first
+                           // 2: tagged-word exchange INSIDE this kernel (comm.cuh): this rank's partial rows `lsrc` are
+                           //    reduced and stored to every peer, then every column is taken from the R slots
   unsigned long long seq;
   CommView comm;
+  const void* lsrc;        // use_comm == 2: local partial rows (lnsrc rows, stride lsrc_ld)
+  long long lsrc_ld;
+  int lnsrc;
+  const int* uflag_src;    // use_comm == 2: "this rank produced a non-finite u" (travels as element m)
+  unsigned long long ll_off;  // byte offset of the tagged-word region inside a slot
   const void* b;
   const void* logb;
   void* vring;
@@ -695,8 +702,10 @@ struct FinParams {
 // balanced headline runs exactly at the register limit where TWO resident finalize blocks (32 registers) and the
 // programmatically launched next sweep CTA (192) share an SM: 40 registers pushed the sweep's early start behind the
 // finalize blocks' exit, +30 us per 2.7 ms iteration at 65536^2 (profiles/r01c_ab_finalize_stabilized.jsonl).
-template <typename T, int MODE, bool STAB = false>
-__global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
+// LL: the tagged-word exchange (use_comm == 2) is its own instantiation for the same reason (79 registers with the
+// polling loops in; capped at 48 so that a finalize block and the early-started sweep CTA still share an SM).
+template <typename T, int MODE, bool STAB, bool LL>
+__device__ __forceinline__ void finalize_body(const FinParams& p) {
   __shared__ double sred[256];
   __shared__ int sflags;
   __shared__ int s_last;
@@ -707,7 +716,36 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
   const int tid = threadIdx.x;
   // fused "take" of the NVLink exchange.  The wait is NOT gated on the solver status: every sequence number is
   // waited for (comm.cuh), also by the no-op iterations enqueued after the solve stopped -- except after a timeout.
-  if (p.use_comm && status_in != ST_COMM_TIMEOUT && !comm_wait(p.comm, p.seq)) {
+  __shared__ int s_tmo;
+  const unsigned int tag = (unsigned int)p.seq;
+  const int par = (int)(p.seq & 1ull);
+  if (LL && p.use_comm == 2) {
+    // Tagged-word exchange, put side: reduce the local partial rows of every column (and the u flag as element m) and
+    // store the words into this rank's slot on every peer.  NOT gated on the solver status: every sequence number is
+    // sent and taken by every rank (comm.cuh), a stopped solver sends zeros.
+    if (tid == 0) s_tmo = 0;
+    const T* lsrc = reinterpret_cast<const T*>(p.lsrc);
+    for (long long j = (long long)blockIdx.x * 256 + tid; j <= p.m; j += (long long)gridDim.x * 256) {
+      T c = (T)0;
+      if (status_in == ST_RUNNING) {
+        if (j < p.m)
+          for (int q = 0; q < p.lnsrc; ++q) c += __ldcg(&lsrc[(long long)q * p.lsrc_ld + j]);
+        else
+          c = (T)(atomicOr(const_cast<int*>(p.uflag_src), 0) ? 1 : 0);
+      }
+      for (int r = 0; r < p.comm.nranks; ++r)
+        LLWords<T>::put(comm_ll_slot(p.comm, r, par, p.comm.rank, p.ll_off), j, c, tag);
+    }
+    if (status_in != ST_RUNNING) {  // consume the peers' words of this sequence number all the same
+      if (status_in != ST_COMM_TIMEOUT)
+        for (long long j = (long long)blockIdx.x * 256 + tid; j <= p.m; j += (long long)gridDim.x * 256) {
+          T c;
+          if (!comm_ll_take<T>(p.comm, par, p.ll_off, j, tag, c)) break;
+        }
+      return;
+    }
+    __syncthreads();
+  } else if (p.use_comm && status_in != ST_COMM_TIMEOUT && !comm_wait(p.comm, p.seq)) {
     if (tid == 0) st->status = ST_COMM_TIMEOUT;
     return;
   }
@@ -760,7 +798,21 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
     cbuf[j] = c;
     vnext[j] = vn;
   };
-  if (!p.qsplit) {
+  if (LL && p.use_comm == 2) {
+    for (long long j = (long long)blockIdx.x * 256 + tid; j < p.m; j += (long long)gridDim.x * 256) {
+      T c;
+      if (!comm_ll_take<T>(p.comm, par, p.ll_off, j, tag, c)) {
+        s_tmo = 1;
+        break;
+      }
+      column(j, c);
+    }
+    __syncthreads();
+    if (s_tmo) {
+      if (tid == 0) st->status = ST_COMM_TIMEOUT;
+      return;
+    }
+  } else if (!p.qsplit) {
     for (long long j = (long long)blockIdx.x * 256 + tid; j < p.m; j += (long long)gridDim.x * 256) {
       T c = (T)0;
       for (int q = 0; q < p.nsrc; ++q) c += __ldcg(&src[(long long)q * p.src_ld + j]);
@@ -848,7 +900,14 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
   const int nflags = atomicOr(&st->next_flags, 0);
   const int nexact = atomicOr(&st->need_exact, 0);
   int uflag = atomicOr(&st->uflag, 0);
-  if (p.extra_flag != nullptr) {
+  if (LL && p.use_comm == 2) {  // element m of the exchange: some rank produced a non-finite u
+    T fsum;
+    if (!comm_ll_take<T>(p.comm, par, p.ll_off, p.m, tag, fsum)) {
+      st->status = ST_COMM_TIMEOUT;
+      return;
+    }
+    if (fsum != (T)0) uflag = 1;
+  } else if (p.extra_flag != nullptr) {
     for (int q = 0; q < p.extra_flag_n; ++q)
       if (__ldcg(reinterpret_cast<const T*>(p.extra_flag) + (long long)q * p.extra_flag_ld) != (T)0) uflag = 1;
   }
@@ -903,6 +962,15 @@ __global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
   st->absorb = 0;
   st->ticket = 0;
   __threadfence();
+}
+
+template <typename T, int MODE, bool STAB = false>
+__global__ void __launch_bounds__(256) finalize_kernel(const FinParams p) {
+  finalize_body<T, MODE, STAB, false>(p);
+}
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256, 5) finalize_ll_kernel(const FinParams p) {
+  finalize_body<T, MODE, false, true>(p);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -167,7 +167,7 @@ class EmpiricalSolver:
         _lib.check(self.lib.b2ot_emp_set_operand(self.h, op), "b2ot_emp_set_operand")
         self.operand = operand
         if group is not None:
-            if exchange == "peer":
+            if exchange in ("peer", "peer_ll"):
                 from .comm import get_comm
 
                 self.comm = get_comm(group, self.device, (self.m + 1) * 8)

@@ -17,6 +17,8 @@ a = torch.full((n,), 1.0 / n, device=dev)
 b = torch.full((m,), 1.0 / m, device=dev)
 KNOBS = [{}, {"B2OT_OCC": "2"}, {"B2OT_WARPS": "16"}, {"B2OT_CLUSTERS": "14"}, {"B2OT_CLUSTERS": "12"},
          {"B2OT_L2_HINT": "0"}, {"B2OT_STAGES": "2"}, {}]
+if os.environ.get("DEFAULT_ONLY"):
+    KNOBS = [{}]
 peak = 6535.1
 for kn in KNOBS:
     for k in ("B2OT_OCC", "B2OT_WARPS", "B2OT_CLUSTERS", "B2OT_L2_HINT", "B2OT_STAGES"):

@@ -3,7 +3,7 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node R --master-addr 127.0.0.1 --master-port P \
         tests/mgpu_worker.py
 
-Every rank checks its own results and exits non-zero on a mismatch.  Checks (exchange = peer and nccl):
+Every rank checks its own results and exits non-zero on a mismatch.  Checks (exchange = peer, peer_ll (tagged words) and nccl):
   1. the stand-alone peer all-reduce against torch.distributed (sum / max, fp32 / fp64, 300 back-to-back calls);
   2. row-sharded sinkhorn_knopp / sinkhorn_log against the CPU oracle (fp64 1e-10, fp32 1e-4) and against the
      single-GPU solve (same niter, same err history), converged and fixed-iteration runs, ragged row split;
@@ -86,7 +86,7 @@ def main():
     b64 = rng.rand(m) + 0.5
     b64 /= b64.sum()
     r0, r1 = shard_rows(n, world, rank)
-    for exchange in ("peer", "nccl"):
+    for exchange in ("peer", "peer_ll", "nccl"):
         for dtype, tol in ((np.float64, 1e-10), (np.float32, 1e-4)):
             M, a, b = M64.astype(dtype), a64.astype(dtype), b64.astype(dtype)
             Ml, al, bd = (torch.as_tensor(M[r0:r1], device=dev), torch.as_tensor(a[r0:r1], device=dev),
@@ -125,7 +125,8 @@ def main():
             kw = dict(numItermax=400, stopThr=1e-4) if cycle % 2 == 0 else dict(numItermax=7 + cycle % 5, stopThr=0.0)
             with warnings.catch_warnings():
                 warnings.simplefilter("ignore")
-                G, lg = fn(al, bd, Ml, 0.1, log=True, group=group, n_total=n, exchange="peer", **kw)
+                G, lg = fn(al, bd, Ml, 0.1, log=True, group=group, n_total=n,
+                           exchange="peer" if (cycle // 2) % 2 == 0 else "peer_ll", **kw)  # both protocols share the slots
             key = (name, cycle % 2, kw["numItermax"])
             if key not in first:
                 first[key] = (G.clone(), lg["niter"])

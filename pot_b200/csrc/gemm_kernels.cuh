@@ -58,8 +58,24 @@ __global__ void __launch_bounds__(256) strided_gemm_kernel(const GemmParams p) {
   // global -> register staging: TM (TN) elements of A (B) per thread and chunk.  Mapping by contiguity:
   //   A: k fastest across threads when A is contiguous along k (sAk == 1), rows fastest otherwise;
   //   B: columns fastest when B is contiguous along j (sBj == 1), k fastest otherwise.
+  // Element q of a thread is element q = 0 plus q times a fixed (k, row) step, so a thread keeps ONE pointer per operand
+  // that advances by a chunk, a row / column validity mask, and checks k only in the last chunk of a feature (the
+  // per-element index arithmetic and bounds checks of the first version were as many instructions as the FMAs).
   const bool a_kfast = (p.sAk == 1) || (p.sAi != 1);
   const bool b_jfast = (p.sBj == 1) || (p.sBk != 1);
+  const int a_k0 = a_kfast ? (tid & 15) : (tid / BM), a_i0 = a_kfast ? (tid >> 4) : (tid % BM);
+  const int a_dk = a_kfast ? 0 : 256 / BM, a_di = a_kfast ? 16 : 0;
+  const int b_k0 = b_jfast ? (tid / BN) : (tid & 15), b_j0 = b_jfast ? (tid % BN) : (tid >> 4);
+  const int b_dk = b_jfast ? 256 / BN : 0, b_dj = b_jfast ? 0 : 16;
+  const long long a_qs = (long long)a_dk * p.sAk + (long long)a_di * p.sAi;
+  const long long b_qs = (long long)b_dk * p.sBk + (long long)b_dj * p.sBj;
+  unsigned a_ok = 0, b_ok = 0;
+#pragma unroll
+  for (int q = 0; q < TM; ++q) a_ok |= (i0 + a_i0 + q * a_di < p.M) ? (1u << q) : 0u;
+#pragma unroll
+  for (int q = 0; q < TN; ++q) b_ok |= (j0 + b_j0 + q * b_dj < p.N) ? (1u << q) : 0u;
+  const T* a_base = reinterpret_cast<const T*>(p.A) + b * p.sAb + f * p.sAf + (i0 + a_i0) * p.sAi + (long long)a_k0 * p.sAk;
+  const T* b_base = reinterpret_cast<const T*>(p.B) + b * p.sBb + f * p.sBf + (j0 + b_j0) * p.sBj + (long long)b_k0 * p.sBk;
   T ra[TM], rb[TN];
   T acc[TM][TN];
 #pragma unroll
@@ -72,36 +88,25 @@ __global__ void __launch_bounds__(256) strided_gemm_kernel(const GemmParams p) {
 
   auto fetch = [&](long long step) {
     const long long s = step / nchunk, k0 = (step % nchunk) * GM_K;
-    const T* Ab = reinterpret_cast<const T*>(p.A) + b * p.sAb + (f + s) * p.sAf;
-    const T* Bb = reinterpret_cast<const T*>(p.B) + b * p.sBb + (f + s) * p.sBf;
+    const T* ap = a_base + s * p.sAf + k0 * p.sAk;
+    const T* bp = b_base + s * p.sBf + k0 * p.sBk;
+    if (k0 + GM_K <= p.K) {
 #pragma unroll
-    for (int q = 0; q < TM; ++q) {
-      const int e = tid + q * 256;  // 0 .. 16 BM - 1
-      const int ak = a_kfast ? (e & 15) : (e / BM), ai = a_kfast ? (e >> 4) : (e % BM);
-      const long long gi = i0 + ai, gk = k0 + ak;
-      ra[q] = (gi < p.M && gk < p.K) ? Ab[gi * p.sAi + gk * p.sAk] : (T)0;
-    }
+      for (int q = 0; q < TM; ++q) ra[q] = (a_ok >> q & 1u) ? ap[q * a_qs] : (T)0;
 #pragma unroll
-    for (int q = 0; q < TN; ++q) {
-      const int e = tid + q * 256;
-      const int bk = b_jfast ? (e / BN) : (e & 15), bj = b_jfast ? (e % BN) : (e >> 4);
-      const long long gj = j0 + bj, gk = k0 + bk;
-      rb[q] = (gj < p.N && gk < p.K) ? Bb[gk * p.sBk + gj * p.sBj] : (T)0;
+      for (int q = 0; q < TN; ++q) rb[q] = (b_ok >> q & 1u) ? bp[q * b_qs] : (T)0;
+    } else {
+#pragma unroll
+      for (int q = 0; q < TM; ++q) ra[q] = ((a_ok >> q & 1u) && k0 + a_k0 + q * a_dk < p.K) ? ap[q * a_qs] : (T)0;
+#pragma unroll
+      for (int q = 0; q < TN; ++q) rb[q] = ((b_ok >> q & 1u) && k0 + b_k0 + q * b_dk < p.K) ? bp[q * b_qs] : (T)0;
     }
   };
   auto stage = [&]() {
 #pragma unroll
-    for (int q = 0; q < TM; ++q) {
-      const int e = tid + q * 256;
-      const int ak = a_kfast ? (e & 15) : (e / BM), ai = a_kfast ? (e >> 4) : (e % BM);
-      As[ak][ai] = ra[q];
-    }
+    for (int q = 0; q < TM; ++q) As[a_k0 + q * a_dk][a_i0 + q * a_di] = ra[q];
 #pragma unroll
-    for (int q = 0; q < TN; ++q) {
-      const int e = tid + q * 256;
-      const int bk = b_jfast ? (e / BN) : (e & 15), bj = b_jfast ? (e % BN) : (e >> 4);
-      Bs[bk][bj] = rb[q];
-    }
+    for (int q = 0; q < TN; ++q) Bs[b_k0 + q * b_dk][b_j0 + q * b_dj] = rb[q];
   };
 
   if (steps > 0) fetch(0);

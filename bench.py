@@ -531,7 +531,7 @@ def bench_dense(ctx, cfg):
     kern = {1: "fused_sweep_kernel<double, knopp>", 2: "log_pp_sweep_kernel (fp32 log-domain ping-pong sweep)",
             3: "fused_sweep_kernel<float, 8, knopp>"}[cfg]
     if info.get("variant") == "resident":
-        kern = ("resident_knopp_kernel<%s> (K in the grid's shared memory, one cooperative launch per chunk of iterations; "
+        kern = ("resident_solve_kernel<%s, knopp> (K in the grid's shared memory, one cooperative launch per chunk of iterations; "
                 "launch_ms = per iteration)" % ("double" if cfg == 1 else "float"))
     roof = {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
             "traffic": traffic_from_profiles(f"{mode}_{DTYPE[cfg]}_{nloc}x{m}"), "kernel": kern,

@@ -573,18 +573,22 @@ static bool plan_fused(b2ot_dense* h) {
   return true;
 }
 
+static const void* resident_fn(const b2ot_dense* h) {
+  if (h->mode == B2OT_MODE_KNOPP)
+    return h->dtype == B2OT_F32 ? (const void*)resident_solve_kernel<float, MODE_KNOPP> : (const void*)resident_solve_kernel<double, MODE_KNOPP>;
+  return h->dtype == B2OT_F32 ? (const void*)resident_solve_kernel<float, MODE_LOG> : (const void*)resident_solve_kernel<double, MODE_LOG>;
+}
 // Resident solver: eligible when the grid's shared memory holds K twice (a block of rows and a block of columns per
 // CTA, at most one CTA per SM).  Scaling domain only.
 static bool plan_resident(b2ot_dense* h, int sm_count) {
   h->res_ok = 0;
-  if (h->mode != B2OT_MODE_KNOPP) return false;
   if (const char* e = diag_env("B2OT_RESIDENT"))
     if (e[0] == '0') return false;
   if (sm_count > RES_MAXG) sm_count = RES_MAXG;
   const long long grid = std::min<long long>(sm_count, std::max(h->n, h->m));
   const long long rows = (h->n + grid - 1) / grid, cols = (h->m + grid - 1) / grid;
   const size_t sz = esize(h->dtype);
-  const size_t smem = ((size_t)rows * h->m + (size_t)cols * h->n + 2 * h->m + h->n + 2 * (rows + cols) + 64) * sz + 64;
+  const size_t smem = ((size_t)rows * h->m + (size_t)cols * h->n + 2 * h->m + h->n + 3 * (rows + cols) + 72) * sz + 64;
   if (smem > 200 * 1024) return false;
   // the exchange words live in the partial-sum scratch of the streaming solver (unused on this path): as many copies
   // as fit, at most 8
@@ -597,7 +601,7 @@ static bool plan_resident(b2ot_dense* h, int sm_count) {
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
   if (!coop) return false;
-  const void* fn = h->dtype == B2OT_F32 ? (const void*)resident_knopp_kernel<float> : (const void*)resident_knopp_kernel<double>;
+  const void* fn = resident_fn(h);
   if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64) != cudaSuccess) {
     cudaGetLastError();
     return false;
@@ -624,7 +628,7 @@ static int launch_resident(b2ot_dense* h, int n_iters) {
   ResParams p;
   memset(&p, 0, sizeof(p));
   p.K = h->K;  p.ld = h->ld;  p.n = h->n;  p.m = h->m;  p.mp = h->mp;
-  p.a = h->a;  p.b = h->b;
+  p.a = h->a;  p.b = h->b;  p.logb = h->logb;
   p.uring = h->uring;  p.vring = h->vring;  p.cbuf = h->cbuf;  p.xbuf = h->partials;
   p.st = h->st;  p.err_hist = h->err_hist;
   p.max_iter = h->max_iter;  p.check_every = h->check_every;  p.stop_thr = h->stop_thr;
@@ -636,8 +640,8 @@ static int launch_resident(b2ot_dense* h, int n_iters) {
   if (diag_env("B2OT_RES_TRACE")) p.trace = (long long*)h->blk_err;  // 64 iterations x 8 stamps = the 512 leading doubles' bytes... (4 KB of the 8 KB block)
 #endif
   void* args[] = {(void*)&p};
-  const cudaError_t e = cudaLaunchCooperativeKernel((const void*)resident_knopp_kernel<T>, dim3((unsigned)h->res_grid),
-                                                    dim3(RES_THREADS), args, h->res_smem, h->stream);
+  const cudaError_t e = cudaLaunchCooperativeKernel(resident_fn(h), dim3((unsigned)h->res_grid), dim3(RES_THREADS), args,
+                                                    h->res_smem, h->stream);
   if (e == cudaErrorCooperativeLaunchTooLarge || e == cudaErrorLaunchOutOfResources) {
     // the grid cannot be co-resident right now (SMs taken away by MPS / a partitioned device): the streaming solver
     // continues the same solve from the same state
@@ -713,8 +717,8 @@ extern "C" int b2ot_dense_create(b2ot_dense** handle, int mode, int dtype, int64
   if (variant == B2OT_VARIANT_RESIDENT) {
     if (!h->res_ok) {
       delete h;
-      set_error("b2ot_dense_create: the resident solver needs the scaling domain and K twice within the grid's shared "
-                "memory (a row block and a column block per CTA, <= 200 KB), got n=%lld m=%lld", (long long)n, (long long)m);
+      set_error("b2ot_dense_create: the resident solver needs K twice within the grid's shared memory (a row block and a "
+                "column block per CTA, <= 200 KB), got n=%lld m=%lld", (long long)n, (long long)m);
       return -1;
     }
     variant = B2OT_VARIANT_AUTO;  // the streaming fallback behind it (unbalanced / stabilized / sharded use)

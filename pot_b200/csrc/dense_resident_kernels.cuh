@@ -1,4 +1,4 @@
-// Resident solver for SMALL dense problems (scaling domain), sm_100a.
+// Resident solver for SMALL dense problems (scaling domain and log domain), sm_100a.
 //
 // BASELINE config 1 (ot.sinkhorn, 1000 x 1000 fp64, 1000 iterations) is 8 MB: the streaming solver runs it as two
 // dependent launches per iteration (fused sweep + finalize, 12.1 us per iteration, of which the L2-resident data
@@ -27,6 +27,9 @@
 // (v-then-u, ot/bregman/_sinkhorn.py:629-631), error ||v * K^T u - b||_2 every check_every iterations (:646-663) and
 // guard with the revert to the previous (u, v) (:633-645) as the streaming solver, so init / poll / export of the
 // handle are unchanged (the plain u / v rings are written alongside).
+// Log domain (MODE_LOG, ot/bregman/_sinkhorn.py:880-906): the same two phases with exact log-sum-exps (block_lses) in place
+// of the dot products: u = log a - LSE_j(Mr + v) on the rows, L_j = LSE_i(Mr + u) on the columns, error term
+// (exp(L_j + v_j) - b_j)^2 = the column marginal of exp(Mr + u + v), next v = log b - L_j; no guard, like the reference.
 #pragma once
 
 #include "common.cuh"
@@ -46,8 +49,9 @@ struct ResParams {
   long long* trace;  // diagnosis build: clock64 stamps of CTA 0, [iteration][8]
   const void* K;
   long long ld, n, m, mp;
-  const void* a;
+  const void* a;     // KNOPP: a, LOG: log a
   const void* b;
+  const void* logb;  // LOG only
   void* uring;       // 2 x n
   void* vring;       // 3 x mp
   void* cbuf;        // mp
@@ -185,6 +189,71 @@ __device__ __forceinline__ void block_dots(const T* mat, const T* vec, int nrows
     __syncthreads();
   }
 }
+// `nrows` log-sum-exps  out[r] = log sum_j exp(mat[r][j] + vec[j])  by the whole block (log domain): exact row maxima
+// first (no exponential), then sum exp(x - max) - one exponential per element, fixed summation order.  A row of -inf
+// gives -inf.  rmx: 8 values of shared memory.
+template <typename T>
+__device__ __forceinline__ void block_lses(const T* mat, const T* vec, int nrows, long long len, T* red, T* rmx, T* out) {
+  constexpr int RB = 8;
+  const int tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
+  for (int i0 = 0; i0 < nrows; i0 += RB) {
+    const int nb = nrows - i0 < RB ? nrows - i0 : RB;
+    T mx[RB];
+#pragma unroll
+    for (int r = 0; r < RB; ++r) mx[r] = neg_inf<T>();
+    for (long long j = tid; j < len; j += RES_THREADS) {
+      const T x = vec[j];
+#pragma unroll
+      for (int r = 0; r < RB; ++r)
+        if (r < nb) mx[r] = max_t(mx[r], mat[(size_t)(i0 + r) * len + j] + x);
+    }
+#pragma unroll
+    for (int r = 0; r < RB; ++r) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) mx[r] = max_t(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], o));
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int r = 0; r < RB; ++r) red[wrp * RB + r] = mx[r];
+    }
+    __syncthreads();
+    if (tid < RB) {
+      T M = red[tid];
+#pragma unroll
+      for (int w = 1; w < 8; ++w) M = max_t(M, red[w * RB + tid]);
+      rmx[tid] = M;
+    }
+    __syncthreads();
+    T ref[RB], sm[RB];
+#pragma unroll
+    for (int r = 0; r < RB; ++r) {
+      const T M = rmx[r];
+      ref[r] = (M == neg_inf<T>()) ? (T)0 : M;
+      sm[r] = (T)0;
+    }
+    for (long long j = tid; j < len; j += RES_THREADS) {
+      const T x = vec[j];
+#pragma unroll
+      for (int r = 0; r < RB; ++r)
+        if (r < nb) sm[r] += exp_t(mat[(size_t)(i0 + r) * len + j] + x - ref[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < RB; ++r) sm[r] = warp_sum_down(sm[r]);
+    if (lane == 0) {
+#pragma unroll
+      for (int r = 0; r < RB; ++r) red[wrp * RB + r] = sm[r];
+    }
+    __syncthreads();
+    if (tid < nb) {
+      T t = (T)0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) t += red[w * RB + tid];
+      const T M = rmx[tid];
+      out[i0 + tid] = ((M == neg_inf<T>()) ? (T)0 : M) + log_t(t);
+    }
+    __syncthreads();
+  }
+}
 // words of ONE copy of the exchange area (multiple of 16: copies start on 128-byte lines)
 __host__ __device__ inline size_t res_xcopy_words(long long n, long long m, int elem_words) {
   return (((size_t)(n + m) * elem_words + 2 + 2 * (size_t)RES_MAXG) + 15) & ~(size_t)15;
@@ -194,8 +263,8 @@ __host__ __device__ inline size_t res_xbuf_bytes(long long n, long long m, int e
 }
 
 
-template <typename T>
-__global__ void __launch_bounds__(RES_THREADS, 1) resident_knopp_kernel(const ResParams p) {
+template <typename T, int MODE>
+__global__ void __launch_bounds__(RES_THREADS, 1) resident_solve_kernel(const ResParams p) {
   extern __shared__ __align__(16) unsigned char res_smem[];
   const int tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
   const unsigned int G = gridDim.x;
@@ -214,8 +283,10 @@ __global__ void __launch_bounds__(RES_THREADS, 1) resident_knopp_kernel(const Re
   T* vn = us + n;                           // m       : v being produced
   T* as = vn + m;                           // R       : a on the CTA's rows
   T* bs = as + R;                           // Q       : b on the CTA's columns
-  T* red = bs + Q;                          // 64      : warp partials of block_dots
-  T* dots = red + 64;                       // max(R, Q)
+  T* red = bs + Q;                          // 64      : warp partials of block_dots / block_lses
+  T* rmx = red + 64;                        // 8       : row maxima of block_lses
+  T* dots = rmx + 8;                        // max(R, Q)
+  T* lbs = dots + (R > Q ? R : Q);          // Q       : log b on the CTA's columns (log domain)
   __shared__ double sred[8];
 
   const T* Kg = reinterpret_cast<const T*>(p.K);
@@ -251,7 +322,10 @@ __global__ void __launch_bounds__(RES_THREADS, 1) resident_knopp_kernel(const Re
     const T* v0 = vring + (long long)sel_v * p.mp;
     for (long long j = tid; j < m; j += RES_THREADS) vs[j] = __ldcg(&v0[j]);
     for (int i = tid; i < nr; i += RES_THREADS) as[i] = a[r0 + i];
-    for (int q = tid; q < nq; q += RES_THREADS) bs[q] = b[j0 + q];
+    for (int q = tid; q < nq; q += RES_THREADS) {
+      bs[q] = b[j0 + q];
+      if (MODE == MODE_LOG) lbs[q] = reinterpret_cast<const T*>(p.logb)[j0 + q];
+    }
   }
   __syncthreads();
 
@@ -260,14 +334,18 @@ __global__ void __launch_bounds__(RES_THREADS, 1) resident_knopp_kernel(const Re
     T* unew = uring + (long long)(sel_u ^ 1) * n;
     epoch += 1;
     RES_TRACE(0);
-    block_dots(Ks, vs, nr, m, red, dots);
+    if (MODE == MODE_LOG)
+      block_lses(Ks, vs, nr, m, red, rmx, dots);   // u = log a - LSE_j(Mr + v)   (_sinkhorn.py:882)
+    else
+      block_dots(Ks, vs, nr, m, red, dots);
     for (int i = tid; i < nr; i += RES_THREADS) {
-      const T u = as[i] / dots[i];
+      const T u = (MODE == MODE_LOG) ? as[i] - dots[i] : as[i] / dots[i];
       for (int r = 0; r < nrep; ++r) XWords<T>::put(xall + (size_t)r * xstride, r0 + i, u, epoch);
       unew[r0 + i] = u;
     }
     RES_TRACE(1);
-    const int uf = __syncthreads_or(res_gather<T>(xu, n, R, G, epoch, us));
+    int uf = __syncthreads_or(res_gather<T>(xu, n, R, G, epoch, us));
+    if (MODE == MODE_LOG) uf = 0;  // -inf is a legitimate log-scaling; sinkhorn_log has no numerical guard
     RES_TRACE(2);
 
     // ---------------- phase B: c = K^T u on the CTA's columns, v = b / c, error term; all-gather of v ----------------
@@ -275,15 +353,26 @@ __global__ void __launch_bounds__(RES_THREADS, 1) resident_knopp_kernel(const Re
     const int ii = iter;
     const bool check = (ii % p.check_every) == 0;
     epoch += 1;
-    block_dots(Kt, us, nq, n, red, dots);
+    if (MODE == MODE_LOG)
+      block_lses(Kt, us, nq, n, red, rmx, dots);   // L_j = LSE_i(Mr + u)
+    else
+      block_dots(Kt, us, nq, n, red, dots);
     double e2 = 0.0;
     for (int q = tid; q < nq; q += RES_THREADS) {
       const long long j = j0 + q;
-      const T c = dots[q];
       const T bj = bs[q];
-      const T d = vs[j] * c - bj;  // column marginal of diag(u) K diag(v) minus b
-      e2 += (double)d * (double)d;
-      const T vnew = bj / c;
+      T c, vnew;
+      if (MODE == MODE_LOG) {
+        c = exp_t(dots[q] + vs[j]);    // column marginal of exp(Mr + u + v) with the new u (:884-889)
+        vnew = lbs[q] - dots[q];       // v of the next iteration = log b - LSE_i(Mr + u)   (:881)
+        const T d = c - bj;
+        e2 += (double)d * (double)d;
+      } else {
+        c = dots[q];
+        const T d = vs[j] * c - bj;    // column marginal of diag(u) K diag(v) minus b
+        e2 += (double)d * (double)d;
+        vnew = bj / c;
+      }
       for (int r = 0; r < nrep; ++r) XWords<T>::put(xall + (size_t)r * xstride + off_v, j, vnew, epoch);
       cbuf[j] = c;
       vnext[j] = vnew;
@@ -315,12 +404,12 @@ __global__ void __launch_bounds__(RES_THREADS, 1) resident_knopp_kernel(const Re
       x = warp_sum_down(x);
       if (lane == 0) sred[0] = x;
     }
-    const int nflags = __syncthreads_or(vbad) ? FLAG_VBAD : 0;
+    const int nflags = (__syncthreads_or(vbad) && MODE == MODE_KNOPP) ? FLAG_VBAD : 0;
     if (check) err2 = sred[0];
     RES_TRACE(5);
 
     // ---------------- decision (redundant, identical in every CTA) ----------------
-    if (cur_flags != 0 || uf != 0) {
+    if (MODE == MODE_KNOPP && (cur_flags != 0 || uf != 0)) {
       // reference guard (_sinkhorn.py:633-645): come back to the previous (u, v) and stop
       status = ST_NUMERR;
       niter = ii;

@@ -79,7 +79,7 @@ def test_knopp_golden_fixed(golden, case, variant):
     assert all(e.dtype == Mt.dtype and e.device == Mt.device for e in lg["err"])
 
 
-@pytest.mark.parametrize("variant", ["fused", "split"])
+@pytest.mark.parametrize("variant", ["fused", "split", "resident"])
 @pytest.mark.parametrize("case", DENSE)
 def test_log_golden_fixed(golden, case, variant):
     a, b, M = golden(case, "a"), golden(case, "b"), golden(case, "M")
@@ -332,8 +332,48 @@ def test_resident_handle_chunks_and_info():
     s = _dense.DenseSolver("knopp", K, a, b, None, max_iter=1000, check_every=10, stop_thr=0.0)
     assert s.info()["variant"] == "resident"   # what "auto" resolves to at this size
     s.close()
-    with pytest.raises(_lib.B2otError, match="resident solver needs"):
-        _dense.DenseSolver("log", K.log(), a.log(), b, b.log(), max_iter=10, check_every=10, stop_thr=0.0, variant="resident")
+    s = _dense.DenseSolver("log", K.log(), a.log(), b, b.log(), max_iter=10, check_every=10, stop_thr=0.0)
+    assert s.info()["variant"] == "resident"   # the log domain has its resident form too
+    s.close()
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("shape", [(1, 1), (3, 4), (7, 1), (149, 257), (257, 1031), (1000, 1000), (300, 2100)])
+def test_resident_log_solver(shape, dtype):
+    """Log-domain resident solver (exact log-sum-exps on the row and column blocks) against the oracle's sinkhorn_log
+    (ot/bregman/_sinkhorn.py:880-906) and the streaming sweep."""
+    n, m = shape
+    rng = np.random.RandomState(n * 3 + m)
+    xs, xt = rng.randn(n, 2), rng.randn(m, 2) + 1.0
+    M = orc.sqeuclidean(xs, xt)
+    M = (M / M.max()).astype(dtype)
+    a = rng.rand(n) + 0.1
+    b = rng.rand(m) + 0.1
+    a, b = (a / a.sum()).astype(dtype), (b / b.sum()).astype(dtype)
+    at, bt, Mt = to_dev(a, b, M)
+    tol = tol_of(dtype)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        G, lg = ot.bregman.sinkhorn_log(at, bt, Mt, 0.05, numItermax=23, stopThr=0, log=True, warn=False,
+                                        b2ot_variant="resident")
+        Gr, lgr = orc.sinkhorn_log(a, b, M, 0.05, numItermax=23, stopThr=0, log=True, warn=False)
+        Gs, lgs = ot.bregman.sinkhorn_log(at, bt, Mt, 0.05, numItermax=23, stopThr=0, log=True, warn=False,
+                                          b2ot_variant="split")
+    assert lg["niter"] == lgr["niter"] == 22
+    assert_plan(G, Gr, tol)
+    fin = np.isfinite(lgr["log_u"])
+    assert np.array_equal(np.isfinite(lg["log_u"].cpu().numpy()), fin)
+    assert_logpot(lg["log_u"][torch.as_tensor(fin, device=DEV)], lgr["log_u"][fin], tol)
+    assert_logpot(lg["log_v"], lgr["log_v"], tol)
+    assert_errs(lg["err"], lgr["err"], dtype)
+    assert_plan(G, Gs.cpu().numpy(), 10 * tol)
+    # converging solve: same stop iteration as the reference in fp64
+    Gc, lgc = ot.bregman.sinkhorn_log(at, bt, Mt, 0.05, numItermax=3000, stopThr=1e-6, log=True, warn=False)
+    Grc, lgrc = orc.sinkhorn_log(a, b, M, 0.05, numItermax=3000, stopThr=1e-6, log=True, warn=False)
+    if dtype == np.float64:
+        assert lgc["niter"] == lgrc["niter"]
+    else:
+        assert abs(lgc["niter"] - lgrc["niter"]) <= 10
 
 
 def test_noncontiguous_and_strided_inputs():

@@ -41,7 +41,7 @@ extern "C" {
 #define B2OT_VARIANT_AUTO 0    /* resident when K fits the grid's shared memory, else fused cluster sweep when the layout allows it, else split */
 #define B2OT_VARIANT_FUSED 1   /* one pass over K per iteration: TMA-bulk staged row tiles, cluster/DSMEM row reduce */
 #define B2OT_VARIANT_SPLIT 2   /* two passes (row kernel + column kernel); any shape / alignment */
-#define B2OT_VARIANT_RESIDENT 3 /* small problems, scaling domain: K resident in the grid's shared memory, one cooperative
+#define B2OT_VARIANT_RESIDENT 3 /* small problems, both domains: K resident in the grid's shared memory, one cooperative
                                    launch per chunk of iterations (AUTO picks it when K fits and m <= 4096) */
 
 /* ---- library ---- */

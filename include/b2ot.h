@@ -168,6 +168,14 @@ int b2ot_dense_plan_value(int mode, int dtype, const void* K, const void* M, con
 size_t b2ot_colsum_scratch_bytes(int64_t n, int64_t m);
 int b2ot_colsum(int dtype, const void* P, int64_t n, int64_t m, int64_t ld, void* out, void* scratch_dev,
                 void* stream);
+/* b2ot_colsum that allocates nothing and takes no scratch pointer: the partials live in a file-scope device array of
+ * 32 x B2OT_COLSUM_STATIC_MAX_COLS doubles (4 MiB per GPU that loads the library, held until exit).  No counterpart in
+ * the reference: added for callers that cannot call cudaMalloc (CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  m > B2OT_COLSUM_STATIC_MAX_COLS is rejected (-1, message in
+ * b2ot_last_error()).  Same kernels and summation order as b2ot_colsum: identical results.  All calls share the array:
+ * calls that overlap on the GPU race; order them on one stream (or by events). */
+#define B2OT_COLSUM_STATIC_MAX_COLS 16384
+int b2ot_colsum_static(int dtype, const void* P, int64_t n, int64_t m, int64_t ld, void* out, void* stream);
 
 /* ---- batched Sinkhorn (ot.batch): B independent n x m problems, each solved on chip ----
  * Replaces bregman_projection_batch (ot/batch/_utils.py:46-162; mode KNOPP, potentials = scalings f, g),

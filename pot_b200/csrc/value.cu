@@ -1,6 +1,7 @@
 // C ABI of the plan / objective epilogue (see include/b2ot.h, value_kernels.cuh).
 #include <algorithm>
 #include <cstdint>
+#include <mutex>
 
 #include "../../include/b2ot.h"
 #include "host_util.h"
@@ -118,6 +119,57 @@ extern "C" int b2ot_colsum(int dtype, const void* P, int64_t n, int64_t m, int64
     colsum_kernel<double><<<grid, 256, 0, s>>>((const double*)P, n, m, ld, (double*)scratch_dev);
     B2OT_CHECK_LAUNCH();
     colsum_reduce_kernel<double><<<grid.x, 256, 0, s>>>((const double*)scratch_dev, m, S, (double*)out);
+  }
+  B2OT_CHECK_LAUNCH();
+  return 0;
+}
+
+// ---- b2ot_colsum without any allocation: the row-block partials live in a file-scope device array ----
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, serving loops, harnesses that forbid it).  kColSplit x B2OT_COLSUM_STATIC_MAX_COLS doubles = 4 MiB,
+// held by every GPU that loads the library until the process exits.  Host code must not pass the array's name to a kernel
+// (on the host it is a stand-in symbol, not a device address): the device address is looked up once per device with
+// cudaGetSymbolAddress, with that device current, and cached.  All calls share the array: calls that overlap on the GPU
+// (different streams, or graph branches without an edge between them) race.  Nothing has to start at zero - a call
+// writes every partial [0, S) x [0, m) it later reads (colsum_kernel), so the previous call's contents are dead.
+static __device__ __align__(256) double g_colsum_static_scratch[(size_t)kColSplit * B2OT_COLSUM_STATIC_MAX_COLS];
+
+static const int kMaxDevices = 64;
+static std::mutex g_colsum_static_mutex;
+static double* g_colsum_static_ptr[kMaxDevices] = {};
+
+extern "C" int b2ot_colsum_static(int dtype, const void* P, int64_t n, int64_t m, int64_t ld, void* out, void* stream) {
+  B2OT_REQUIRE(dtype == B2OT_F32 || dtype == B2OT_F64, "b2ot_colsum_static: bad dtype %d", dtype);
+  B2OT_REQUIRE(P && out && n >= 1 && m >= 1 && ld >= m, "b2ot_colsum_static: bad arguments");
+  B2OT_REQUIRE(m <= (int64_t)B2OT_COLSUM_STATIC_MAX_COLS,
+               "b2ot_colsum_static: m=%lld exceeds the static scratch (at most %d columns); use b2ot_colsum with "
+               "caller-provided scratch",
+               (long long)m, (int)B2OT_COLSUM_STATIC_MAX_COLS);
+  int dev = -1;
+  B2OT_CUDA(cudaGetDevice(&dev));
+  B2OT_REQUIRE(dev >= 0 && dev < kMaxDevices, "b2ot_colsum_static: device ordinal %d out of range", dev);
+  double* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_colsum_static_mutex);
+    if (g_colsum_static_ptr[dev] == nullptr) {
+      double* ptr = nullptr;
+      B2OT_CUDA(cudaGetSymbolAddress((void**)&ptr, g_colsum_static_scratch));
+      B2OT_REQUIRE(ptr != nullptr, "b2ot_colsum_static: cudaGetSymbolAddress returned a null address");
+      g_colsum_static_ptr[dev] = ptr;
+    }
+    scratch = g_colsum_static_ptr[dev];
+  }
+  const int S = (int)std::min<long long>(n, kColSplit);
+  dim3 grid((unsigned)((m + 255) / 256), (unsigned)S);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (dtype == B2OT_F32) {
+    colsum_kernel<float><<<grid, 256, 0, s>>>((const float*)P, n, m, ld, scratch);
+    B2OT_CHECK_LAUNCH();
+    colsum_reduce_kernel<float><<<grid.x, 256, 0, s>>>(scratch, m, S, (float*)out);
+  } else {
+    colsum_kernel<double><<<grid, 256, 0, s>>>((const double*)P, n, m, ld, scratch);
+    B2OT_CHECK_LAUNCH();
+    colsum_reduce_kernel<double><<<grid.x, 256, 0, s>>>(scratch, m, S, (double*)out);
   }
   B2OT_CHECK_LAUNCH();
   return 0;

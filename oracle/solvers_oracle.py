@@ -229,23 +229,35 @@ def solve_unbalanced(M, a=None, b=None, reg=None, unbalanced=None, max_iter=None
 
 def sinkhorn_stabilized(a, b, M, reg, numItermax=1000, tau=1e3, stopThr=1e-9, warmstart=None, print_period=20,
                         log=False, warn=True):
-    """ot.bregman.sinkhorn_stabilized for a 1-D b (ot/bregman/_sinkhorn.py:1105-1382).
+    """ot.bregman.sinkhorn_stabilized (ot/bregman/_sinkhorn.py:1105-1382), 1-D and 2-D b.
 
     Scalings start at 1/n, 1/m (:1252-1254); each iteration is v = b / K^T u, u = a / K v (:1270-1271); when
     max|u| or max|v| exceeds tau the scalings are folded into the potentials and K is rebuilt (:1274-1288); every
     print_period iterations err = || sum_i Gamma_ij - b ||_2 (:1303-1304); stop on err <= stopThr (:1316); nan in
     u or v -> previous (u, v) and stop (:1319-1325).  Returns the plan Gamma (:1349 / :1360) and, with log=True,
     the dict of :1332-1340.
+
+    2-D b (n_hists columns, :1230-1234): u, v are (dim, n_hists) and share ONE kernel K.  The absorption is joint and
+    keeps the scalings (:1275-1279: alpha += reg * max over the histograms of log u, beta += reg * the SCALAR max of
+    log v; the reset of u, v sits in the 1-D branch only); the error is the relative max-change of u and v
+    (:1297-1301); the result is the vector of losses <M, Gamma_h> (:1342-1348).
     """
     a, b, M = so._as_arrays(a, b, M)
+    n_hists = b.shape[1] if b.ndim > 1 else 0
+    if n_hists:
+        a = a[:, None]  # :1232
     dim_a, dim_b = len(a), len(b)
     hist = {"err": []}
     if warmstart is None:
         alpha, beta = np.zeros(dim_a, dtype=M.dtype), np.zeros(dim_b, dtype=M.dtype)
     else:
         alpha, beta = warmstart
-    u = np.ones(dim_a, dtype=M.dtype) / dim_a
-    v = np.ones(dim_b, dtype=M.dtype) / dim_b
+    if n_hists:
+        u = np.ones((dim_a, n_hists), dtype=M.dtype) / dim_a
+        v = np.ones((dim_b, n_hists), dtype=M.dtype) / dim_b
+    else:
+        u = np.ones(dim_a, dtype=M.dtype) / dim_a
+        v = np.ones(dim_b, dtype=M.dtype) / dim_b
 
     def get_K(alpha, beta):
         return np.exp(-(M - alpha.reshape((dim_a, 1)) - beta.reshape((1, dim_b))) / reg)  # :1256-1258
@@ -264,14 +276,22 @@ def sinkhorn_stabilized(a, b, M, reg, numItermax=1000, tau=1e3, stopThr=1e-9, wa
         v = b / np.dot(K.T, u)
         u = a / np.dot(K, v)
         if np.max(np.abs(u)) > tau or np.max(np.abs(v)) > tau:
-            alpha, beta = alpha + reg * np.log(u), beta + reg * np.log(v)
-            u = np.ones(dim_a, dtype=M.dtype) / dim_a
-            v = np.ones(dim_b, dtype=M.dtype) / dim_b
+            if n_hists:
+                alpha, beta = alpha + reg * np.max(np.log(u), 1), beta + reg * np.max(np.log(v))
+            else:
+                alpha, beta = alpha + reg * np.log(u), beta + reg * np.log(v)
+                u = np.ones(dim_a, dtype=M.dtype) / dim_a
+                v = np.ones(dim_b, dtype=M.dtype) / dim_b
             K = get_K(alpha, beta)
             n_absorb += 1
         if ii % print_period == 0:
-            transp = get_Gamma(alpha, beta, u, v)
-            err = np.linalg.norm(np.sum(transp, axis=0) - b)
+            if n_hists:
+                err_u = np.max(np.abs(u - uprev)) / max(np.max(np.abs(u)), np.max(np.abs(uprev)), 1.0)
+                err_v = np.max(np.abs(v - vprev)) / max(np.max(np.abs(v)), np.max(np.abs(vprev)), 1.0)
+                err = 0.5 * (err_u + err_v)
+            else:
+                transp = get_Gamma(alpha, beta, u, v)
+                err = np.linalg.norm(np.sum(transp, axis=0) - b)
             hist["err"].append(err)
         if err <= stopThr:
             converged = True
@@ -284,7 +304,11 @@ def sinkhorn_stabilized(a, b, M, reg, numItermax=1000, tau=1e3, stopThr=1e-9, wa
     if not converged and warn:
         warnings.warn("Sinkhorn did not converge. You might want to increase the number of iterations "
                       "`numItermax` or the regularization parameter `reg`.")
-    G = get_Gamma(alpha, beta, u, v)
+    if n_hists:
+        G = np.stack([np.sum(get_Gamma(alpha, beta, u[:, h], v[:, h]) * M) for h in range(n_hists)])
+        alpha, beta = alpha[:, None], beta[:, None]  # :1333-1334
+    else:
+        G = get_Gamma(alpha, beta, u, v)
     if not log:
         return G
     hist["n_iter"] = ii

@@ -65,6 +65,12 @@ def gstab():
 
 
 @pytest.fixture(scope="session")
+def gstabm():
+    """Golden vectors of sinkhorn_stabilized with 2-D b: golden_stabilized_multi.npz."""
+    return Golden(os.path.join(GOLDEN_DIR, "golden_stabilized_multi.npz"))
+
+
+@pytest.fixture(scope="session")
 def ggw():
     """Golden vectors of entropic_gromov_wasserstein: golden_gromov.npz."""
     return Golden(os.path.join(GOLDEN_DIR, "golden_gromov.npz"))

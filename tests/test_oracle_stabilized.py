@@ -80,3 +80,47 @@ def test_epsilon_scaling(gstab, name):
     ref = gstab(case, "err")
     assert len(log["err"]) == len(ref)
     np.testing.assert_allclose(log["err"], ref, rtol=1e-5, atol=1e-20)
+
+
+# ---- several target histograms (2-D b): tests/golden/golden_stabilized_multi.npz ----
+STABM = ["mild_f64", "absorb_f64", "absorb_tau10_f64", "period7_f64", "conv_f64", "conv_absorb_f64", "wide_f64",
+         "one_hist_f64", "mild_f32", "absorb_f32"]
+
+
+@pytest.mark.parametrize("name", STABM)
+def test_stabilized_multi(gstabm, name):
+    case = f"stabm_{name}"
+    M, a, b, reg = (gstabm(case, k) for k in ("M", "a", "b", "reg"))
+    assert b.ndim == 2
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        res, log = orc.sinkhorn_stabilized(a, b, M, float(reg), log=True, **kwargs(gstabm, case))
+    t = rtol(case)
+    assert log["n_iter"] == int(gstabm(case, "n_iter"))
+    if "absorb" in name:
+        assert log["n_absorb"] >= 1
+    assert res.shape == (b.shape[1],)
+    close(res, gstabm(case, "losses"), t)
+    for k in ("logu", "logv", "alpha", "beta"):
+        assert log[k].shape == gstabm(case, k).shape
+        close(log[k], gstabm(case, k), t)
+    ref = gstabm(case, "err")
+    assert len(log["err"]) == len(ref)
+    np.testing.assert_allclose(log["err"], ref, rtol=1e-6 if "f64" in case else 5e-2, atol=1e-13 if "f64" in case else 1e-6)
+
+
+def test_stabilized_multi_warmstart(gstabm):
+    case = "stabm_absorb_f64"
+    M, a, b, reg = (gstabm(case, k) for k in ("M", "a", "b", "reg"))
+    ws = (gstabm(case + "_warm", "ws_alpha"), gstabm(case + "_warm", "ws_beta"))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        res, log = orc.sinkhorn_stabilized(a, b, M, float(reg), numItermax=40, stopThr=0.0, warmstart=ws, log=True)
+    close(res, gstabm(case + "_warm", "losses"), 1e-10)
+    close(log["alpha"], gstabm(case + "_warm", "alpha"), 1e-10)
+    close(log["beta"], gstabm(case + "_warm", "beta"), 1e-10)
+    assert log["n_iter"] == int(gstabm(case + "_warm", "n_iter"))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        res = orc.sinkhorn_stabilized(a, b, M, float(reg), numItermax=200, stopThr=0.0)
+    close(res, gstabm(case + "_loss", "value"), 1e-10)

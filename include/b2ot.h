@@ -110,6 +110,26 @@ int b2ot_dense_set_stabilized(b2ot_dense* handle, double tau, const void* Mr, in
                               void* beta_r);
 /* number of absorptions so far (synchronises the stream) */
 int b2ot_dense_absorb_count(b2ot_dense* handle, int* count);
+/* Several target histograms on ONE kernel matrix: the loop body of sinkhorn_stabilized with a 2-D b
+ * (ot/bregman/_sinkhorn.py:1230-1234: u is n x H, v is m x H, row-major, H = b.shape[1]).
+ * b2ot_multi_scaling_step enqueues one iteration (:1270-1271)
+ *     v_new = B / (K^T u_prev),   u_new = a / (K v_new)           (out of place; a: n values, B: m x H)
+ * and, when stats_dev is not null, the 8 doubles the host's tests need (one 64-byte read per iteration; the reference
+ * syncs every iteration at :1274 too):
+ *     [0] max|u_new| [1] max|v_new| [2] max|u_new - u_prev| [3] max|u_prev| [4] max|v_new - v_prev| [5] max|v_prev|
+ *     [6] u_new contains nan [7] v_new contains nan        (the maxima skip nan entries)
+ * i.e. the absorption trigger (:1274), the error of :1297-1301 and the guard of :1319.
+ * scratch_dev >= b2ot_multi_scratch_bytes(n, m, H); deterministic.
+ * b2ot_multi_absorb enqueues the joint absorption of :1275-1279 on alpha_r = alpha/reg (n doubles), beta_r = beta/reg
+ * (m doubles): alpha_r[i] += max_h log u[i, h], beta_r[j] += max over ALL entries of log v (a scalar, as written in
+ * the reference); u, v are kept (that branch has no reset).  The caller then rebuilds K = exp(Mr + alpha_r + beta_r)
+ * with b2ot_dense_plan (mode LOG). */
+size_t b2ot_multi_scratch_bytes(int64_t n, int64_t m, int64_t H);
+int b2ot_multi_scaling_step(int dtype, const void* K, int64_t n, int64_t m, int64_t ld, int64_t H, const void* a,
+                            const void* B, const void* u_prev, const void* v_prev, void* u_new, void* v_new,
+                            double* stats_dev, void* scratch_dev, void* stream);
+int b2ot_multi_absorb(int dtype, int64_t n, int64_t m, int64_t H, const void* u, const void* v, double* alpha_r,
+                      double* beta_r, void* stream);
 int b2ot_dense_set_allreduce(b2ot_dense* handle, b2ot_allreduce_fn fn, void* ctx);
 /* enqueue: load the initial scalings (u0: n, v0: m; log-scalings in LOG mode) and run the
  * column-only pass that seeds the first v update (:629 / :881 of the reference loop) */

@@ -182,10 +182,11 @@ class DenseSolver:
             pass
 
 
-def plan(mode, K, u, v):
-    """KNOPP: u_i K_ij v_j (_sinkhorn.py:685-687); LOG: exp(K_ij + u_i + v_j) (:915-918)."""
+def plan(mode, K, u, v, out=None):
+    """KNOPP: u_i K_ij v_j (_sinkhorn.py:685-687); LOG: exp(K_ij + u_i + v_j) (:915-918).  `out`: optional destination."""
     lib = _lib.load()
-    out = torch.empty_like(K, memory_format=torch.contiguous_format)
+    if out is None:
+        out = torch.empty_like(K, memory_format=torch.contiguous_format)
     with torch.cuda.device(K.device):
         _lib.check(lib.b2ot_dense_plan(_lib.MODE_KNOPP if mode == "knopp" else _lib.MODE_LOG, dtype_code(K.dtype),
                                        K.data_ptr(), u.data_ptr(), v.data_ptr(), out.data_ptr(), K.shape[0],

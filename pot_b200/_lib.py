@@ -63,6 +63,12 @@ PROTOTYPES = {
     "b2ot_colsum_scratch_bytes": (C.c_size_t, [C.c_int64, C.c_int64]),
     "b2ot_colsum": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
                               C.c_void_p]),
+    "b2ot_multi_scratch_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int64]),
+    "b2ot_multi_scaling_step": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p,
+                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_void_p]),
+    "b2ot_multi_absorb": (C.c_int, [C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.c_void_p, C.c_void_p]),
     "b2ot_colsum_static": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p,
                                      C.c_void_p]),
     "b2ot_batch_workspace_bytes": (C.c_size_t, [C.c_int64]),

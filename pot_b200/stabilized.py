@@ -2,7 +2,7 @@
 
 Mirrors (same names, argument meaning, return values, warnings and errors):
 
-    ot.bregman.sinkhorn_stabilized        ot/bregman/_sinkhorn.py:1105-1382   (1-D b)
+    ot.bregman.sinkhorn_stabilized        ot/bregman/_sinkhorn.py:1105-1382   (1-D b: device loop; 2-D b: _stabilized_multi)
     ot.bregman.sinkhorn_epsilon_scaling   ot/bregman/_sinkhorn.py:1385-1573
 
 The stabilized iteration is the balanced scaling iteration v = b / K^T u, u = a / K v (:1270-1271) on the kernel
@@ -58,11 +58,101 @@ def _stabilized_core(a, b, Mc, reg, numItermax, tau, stopThr, warmstart, print_p
     return Mr, alpha_r, beta_r, u, v, errs, niter, status, cnt.value
 
 
+def _stabilized_multi(a, b, Mc, reg, numItermax, tau, stopThr, warmstart, print_period):
+    """2-D ``b`` (ot/bregman/_sinkhorn.py:1230-1234): H histograms on ONE kernel, joint absorption and joint error.
+
+    The loop is the reference's (:1267-1325) with its per-iteration host decision (:1274): every iteration is one
+    `b2ot_multi_scaling_step` (two passes over K for all histograms + the statistics of the host's tests, four
+    launches) and one 64-byte read; an absorption is `b2ot_multi_absorb` + a rewrite of K from Mr = -M/reg.
+    Returns (Mr, alpha/reg, beta/reg (float64), u, v (dim x H), errs, n_iter, status).
+    """
+    lib = _lib.load()
+    n, m = Mc.shape
+    H = b.shape[1]
+    dt, dev = Mc.dtype, Mc.device
+    code = _dense.dtype_code(dt)
+    f64 = torch.float64
+    if warmstart is None:
+        alpha_r = torch.zeros(n, dtype=f64, device=dev)
+        beta_r = torch.zeros(m, dtype=f64, device=dev)
+    else:
+        alpha_r = (warmstart[0].detach().to(f64).reshape(-1) / reg).contiguous()
+        beta_r = (warmstart[1].detach().to(f64).reshape(-1) / reg).contiguous()
+    u = torch.full((n, H), 1.0 / n, dtype=dt, device=dev)  # :1250-1251
+    v = torch.full((m, H), 1.0 / m, dtype=dt, device=dev)
+    un, vn = torch.empty_like(u), torch.empty_like(v)
+    Mr = _dense.cost_transform(Mc, reg, "negscale")
+    K = _dense.plan("log", Mr, alpha_r.to(dt), beta_r.to(dt))  # get_K, :1256-1258
+    stats = torch.zeros(8, dtype=f64, device=dev)
+    stats_host = torch.zeros(8, dtype=f64).pin_memory()
+    scratch = torch.empty(lib.b2ot_multi_scratch_bytes(n, m, H), dtype=torch.uint8, device=dev)
+    stream = _dense.stream_ptr(dev)
+    nan = float("nan")
+    errs, err, ii, status = [], 1.0, 0, _lib.ST_MAXITER
+    for ii in range(numItermax):
+        _lib.check(lib.b2ot_multi_scaling_step(code, K.data_ptr(), n, m, K.stride(0), H, a.data_ptr(), b.data_ptr(),
+                                               u.data_ptr(), v.data_ptr(), un.data_ptr(), vn.data_ptr(),
+                                               stats.data_ptr(), scratch.data_ptr(), stream),
+                   "b2ot_multi_scaling_step")
+        stats_host.copy_(stats, non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+        mu, mv, du, mup, dv, mvp, nan_u, nan_v = stats_host.tolist()
+        if nan_u:  # numpy's max propagates nan
+            mu = du = nan
+        if nan_v:
+            mv = dv = nan
+        uprev, vprev, u, v = u, v, un, vn
+        un, vn = uprev, vprev  # the next step writes over the buffers of the iteration before this one
+        if mu > tau or mv > tau:  # :1274-1288, n_hists branch: joint absorption, the scalings are kept
+            _lib.check(lib.b2ot_multi_absorb(code, n, m, H, u.data_ptr(), v.data_ptr(), alpha_r.data_ptr(),
+                                             beta_r.data_ptr(), stream), "b2ot_multi_absorb")
+            _dense.plan("log", Mr, alpha_r.to(dt), beta_r.to(dt), out=K)
+        if ii % print_period == 0:  # :1297-1301
+            err = 0.5 * (du / max(mu, mup, 1.0) + dv / max(mv, mvp, 1.0))
+            errs.append(err)
+        if err <= stopThr:  # :1316
+            status = _lib.ST_CONVERGED
+            break
+        if nan_u or nan_v:  # :1319-1325
+            u, v = uprev, vprev
+            status = _lib.ST_NUMERR
+            break
+    return Mr, alpha_r, beta_r, u, v, errs, ii, status
+
+
+def _multi_result(a, b, Mc, reg, numItermax, tau, stopThr, warmstart, verbose, print_period, log, warn):
+    """sinkhorn_stabilized for a 2-D b: the losses <M, Gamma_h> (:1342-1348) and the log dict of :1332-1341."""
+    dt, dev = Mc.dtype, Mc.device
+    with torch.cuda.device(dev):
+        Mr, alpha_r, beta_r, u, v, errs, niter, status = _stabilized_multi(
+            a, b, Mc, reg, int(numItermax), float(tau), float(stopThr), warmstart, int(print_period))
+        if status == _lib.ST_NUMERR:
+            warnings.warn("Numerical errors at iteration %d" % niter)
+        elif status == _lib.ST_MAXITER and warn:
+            warnings.warn(_NOCONV)
+        if verbose:
+            for k, e in enumerate(errs):
+                ii = k * int(print_period)
+                if ii % (int(print_period) * 20) == 0:
+                    print("{:5s}|{:12s}".format("It.", "Err") + "\n" + "-" * 19)
+                print("{:5d}|{:8e}|".format(ii, e))
+        logu = (alpha_r[:, None] + torch.log(u.double())).to(dt)  # :1333-1336
+        logv = (beta_r[:, None] + torch.log(v.double())).to(dt)
+        res = torch.stack([_dense.loss("log", Mr, Mc, logu[:, h].contiguous(), logv[:, h].contiguous())
+                           for h in range(b.shape[1])]).to(dt)
+    if not log:
+        return res
+    alpha_out, beta_out = reg * logu, reg * logv
+    return res, {"err": [torch.tensor(e, dtype=dt, device=dev) for e in errs], "n_iter": niter, "logu": logu,
+                 "logv": logv, "alpha": alpha_out, "beta": beta_out, "warmstart": (alpha_out, beta_out)}
+
+
 def sinkhorn_stabilized(a, b, M, reg, numItermax=1000, tau=1e3, stopThr=1e-9, warmstart=None, verbose=False,
                         print_period=20, log=False, warn=True, **kwargs):
-    """Drop-in for ot.bregman.sinkhorn_stabilized (ot/bregman/_sinkhorn.py:1105-1382), 1-D ``b``.
+    """Drop-in for ot.bregman.sinkhorn_stabilized (ot/bregman/_sinkhorn.py:1105-1382).
 
-    Returns the plan; with ``log=True`` also {"err", "n_iter", "logu", "logv", "alpha", "beta", "warmstart"} (:1332-1340).
+    Returns the plan (1-D ``b``) or the losses per histogram (2-D ``b``, :1342-1348); with ``log=True`` also
+    {"err", "n_iter", "logu", "logv", "alpha", "beta", "warmstart"} (:1332-1340).
     """
     if not kwargs.get("b2ot_loss", False):
         _autograd.warn_detached("sinkhorn_stabilized", M, a, b)
@@ -71,8 +161,7 @@ def sinkhorn_stabilized(a, b, M, reg, numItermax=1000, tau=1e3, stopThr=1e-9, wa
     a = _weights(a, Mc.shape[0], Mc, "a").detach()
     b = _weights(b, Mc.shape[1], Mc, "b").detach()
     if b.dim() > 1:
-        raise NotImplementedError("pot_b200: sinkhorn_stabilized with several target histograms (2-D b) is outside "
-                                  "the accelerated hot path")
+        return _multi_result(a, b, Mc, reg, numItermax, tau, stopThr, warmstart, verbose, print_period, log, warn)
     dt, dev = Mc.dtype, Mc.device
     with torch.cuda.device(dev):
         Mr, alpha_r, beta_r, u, v, errs, niter, status, _ = _stabilized_core(

@@ -17,7 +17,7 @@ if torch.cuda.is_available():
     import pot_b200 as ot
     from pot_b200 import _dense, _lib, stabilized
 from oracle import solvers_oracle as sorc
-from test_oracle_stabilized import STAB, kwargs
+from test_oracle_stabilized import STAB, STABM, kwargs
 from test_solvers_gpu import assert_plan, assert_scalar, assert_vec, npf, to_dev
 
 DEV = "cuda:0"
@@ -187,8 +187,6 @@ def test_errors():
     M = torch.rand(8, 9, device=DEV, dtype=torch.float64)
     a = torch.full((8,), 1 / 8, device=DEV, dtype=torch.float64)
     b2 = torch.full((9, 2), 1 / 9, device=DEV, dtype=torch.float64)
-    with pytest.raises(NotImplementedError):
-        ot.bregman.sinkhorn_stabilized(a, b2, M, 0.1)
     with pytest.raises(TypeError):
         ot.bregman.sinkhorn_stabilized(a.cpu().numpy(), b2[:, 0].cpu().numpy(), M.cpu().numpy(), 0.1)
     # C ABI misuse: log-domain handles cannot be switched, tau must be positive, buffers must be given
@@ -228,3 +226,159 @@ def test_odd_layouts_take_the_scalar_rebuild():
     assert_plan(G, Gr, 1e-10)
     assert_vec(lg["alpha"], lr["alpha"], 1e-10)
     check_errs(lg["err"], np.asarray(lr["err"], dtype=np.float64), True)
+
+
+# ---- several target histograms (2-D b): joint absorption / joint error on one kernel (:1230-1234, :1275-1279) ----
+@pytest.mark.parametrize("name", STABM)
+def test_stabilized_multi_golden(gstabm, name):
+    case = f"stabm_{name}"
+    M, a, b = to_dev(gstabm(case, "M"), gstabm(case, "a"), gstabm(case, "b"))
+    reg, tol = float(gstabm(case, "reg")), tol_of(name)
+    kw = fixed_count(kwargs(gstabm, case))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        res, log = ot.bregman.sinkhorn_stabilized(a, b, M, reg, log=True, **kw)
+    assert res.dtype == M.dtype and res.device == M.device and tuple(res.shape) == (b.shape[1],)
+    # fp32: the reference can hit u == uprev exactly (err = 0.0 <= stopThr = 0) and leave early; the device path sums in
+    # double, keeps the fixed count and sits on the same fixed point
+    same_count = int(gstabm(case, "n_iter")) == kw["numItermax"] - 1 or kw["stopThr"] > 0
+    assert same_count or "f32" in name
+    if same_count:
+        assert log["n_iter"] == int(gstabm(case, "n_iter"))
+        check_errs(log["err"], gstabm(case, "err"), "f64" in name)
+    assert_vec(res, gstabm(case, "losses"), tol)
+    for k in ("logu", "logv", "alpha", "beta"):
+        assert tuple(log[k].shape) == gstabm(case, k).shape
+        assert_vec(log[k], gstabm(case, k), tol)
+    assert_vec(log["warmstart"][1], gstabm(case, "beta"), tol)
+
+
+def test_stabilized_multi_warmstart_and_sinkhorn2(gstabm):
+    case = "stabm_absorb_f64"
+    M, a, b = to_dev(gstabm(case, "M"), gstabm(case, "a"), gstabm(case, "b"))
+    reg = float(gstabm(case, "reg"))
+    ws = tuple(to_dev(gstabm(case + "_warm", "ws_alpha"), gstabm(case + "_warm", "ws_beta")))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        res, log = ot.sinkhorn(a, b, M, reg, method="sinkhorn_stabilized", warmstart=ws, numItermax=40, stopThr=-1.0,
+                               log=True)
+        val = ot.sinkhorn2(a, b, M, reg, method="sinkhorn_stabilized", numItermax=200, stopThr=-1.0)
+    assert log["n_iter"] == int(gstabm(case + "_warm", "n_iter"))
+    assert_vec(res, gstabm(case + "_warm", "losses"), 1e-10)
+    assert_vec(log["alpha"], gstabm(case + "_warm", "alpha"), 1e-10)
+    assert_vec(log["beta"], gstabm(case + "_warm", "beta"), 1e-10)
+    check_errs(log["err"], gstabm(case + "_warm", "err"), True)
+    assert_vec(val, gstabm(case + "_loss", "value"), 1e-10)
+
+
+@pytest.mark.parametrize("dtype,n,m,h,reg,its,tau", [
+    (np.float64, 300, 257, 5, 0.01, 120, 10.0),
+    (np.float64, 1000, 130, 2, 0.05, 60, 1e3),
+    (np.float32, 200, 333, 6, 0.05, 80, 1e3),
+])
+def test_stabilized_multi_vs_oracle_larger(dtype, n, m, h, reg, its, tau):
+    rng = np.random.RandomState(n + m + h)
+    M = rng.rand(n, m).astype(dtype)
+    a = (rng.rand(n) + 0.1).astype(dtype)
+    a = (a / a.sum()).astype(dtype)
+    b = (rng.rand(m, h) + 0.1).astype(dtype)
+    b = (b / b.sum(0)).astype(dtype)
+    f64 = dtype == np.float64
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        rr, lr = sorc.sinkhorn_stabilized(a.astype(np.float64), b.astype(np.float64), M.astype(np.float64), reg,
+                                          numItermax=its, tau=tau, stopThr=-1.0, log=True)
+        rg, lg = ot.bregman.sinkhorn_stabilized(*to_dev(a, b, M), reg, numItermax=its, tau=tau, stopThr=-1.0, log=True)
+    tol = 1e-10 if f64 else 1e-4
+    assert lg["n_iter"] == lr["n_iter"] == its - 1
+    assert_vec(rg, rr, tol)
+    assert_vec(lg["logu"], lr["logu"], tol)
+    assert_vec(lg["logv"], lr["logv"], tol)
+    check_errs(lg["err"], np.asarray(lr["err"], dtype=np.float64), f64)
+
+
+def test_stabilized_multi_convergence_and_guard():
+    rng = np.random.RandomState(11)
+    n, m, h = 50, 60, 3
+    M = rng.rand(n, m)
+    a = np.ones(n) / n
+    b = rng.rand(m, h) + 0.1
+    b /= b.sum(0)
+    # stop rule (:1316): same iteration as the oracle, no warning
+    with warnings.catch_warnings():
+        warnings.simplefilter("error")
+        rr, lr = sorc.sinkhorn_stabilized(a, b, M, 0.1, numItermax=5000, stopThr=1e-9, print_period=3, log=True)
+        rg, lg = ot.bregman.sinkhorn_stabilized(*to_dev(a, b, M), 0.1, numItermax=5000, stopThr=1e-9, print_period=3,
+                                                log=True)
+    assert 0 < lr["n_iter"] < 4999 and lg["n_iter"] == lr["n_iter"]
+    assert_vec(rg, rr, 1e-10)
+    # not converged: the reference's warning
+    with pytest.warns(UserWarning, match="did not converge"):
+        ot.bregman.sinkhorn_stabilized(*to_dev(a, b, M), 0.1, numItermax=3, stopThr=1e-30)
+    # numerical guard (:1319-1325): K underflows to 0 -> v = inf, u = nan at the first iteration
+    with warnings.catch_warnings(record=True) as wr:
+        warnings.simplefilter("always")
+        _, lr = sorc.sinkhorn_stabilized(a, b, M * 1e6, 1e-3, numItermax=10, stopThr=0.0, log=True)
+    with warnings.catch_warnings(record=True) as wg:
+        warnings.simplefilter("always")
+        _, lg = ot.bregman.sinkhorn_stabilized(*to_dev(a, b, M * 1e6), 1e-3, numItermax=10, stopThr=0.0, log=True)
+    assert any("Numerical errors at iteration" in str(w.message) for w in wr)
+    assert [str(w.message) for w in wg if "Numerical errors" in str(w.message)] == \
+        [str(w.message) for w in wr if "Numerical errors" in str(w.message)]
+    assert lg["n_iter"] == lr["n_iter"]
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+def test_multi_step_cabi(dtype):
+    """b2ot_multi_scaling_step / b2ot_multi_absorb against fp64 torch on a ragged, strided problem (several chunks of
+    histograms, fewer rows than row blocks in one case)."""
+    lib = _lib.load()
+    gen = torch.Generator().manual_seed(3)
+    for n, m, h in [(130, 77, 6), (9, 700, 1), (515, 300, 9)]:
+        Kfull = (torch.rand(n, m + 5, generator=gen, dtype=torch.float64) + 0.05).to(dtype).to(DEV)
+        K = Kfull[:, 2:m + 2]
+        a = (torch.rand(n, generator=gen, dtype=torch.float64) + 0.1).to(dtype).to(DEV)
+        B = (torch.rand(m, h, generator=gen, dtype=torch.float64) + 0.1).to(dtype).to(DEV)
+        up = (torch.rand(n, h, generator=gen, dtype=torch.float64) + 0.1).to(dtype).to(DEV)
+        vp = (torch.rand(m, h, generator=gen, dtype=torch.float64) + 0.1).to(dtype).to(DEV)
+        un, vn = torch.full_like(up, float("nan")), torch.full_like(vp, float("nan"))
+        stats = torch.zeros(8, dtype=torch.float64, device=DEV)
+        scratch = torch.empty(lib.b2ot_multi_scratch_bytes(n, m, h), dtype=torch.uint8, device=DEV)
+        rc = lib.b2ot_multi_scaling_step(_dense.dtype_code(dtype), K.data_ptr(), n, m, K.stride(0), h, a.data_ptr(),
+                                         B.data_ptr(), up.data_ptr(), vp.data_ptr(), un.data_ptr(), vn.data_ptr(),
+                                         stats.data_ptr(), scratch.data_ptr(), _dense.stream_ptr(torch.device(DEV)))
+        assert rc == 0, lib.b2ot_last_error()
+        Kd = K.double()
+        vref = B.double() / (Kd.T @ up.double())
+        uref = a.double()[:, None] / (Kd @ vn.double())
+        rt = 1e-12 if dtype == torch.float64 else 2e-6
+        torch.testing.assert_close(vn.double(), vref, rtol=rt, atol=0)
+        torch.testing.assert_close(un.double(), uref, rtol=rt, atol=0)
+        want = torch.stack([un.abs().max(), vn.abs().max(), (un - up).abs().max(), up.abs().max(),
+                            (vn - vp).abs().max(), vp.abs().max()]).double()
+        torch.testing.assert_close(stats[:6], want, rtol=1e-15, atol=0)
+        assert stats[6].item() == 0.0 and stats[7].item() == 0.0
+        # a nan in the input shows up in the flags, the maxima skip it
+        up2 = up.clone()
+        up2[n // 2, 0] = float("nan")
+        rc = lib.b2ot_multi_scaling_step(_dense.dtype_code(dtype), K.data_ptr(), n, m, K.stride(0), h, a.data_ptr(),
+                                         B.data_ptr(), up2.data_ptr(), vp.data_ptr(), un.data_ptr(), vn.data_ptr(),
+                                         stats.data_ptr(), scratch.data_ptr(), _dense.stream_ptr(torch.device(DEV)))
+        assert rc == 0
+        assert stats[6].item() == 1.0 and stats[7].item() == 1.0 and bool(torch.isfinite(stats[:2]).all())
+        # absorption
+        al = torch.rand(n, generator=gen, dtype=torch.float64).to(DEV)
+        be = torch.rand(m, generator=gen, dtype=torch.float64).to(DEV)
+        al0, be0 = al.clone(), be.clone()
+        rc = lib.b2ot_multi_absorb(_dense.dtype_code(dtype), n, m, h, up.data_ptr(), vp.data_ptr(), al.data_ptr(),
+                                   be.data_ptr(), _dense.stream_ptr(torch.device(DEV)))
+        assert rc == 0
+        torch.testing.assert_close(al, al0 + torch.log(up.double()).amax(1), rtol=1e-14, atol=1e-15)
+        torch.testing.assert_close(be, be0 + torch.log(vp.double()).max(), rtol=1e-14, atol=1e-15)
+    # misuse
+    assert lib.b2ot_multi_scaling_step(_dense.dtype_code(dtype), K.data_ptr(), n, m, m - 1, h, a.data_ptr(),
+                                       B.data_ptr(), up.data_ptr(), vp.data_ptr(), un.data_ptr(), vn.data_ptr(),
+                                       stats.data_ptr(), scratch.data_ptr(), None) != 0
+    assert lib.b2ot_multi_scaling_step(_dense.dtype_code(dtype), K.data_ptr(), n, m, K.stride(0), h, a.data_ptr(),
+                                       B.data_ptr(), up.data_ptr(), vp.data_ptr(), up.data_ptr(), vn.data_ptr(),
+                                       stats.data_ptr(), scratch.data_ptr(), None) != 0

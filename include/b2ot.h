@@ -89,7 +89,10 @@ int b2ot_dense_create(b2ot_dense** handle, int mode, int dtype, int64_t n, int64
  * u = (a / K v)^fi_1 (inside the one fused sweep), v = (b / K^T u)^fi_2, fi = reg_m / (reg_m + reg) (:743-744);
  * K is the caller's exp(-M/reg) * c (:736-740).  Guard: K^T u == 0 or nan / inf in u, v -> previous (u, v), status
  * NUMERR (:760-772).  Error every iteration: (|u-uprev|_inf / max(|u|_inf, |uprev|_inf, 1) + same for v) / 2, stop
- * when err < stop_thr (:774-787).  b2ot_dense_init then only loads (u0, v0).  Single device only. */
+ * when err < stop_thr (:774-787).  b2ot_dense_init then only loads (u0, v0).
+ * Row-sharded runs (b2ot_dense_set_allreduce / b2ot_dense_set_comm, before or after this call): per iteration one SUM
+ * all-reduce of the m column sums + the guard flag and one MAX all-reduce of the three u statistics of the error (the
+ * error couples all rows); every rank takes the v step and the stop decision on identical data. */
 int b2ot_dense_set_unbalanced(b2ot_dense* handle, double fi_1, double fi_2);
 /* switch a KNOPP handle to the STABILIZED scaling iteration of ot.bregman.sinkhorn_stabilized
  * (ot/bregman/_sinkhorn.py:1105-1382).  The iteration itself is the balanced one (v = b / K^T u, u = a / K v, :1270-1271,

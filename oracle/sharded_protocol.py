@@ -80,3 +80,38 @@ def log_sharded(a_loc, b, M_loc, reg, numItermax, stopThr, allreduce):
             return u, v, errs, ii, 3
         v = v + (logb - np.log(cm))
     raise AssertionError("unreachable")
+
+
+def unbalanced_sharded(a_loc, b, K_loc, fi_1, fi_2, numItermax, stopThr, allreduce):
+    """Row-sharded unbalanced scaling iteration (pot_b200/csrc/dense.cu::launch_finalize_unbal; reference loop
+    ot/unbalanced/_sinkhorn.py:749-787).  K_loc: this rank's rows of exp(-M/reg) * c.  Two exchanges per iteration:
+    SUM of the m column sums + the "u not finite" flag, MAX of the three u statistics of the error.
+    Returns (u_loc, v, err list, n_iterations_done, status) with status 1 converged / 2 guard / 3 max-iter."""
+    dt = K_loc.dtype
+    m = b.shape[0]
+    u = np.ones(a_loc.shape[0], dtype=dt)
+    v = np.ones(m, dtype=dt)
+    errs = []
+    for ii in range(numItermax):
+        with np.errstate(divide="ignore", invalid="ignore"):
+            u_new = (a_loc / (K_loc @ v)) ** fi_1                      # fused sweep, phase A (local rows)
+            part = K_loc.T @ u_new                                     # fused sweep, phase B
+        buf = np.concatenate([part, np.array([0.0 if np.all(np.isfinite(u_new)) else 1.0], dtype=dt)])
+        allreduce(buf, "sum")                                          # exchange 1
+        c, uflag = buf[:m], buf[m] != 0
+        with np.errstate(invalid="ignore"):                            # inf - inf on a guarded iteration
+            stats = np.array([np.max(np.abs(u_new - u)), np.max(np.abs(u_new)), np.max(np.abs(u))], dtype=dt)
+        stats = np.where(np.isnan(stats), 0.0, stats).astype(dt)       # fmax skips nan on the device
+        allreduce(stats, "max")                                        # exchange 2
+        with np.errstate(divide="ignore", invalid="ignore"):
+            v_new = (b / c) ** fi_2
+        if uflag or np.any(c == 0) or np.any(~np.isfinite(v_new)):     # guard: previous (u, v), stop (:760-772)
+            return u, v, errs, ii, 2
+        err_u = stats[0] / max(stats[1], stats[2], 1.0)
+        err_v = np.max(np.abs(v_new - v)) / max(np.max(np.abs(v_new)), np.max(np.abs(v)), 1.0)
+        u, v = u_new, v_new
+        err = 0.5 * (err_u + err_v)
+        errs.append(float(err))
+        if err < stopThr:
+            return u, v, errs, ii, 1
+    return u, v, errs, numItermax - 1, 3

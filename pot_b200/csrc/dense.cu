@@ -756,7 +756,6 @@ extern "C" int b2ot_dense_set_unbalanced(b2ot_dense* h, double fi_1, double fi_2
   B2OT_REQUIRE(h->mode == B2OT_MODE_KNOPP, "b2ot_dense_set_unbalanced: the handle must be in the scaling domain (KNOPP)");
   B2OT_REQUIRE(h->check_every == 1, "b2ot_dense_set_unbalanced: the unbalanced error is evaluated every iteration; "
                                     "create the handle with check_every = 1 (got %d)", h->check_every);
-  B2OT_REQUIRE(h->ar == nullptr && h->comm == nullptr, "b2ot_dense_set_unbalanced: row-sharded runs are not supported");
   B2OT_REQUIRE(fi_1 > 0.0 && fi_1 <= 1.0 && fi_2 > 0.0 && fi_2 <= 1.0,
                "b2ot_dense_set_unbalanced: exponents must be in (0, 1], got %g %g", fi_1, fi_2);
   drop_graph(h);
@@ -770,7 +769,6 @@ extern "C" int b2ot_dense_set_unbalanced(b2ot_dense* h, double fi_1, double fi_2
 
 extern "C" int b2ot_dense_set_allreduce(b2ot_dense* h, b2ot_allreduce_fn fn, void* ctx) {
   B2OT_REQUIRE(h != nullptr, "b2ot_dense_set_allreduce: null handle");
-  B2OT_REQUIRE(!h->unbal, "b2ot_dense_set_allreduce: the unbalanced iteration runs on a single device");
   h->ar = fn;
   h->ar_ctx = ctx;
   return 0;
@@ -778,7 +776,6 @@ extern "C" int b2ot_dense_set_allreduce(b2ot_dense* h, b2ot_allreduce_fn fn, voi
 
 extern "C" int b2ot_dense_set_comm(b2ot_dense* h, b2ot_comm* comm) {
   B2OT_REQUIRE(h != nullptr, "b2ot_dense_set_comm: null handle");
-  B2OT_REQUIRE(!h->unbal, "b2ot_dense_set_comm: the unbalanced iteration runs on a single device");
   if (comm != nullptr) {
     const size_t need = (size_t)(h->m + 1) * esize(h->dtype);
     B2OT_REQUIRE(comm->view.slot_bytes >= need, "b2ot_dense_set_comm: exchange slots hold %llu bytes, %zu needed",
@@ -984,7 +981,10 @@ static int launch_finalize(const b2ot_dense* h, int nsrc, int init, int gate_reb
   return 0;
 }
 
-// unbalanced iteration: v = (b / K^T u)^fi2, guard, error, stop decision (single device only)
+// unbalanced iteration: v = (b / K^T u)^fi2, guard, error, stop decision.  Row-sharded runs (all-reduce hook or peer
+// communicator): the column sums + the "u not finite" flag are collapsed and SUM-all-reduced like the balanced
+// iteration's (reduce_partials_kernel), the three u statistics of the error are MAX-all-reduced (the error couples all
+// rows, ot/unbalanced/_sinkhorn.py:774-781); every rank then takes the v step and the stop decision on identical data.
 template <typename T>
 static int launch_finalize_unbal(const b2ot_dense* h, int nsrc) {
   FinUnbalParams p;
@@ -992,6 +992,22 @@ static int launch_finalize_unbal(const b2ot_dense* h, int nsrc) {
   p.src = h->partials;
   p.src_ld = h->mp;
   p.nsrc = nsrc;
+  if (h->ar != nullptr || h->comm != nullptr) {
+    const unsigned g = (unsigned)((h->m + 1 + 255) / 256);
+    reduce_partials_kernel<T><<<g, 256, 0, h->stream>>>(h->partials, h->mp, nsrc, h->cbuf, h->m, h->st, ST_RUNNING);
+    B2OT_CHECK_LAUNCH();
+    int rc = call_allreduce(h, h->cbuf, h->m + 1, B2OT_OP_SUM);
+    if (rc) return rc;
+    void* ustats = (void*)(h->blk_err + 1000);  // behind the 6 x 160 block maxima of finalize_unbal_kernel
+    unbal_ustats_kernel<T><<<1, 1024, 0, h->stream>>>(h->uring, h->n, h->st, ustats);
+    B2OT_CHECK_LAUNCH();
+    rc = call_allreduce(h, ustats, 3, B2OT_OP_MAX);
+    if (rc) return rc;
+    p.src = h->cbuf;
+    p.nsrc = 1;
+    p.ustats = ustats;
+    p.extra_flag = (const char*)h->cbuf + (size_t)h->m * sizeof(T);
+  }
   p.b = h->b;
   p.vring = h->vring;
   p.uring = h->uring;

@@ -1104,7 +1104,44 @@ struct FinUnbalParams {
   double stop_thr;
   double fi;            // fi_2
   int qsplit;           // 1: blocks of 32 columns x 8 warps over the partial rows (small m, many partial rows)
+  // row-sharded runs: `src` is the all-reduced column-sum vector; the u statistics (|u - uprev|_inf, |u|_inf,
+  // |uprev|_inf over ALL ranks' rows: 3 values of T, max-all-reduced, written by unbal_ustats_kernel) and the summed
+  // "u not finite" flags of the ranks come from memory instead of this rank's rows / state word
+  const void* ustats;
+  const void* extra_flag;
 };
+
+// Row-sharded unbalanced runs: this rank's part of the u statistics of the error, 3 values of T for a MAX all-reduce.
+// One block (n_local is a fraction of the rows; the kernel sits between two collectives anyway).
+template <typename T>
+__global__ void __launch_bounds__(1024) unbal_ustats_kernel(const void* uring, long long n, const SolveState* st,
+                                                            void* out) {
+  __shared__ double sred[3][32];
+  if (st->status != ST_RUNNING) return;
+  const int sel_u = st->sel_u;
+  const T* ucur = reinterpret_cast<const T*>(uring) + (long long)sel_u * n;
+  const T* unew = reinterpret_cast<const T*>(uring) + (long long)(sel_u ^ 1) * n;
+  double mx[3] = {0.0, 0.0, 0.0};
+  for (long long i = threadIdx.x; i < n; i += blockDim.x) {
+    const T un = unew[i], uo = ucur[i];
+    mx[0] = fmax(mx[0], (double)abs_t(un - uo));
+    mx[1] = fmax(mx[1], (double)abs_t(un));
+    mx[2] = fmax(mx[2], (double)abs_t(uo));
+  }
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    double x = mx[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x = fmax(x, __shfl_xor_sync(0xffffffffu, x, o));
+    if ((threadIdx.x & 31) == 0) sred[k][threadIdx.x >> 5] = x;
+  }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    double x = 0.0;
+    for (int w = 0; w < 32; ++w) x = fmax(x, sred[threadIdx.x][w]);
+    reinterpret_cast<T*>(out)[threadIdx.x] = (T)x;  // maxima of |T| values: exact in T
+  }
+}
 
 template <typename T>
 __global__ void __launch_bounds__(256) finalize_unbal_kernel(const FinUnbalParams p) {
@@ -1166,11 +1203,13 @@ __global__ void __launch_bounds__(256) finalize_unbal_kernel(const FinUnbalParam
       __syncthreads();
     }
   }
-  for (long long i = (long long)blockIdx.x * 256 + tid; i < p.n; i += (long long)gridDim.x * 256) {
-    const T un = unew[i], uo = ucur[i];
-    mx[0] = fmax(mx[0], (double)abs_t(un - uo));
-    mx[1] = fmax(mx[1], (double)abs_t(un));
-    mx[2] = fmax(mx[2], (double)abs_t(uo));
+  if (p.ustats == nullptr) {
+    for (long long i = (long long)blockIdx.x * 256 + tid; i < p.n; i += (long long)gridDim.x * 256) {
+      const T un = unew[i], uo = ucur[i];
+      mx[0] = fmax(mx[0], (double)abs_t(un - uo));
+      mx[1] = fmax(mx[1], (double)abs_t(un));
+      mx[2] = fmax(mx[2], (double)abs_t(uo));
+    }
   }
   if (flags) atomicOr(&sflags, flags);
 #pragma unroll
@@ -1209,7 +1248,14 @@ __global__ void __launch_bounds__(256) finalize_unbal_kernel(const FinUnbalParam
   __syncthreads();
   if (tid != 0) return;
   const int nflags = atomicOr(&st->next_flags, 0);
-  const int uflag = atomicOr(&st->uflag, 0);
+  int uflag = atomicOr(&st->uflag, 0);
+  if (p.extra_flag != nullptr && __ldcg(reinterpret_cast<const T*>(p.extra_flag)) > (T)0) uflag = 1;  // any rank
+  if (p.ustats != nullptr) {
+    const T* us = reinterpret_cast<const T*>(p.ustats);
+    sred[0][0] = (double)__ldcg(&us[0]);
+    sred[1][0] = (double)__ldcg(&us[1]);
+    sred[2][0] = (double)__ldcg(&us[2]);
+  }
   const int ii = st->iter;
   if (nflags != 0 || uflag != 0) {
     st->status = ST_NUMERR;  // previous (u, v) stay current

@@ -10,7 +10,9 @@ Every rank evaluates the stop test on identical data, so all ranks stop at the s
 any further communication.
 
 The reference has no multi-device path; the functions keep the argument meaning of
-ot.bregman.sinkhorn_knopp / sinkhorn_log (ot/bregman/_sinkhorn.py:487, :690) with *_local row blocks.
+ot.bregman.sinkhorn_knopp / sinkhorn_log (ot/bregman/_sinkhorn.py:487, :690) with *_local row blocks;
+sinkhorn_knopp_unbalanced_sharded does the same for ot.unbalanced.sinkhorn_knopp_unbalanced (two small exchanges per
+iteration: the error of the unbalanced iteration couples all rows).
 """
 
 import warnings
@@ -20,8 +22,8 @@ import torch
 from . import _dense, _lib
 from .bregman import _NOCONV, POLL_EVERY, _require_cuda_matrix, _rowmajor
 
-__all__ = ["shard_rows", "sinkhorn_knopp_sharded", "sinkhorn_log_sharded", "empirical_sinkhorn_sharded",
-           "solve_sharded", "solve_batch_sharded"]
+__all__ = ["shard_rows", "sinkhorn_knopp_sharded", "sinkhorn_log_sharded", "sinkhorn_knopp_unbalanced_sharded",
+           "empirical_sinkhorn_sharded", "solve_sharded", "solve_batch_sharded"]
 
 
 def shard_rows(n, world_size, rank):
@@ -141,6 +143,77 @@ def empirical_sinkhorn_sharded(X_s_local, X_t, reg, a_local=None, b=None, metric
     if log:
         return f, g, {"err": [torch.tensor(e, dtype=dt, device=dev) for e in errs], "niter": niter, "u": f, "v": g}
     return f, g
+
+
+def sinkhorn_knopp_unbalanced_sharded(a_local, b, M_local, reg, reg_m, reg_type="kl", warmstart=None, numItermax=1000,
+                                      stopThr=1e-6, log=False, group=None, return_plan=True, **kwargs):
+    """ot.unbalanced.sinkhorn_knopp_unbalanced (ot/unbalanced/_sinkhorn.py:565-818, 1-D b, c = a b^T or the one matrix
+    for reg_type="entropy") on a row-sharded problem.
+
+    Iteration u = (a / Kv)^fi_1 on this rank's rows, v = (b / K^T u)^fi_2 replicated (:756-759): per iteration one SUM
+    exchange of the m column sums (+ the guard flag) and one MAX exchange of the three u statistics of the error
+    (:774-781 couples all rows) - `b2ot_dense_set_unbalanced` on a handle with an exchange installed.  All ranks stop
+    at the same iteration.  Returns this rank's rows of the plan (None with return_plan=False); with log=True also
+    {"err", "logu": local rows, "logv": replicated, "cost", "total_cost"} (:785-797; the three sums and the marginal
+    KL terms are combined across ranks with two small all-reduces)."""
+    import torch.distributed as dist
+
+    from .unbalanced import POLL_EVERY as UPOLL
+    from .unbalanced import _kl_vec, _parameter_pair
+
+    M_local = _require_cuda_matrix(M_local, "M_local")
+    Mc = _rowmajor(M_local.detach())
+    n_loc, m = Mc.shape
+    dt, dev = Mc.dtype, Mc.device
+    a_local, b = a_local.detach().to(dt).contiguous(), b.detach().to(dt).contiguous()
+    if b.dim() != 1:
+        raise NotImplementedError("pot_b200: the row-sharded unbalanced solver takes one target histogram (1-D b)")
+    reg_m1, reg_m2 = _parameter_pair(reg_m)
+    fi_1 = reg_m1 / (reg_m1 + reg) if reg_m1 != float("inf") else 1  # :743-744
+    fi_2 = reg_m2 / (reg_m2 + reg) if reg_m2 != float("inf") else 1
+    entropy = reg_type.lower() == "entropy"
+    if entropy:
+        warnings.warn("If reg_type = entropy, then the matrix c is overwritten by the one matrix.")  # :729-733
+    one_n = torch.ones(n_loc, dtype=dt, device=dev)
+    one_m = torch.ones(m, dtype=dt, device=dev)
+    lib = _lib.load()
+    with torch.cuda.device(dev):
+        if entropy:
+            K = _dense.cost_transform(Mc, reg, "kexp")
+        else:  # K = exp(-M/reg) * a b^T (:736-740), row-local
+            K, _, _ = _dense.plan_value("knopp", one_n, one_m, M=Mc, reg=reg, a=a_local, b=b, kmulq=True)
+        if warmstart is None:
+            u0, v0 = one_n, one_m
+        else:
+            u0 = torch.exp(warmstart[0].detach().to(dt)).contiguous()
+            v0 = torch.exp(warmstart[1].detach().to(dt)).contiguous()
+        solver = _dense.DenseSolver("knopp", K, a_local, b, None, max_iter=int(numItermax), check_every=1,
+                                    stop_thr=float(stopThr), variant=kwargs.get("b2ot_variant", "auto"), group=group,
+                                    exchange=kwargs.get("exchange", "peer"))
+        _lib.check(lib.b2ot_dense_set_unbalanced(solver.h, float(fi_1), float(fi_2)), "b2ot_dense_set_unbalanced")
+        status, niter, _ = solver.solve(u0, v0, poll_every=UPOLL)
+        u, v, errs = solver.export()
+        solver.close()
+        if status == _lib.ST_NUMERR:
+            warnings.warn("Numerical errors at iteration %s" % niter)  # :768
+        if not log:
+            return _dense.plan("knopp", K, u, v) if return_plan else None
+        ones_a, ones_b = (one_n, one_m) if entropy else (a_local, b)
+        plan, vals, rows = _dense.plan_value("knopp", u, v, K=K, M=Mc, a=ones_a, b=ones_b, terms=("linear", "kl"),
+                                             want_rowsum=True)
+        cols = _dense.colsum(plan).double()
+        part = torch.stack([vals[0], vals[2], _kl_vec(rows, a_local).double()])
+    dist.all_reduce(part, group=group)  # <M, P>, KL(P, c), KL(P 1, a): sums over the row blocks
+    dist.all_reduce(cols, group=group)  # column marginal
+    total = part[0] + reg * part[1]
+    if reg_m1 != float("inf"):
+        total = total + reg_m1 * part[2]
+    if reg_m2 != float("inf"):
+        total = total + reg_m2 * _kl_vec(cols, b.double())
+    return (plan if return_plan else None), {
+        "err": [torch.tensor(e, dtype=dt, device=dev) for e in errs], "niter": niter,
+        "logu": torch.log(u + 1e-300), "logv": torch.log(v + 1e-300), "cost": part[0].to(dt),
+        "total_cost": total.to(dt)}
 
 
 def solve_sharded(M_local, a_local=None, b=None, reg=None, reg_type="KL", max_iter=None, tol=None, group=None,

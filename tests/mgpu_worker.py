@@ -8,7 +8,11 @@ Every rank checks its own results and exits non-zero on a mismatch.  Checks (exc
   2. row-sharded sinkhorn_knopp / sinkhorn_log against the CPU oracle (fp64 1e-10, fp32 1e-4) and against the
      single-GPU solve (same niter, same err history), converged and fixed-iteration runs, ragged row split;
   3. source-sharded empirical Sinkhorn against the oracle;
-  4. row-sharded ot.solve (plan rows, value, value_linear, potentials) against the solvers oracle.
+  4. row-sharded ot.solve (plan rows, value, value_linear, potentials) against the solvers oracle;
+  5. problem-sharded batched solver against the oracle;
+  6. row-sharded sinkhorn_knopp_unbalanced (scalar / pair / semi-relaxed reg_m, kl / entropy, fixed count, converged,
+     numerical guard) against the solvers oracle and against the single-device solve.
+MGPU_ONLY=<section number> runs one section (after the all-reduce check).
 """
 import os
 import sys
@@ -26,7 +30,82 @@ from oracle import sinkhorn_oracle as orc  # noqa: E402
 from pot_b200.comm import get_comm  # noqa: E402
 from oracle import solvers_oracle as sorc  # noqa: E402
 from pot_b200.sharded import (empirical_sinkhorn_sharded, shard_rows, sinkhorn_knopp_sharded,  # noqa: E402
-                              sinkhorn_log_sharded, solve_batch_sharded, solve_sharded)
+                              sinkhorn_knopp_unbalanced_sharded, sinkhorn_log_sharded, solve_batch_sharded,
+                              solve_sharded)
+
+
+def unbalanced_section(rank, world, dev, group, check, long_its):
+    """6. row-sharded unbalanced scaling iteration: two exchanges per iteration (column sums + guard flag: sum; the u
+    statistics of the error: max)."""
+    rng = np.random.RandomState(6)
+    n, m = 203, 160
+    xs, xt = rng.randn(n, 2), rng.randn(m, 2) + 1.0
+    M64 = orc.sqeuclidean(xs, xt)
+    M64 /= M64.max()
+    a64 = rng.rand(n) + 0.5
+    a64 /= a64.sum()
+    b64 = rng.rand(m) + 0.5
+    b64 /= 0.8 * b64.sum()  # different total masses
+    r0, r1 = shard_rows(n, world, rank)
+    cases = [(1.0, "kl"), ((0.5, 2.0), "kl"), ((float("inf"), 1.0), "kl"), (1.0, "entropy")]
+    for exchange in ("peer", "nccl"):
+        for dtype, tol in ((np.float64, 1e-10), (np.float32, 1e-4)):
+            M, a, b = M64.astype(dtype), a64.astype(dtype), b64.astype(dtype)
+            Ml, al, bd = (torch.as_tensor(M[r0:r1], device=dev), torch.as_tensor(a[r0:r1], device=dev),
+                          torch.as_tensor(b, device=dev))
+            for reg_m, rt in cases:
+                for kw in (dict(numItermax=60, stopThr=0.0),
+                           dict(numItermax=long_its, stopThr=1e-9 if dtype == np.float64 else 1e-5)):
+                    with warnings.catch_warnings():
+                        warnings.simplefilter("ignore")
+                        G, lg = sinkhorn_knopp_unbalanced_sharded(al, bd, Ml, 0.1, reg_m, reg_type=rt, log=True,
+                                                                  group=group, exchange=exchange, **kw)
+                        Gr, lr = sorc.sinkhorn_knopp_unbalanced(a, b, M, 0.1, reg_m, reg_type=rt, log=True, **kw)
+                    tag = f"unbalanced {exchange} {dtype.__name__} reg_m={reg_m} {rt} {kw['numItermax']}"
+                    if kw["stopThr"] == 0.0 or dtype == np.float64:
+                        check(len(lg["err"]) == len(lr["err"]), f"{tag}: {len(lg['err'])} vs {len(lr['err'])} iterations")
+                    Gn = G.cpu().numpy().astype(np.float64)
+                    ref = Gr[r0:r1].astype(np.float64)
+                    err = np.abs(Gn - ref) / (np.abs(ref) + 1e-6 * Gr.max())
+                    check(err.max() < tol, f"{tag}: plan rel err {err.max():.3e}")
+                    scale = max(abs(float(lr["total_cost"])), abs(float(lr["cost"])))
+                    check(abs(float(lg["cost"]) - float(lr["cost"])) <= tol * scale, f"{tag}: cost")
+                    check(abs(float(lg["total_cost"]) - float(lr["total_cost"])) <= 10 * tol * scale,
+                          f"{tag}: total_cost {float(lg['total_cost'])} vs {float(lr['total_cost'])}")
+                    k = min(len(lg["err"]), len(lr["err"]))
+                    eh = np.abs(np.array([float(e) for e in lg["err"][:k]]) - np.asarray(lr["err"][:k], dtype=np.float64))
+                    check(eh.max() <= (1e-9 if dtype == np.float64 else 1e-4), f"{tag}: err history differs by {eh.max():.2e}")
+                    v = lg["logv"].clone()
+                    v0 = v.clone()
+                    dist.broadcast(v0, 0)
+                    check(torch.equal(v, v0), f"{tag}: replicated v differs across ranks")
+            # the single-device solve of the same problem takes the same decisions (same number of iterations)
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                _, l1 = ot.unbalanced.sinkhorn_knopp_unbalanced(torch.as_tensor(a, device=dev), bd,
+                                                                torch.as_tensor(M, device=dev), 0.1, 1.0, log=True,
+                                                                numItermax=long_its, stopThr=1e-9 if dtype == np.float64 else 1e-5)
+                _, l2 = sinkhorn_knopp_unbalanced_sharded(al, bd, Ml, 0.1, 1.0, log=True, group=group, exchange=exchange,
+                                                          numItermax=long_its, stopThr=1e-9 if dtype == np.float64 else 1e-5)
+            if dtype == np.float64:
+                check(len(l1["err"]) == len(l2["err"]), f"unbalanced {exchange}: sharded {len(l2['err'])} vs single {len(l1['err'])} iterations")
+        # numerical guard: K underflows on the rows of ONE rank only -> every rank must stop at the same iteration
+        Mbad = M64.copy()
+        Mbad[:5] *= 1e7
+        with warnings.catch_warnings(record=True) as wr:
+            warnings.simplefilter("always")
+            _, lr = sorc.sinkhorn_knopp_unbalanced(a64, b64, Mbad, 0.01, 1.0, log=True, numItermax=20, stopThr=0.0)
+        with warnings.catch_warnings(record=True) as wg:
+            warnings.simplefilter("always")
+            _, lg = sinkhorn_knopp_unbalanced_sharded(torch.as_tensor(a64[r0:r1], device=dev), torch.as_tensor(b64, device=dev),
+                                                      torch.as_tensor(Mbad[r0:r1], device=dev), 0.01, 1.0, log=True,
+                                                      group=group, exchange=exchange, numItermax=20, stopThr=0.0)
+        ref_warn = [str(w.message) for w in wr if "Numerical errors" in str(w.message)]
+        got_warn = [str(w.message) for w in wg if "Numerical errors" in str(w.message)]
+        check(ref_warn == got_warn, f"unbalanced {exchange} guard: {got_warn} vs {ref_warn}")
+        check(len(lg["err"]) == len(lr["err"]), f"unbalanced {exchange} guard: err history length")
+        if rank == 0:
+            print(f"unbalanced sharded ok ({exchange}; guard warnings: {len(ref_warn)})", flush=True)
 
 
 def main():
@@ -74,6 +153,15 @@ def main():
     check(torch.equal(x, y), "peer all-reduce is not bit-identical across ranks")
     if rank == 0:
         print("peer all-reduce ok", flush=True)
+
+    only = os.environ.get("MGPU_ONLY", "")
+    if only == "6":
+        unbalanced_section(rank, world, dev, group, check, long_its)
+        dist.barrier()
+        if rank == 0:
+            print("MGPU_OK", flush=True)
+        dist.destroy_process_group()
+        return
 
     # ---- 2. dense row-sharded solves ----
     rng = np.random.RandomState(0)
@@ -207,6 +295,8 @@ def main():
                         check(ev < tol, f"batch {solver} {rt} {dtype.__name__} {key} err {ev:.2e}")
     if rank == 0:
         print("batch sharded ok", flush=True)
+
+    unbalanced_section(rank, world, dev, group, check, long_its)
 
     dist.barrier()
     if rank == 0:

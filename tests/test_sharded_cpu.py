@@ -12,6 +12,7 @@ import torch.multiprocessing as mp
 
 from oracle import sharded_protocol as proto
 from oracle import sinkhorn_oracle as orc
+from oracle import solvers_oracle as sorc
 from pot_b200.sharded import shard_rows
 
 
@@ -36,6 +37,10 @@ def _problem(n, m, dtype, reg_scale=1.0):
     return (a / a.sum()).astype(dtype), (b / b.sum()).astype(dtype), M
 
 
+UNBAL = (("fixed", 0.1, (1.0, 1.0), 25, 0.0), ("pair", 0.1, (0.5, 2.0), 2000, 1e-9),
+         ("semi", 0.1, (float("inf"), 1.0), 2000, 1e-9), ("guard", 0.01, (1.0, 1.0), 20, 0.0))
+
+
 def _worker(rank, world, port, out):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -58,6 +63,15 @@ def _worker(rank, world, port, out):
     for name, reg, its, thr in (("fixed", 0.05, 25, 0.0), ("conv", 0.1, 2000, 1e-9)):
         u, v, errs, niter, st = proto.log_sharded(a[r0:r1], b, M[r0:r1], reg, its, thr, allreduce)
         res["log_" + name] = (u, v, errs, niter, st)
+    for name, reg, reg_m, its, thr in UNBAL:
+        fi = [rm / (rm + reg) if rm != float("inf") else 1 for rm in reg_m]
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            Mc = M.copy()
+            if name == "guard":
+                Mc[:3] *= 1e7   # K underflows on rows of rank 0 only: both ranks must stop together
+            Kl = np.exp(-Mc[r0:r1] / reg) * a[r0:r1, None] * b[None, :]
+            res["unbal_" + name] = proto.unbalanced_sharded(a[r0:r1], b, Kl, fi[0], fi[1], its, thr, allreduce)
     out.put((rank, res))
     dist.barrier()
     dist.destroy_process_group()
@@ -100,3 +114,18 @@ def test_world_size_2_protocol_matches_unsharded_oracle():
             assert niter == lg["niter"], name
             np.testing.assert_allclose(v, lg["log_v"], rtol=1e-10, atol=1e-12)
         np.testing.assert_allclose(u, lg["log_u"], rtol=1e-10, atol=1e-12)
+    for name, reg, reg_m, its, thr in UNBAL:
+        Mc = M.copy()
+        if name == "guard":
+            Mc[:3] *= 1e7
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            Gr, lg = sorc.sinkhorn_knopp_unbalanced(a, b, Mc, reg, reg_m, numItermax=its, stopThr=thr, log=True)
+        u = np.concatenate([got[r]["unbal_" + name][0] for r in range(world)])
+        for r in range(world):
+            _, v, errs, niter, st = got[r]["unbal_" + name]
+            assert st == {"fixed": 3, "pair": 1, "semi": 1, "guard": 2}[name], name
+            assert len(errs) == len(lg["err"]), name
+            np.testing.assert_allclose(errs, lg["err"], rtol=1e-6, atol=1e-16)
+            np.testing.assert_allclose(np.log(v + 1e-300), lg["logv"], rtol=1e-10, atol=1e-12)
+        np.testing.assert_allclose(np.log(u + 1e-300), lg["logu"], rtol=1e-10, atol=1e-12)

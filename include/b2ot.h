@@ -113,24 +113,43 @@ int b2ot_dense_set_stabilized(b2ot_dense* handle, double tau, const void* Mr, in
                               void* beta_r);
 /* number of absorptions so far (synchronises the stream) */
 int b2ot_dense_absorb_count(b2ot_dense* handle, int* count);
-/* Several target histograms on ONE kernel matrix: the loop body of sinkhorn_stabilized with a 2-D b
- * (ot/bregman/_sinkhorn.py:1230-1234: u is n x H, v is m x H, row-major, H = b.shape[1]).
- * b2ot_multi_scaling_step enqueues one iteration (:1270-1271)
- *     v_new = B / (K^T u_prev),   u_new = a / (K v_new)           (out of place; a: n values, B: m x H)
- * and, when stats_dev is not null, the 8 doubles the host's tests need (one 64-byte read per iteration; the reference
- * syncs every iteration at :1274 too):
+/* Several target histograms on ONE kernel matrix (2-D b: u is n x H, v is m x H, row-major, H = b.shape[1]): one
+ * iteration = two passes over K whatever H.  b2ot_multi_scaling_step enqueues step `iter` (out of place; a: n values,
+ * B: m x H) and the 16 doubles of `stats_dev`:
  *     [0] max|u_new| [1] max|v_new| [2] max|u_new - u_prev| [3] max|u_prev| [4] max|v_new - v_prev| [5] max|v_prev|
- *     [6] u_new contains nan [7] v_new contains nan        (the maxima skip nan entries)
- * i.e. the absorption trigger (:1274), the error of :1297-1301 and the guard of :1319.
+ *     [6] u_new contains nan [7] v_new contains nan [8] sum (v_prev * K^T u_prev - B)^2 (KNOPP) [9] some K^T u == 0
+ *     [10] inf in u_new [11] inf in v_new        (the maxima skip nan entries)
+ *     [12] status 0 running / 1 converged / 2 numerical guard  [13] iteration at which the solve ended
+ *     [14] number of errors written to err_hist_dev  [15] last error
+ * mode B2OT_MULTI_STATS      v_new = B / (K^T u_prev), u_new = a / (K v_new); statistics only, the host decides - the loop
+ *                            body of sinkhorn_stabilized with a 2-D b (ot/bregman/_sinkhorn.py:1230-1234, :1270-1271; the
+ *                            tests at :1274, :1297-1301, :1319 read [0..7]; stats_dev may be null);
+ * mode B2OT_MULTI_KNOPP      same update = sinkhorn_knopp with a 2-D b (:626-663).  Decisions on the device: guard
+ *                            ([9] or nan / inf -> status 2 at `iter`, the iterate the step started from stays valid,
+ *                            :633-645); when (iter - 1) % check_every == 0 the error of the PREVIOUS iterate
+ *                            sqrt([8]) = || v * K^T u - b ||_F (:649-653, all histograms jointly) is recorded and
+ *                            `err < stop_thr` sets status 1 at iter - 1 (that iterate = (u_prev, v_prev) of this step);
+ * mode B2OT_MULTI_UNBALANCED u_new = (a / (K v_prev))^fi_1, v_new = (B / (K^T u_new))^fi_2 = sinkhorn_knopp_unbalanced with
+ *                            a 2-D b (ot/unbalanced/_sinkhorn.py:749-787): guard -> status 2 at `iter` (previous iterate
+ *                            valid, :760-772), else err = ([2] / max([0], [3], 1) + [4] / max([1], [5], 1)) / 2 over all
+ *                            histograms (:774-781) is recorded every step, `err < stop_thr` sets status 1 at `iter`
+ *                            (the NEW iterate is the result).
+ * Once the status is non-zero every later step is a no-op, so the host enqueues steps in chunks and polls [12]; the
+ * caller zeroes stats_dev before step 0.  fi_1 = fi_2 = 1 except for UNBALANCED.
  * scratch_dev >= b2ot_multi_scratch_bytes(n, m, H); deterministic.
- * b2ot_multi_absorb enqueues the joint absorption of :1275-1279 on alpha_r = alpha/reg (n doubles), beta_r = beta/reg
- * (m doubles): alpha_r[i] += max_h log u[i, h], beta_r[j] += max over ALL entries of log v (a scalar, as written in
- * the reference); u, v are kept (that branch has no reset).  The caller then rebuilds K = exp(Mr + alpha_r + beta_r)
- * with b2ot_dense_plan (mode LOG). */
+ * b2ot_multi_absorb enqueues the joint absorption of sinkhorn_stabilized (:1275-1279) on alpha_r = alpha/reg (n doubles),
+ * beta_r = beta/reg (m doubles): alpha_r[i] += max_h log u[i, h], beta_r[j] += max over ALL entries of log v (a scalar,
+ * as written in the reference); u, v are kept (that branch has no reset).  The caller then rebuilds
+ * K = exp(Mr + alpha_r + beta_r) with b2ot_dense_plan (mode LOG). */
+#define B2OT_MULTI_STATS 0
+#define B2OT_MULTI_KNOPP 1
+#define B2OT_MULTI_UNBALANCED 2
 size_t b2ot_multi_scratch_bytes(int64_t n, int64_t m, int64_t H);
-int b2ot_multi_scaling_step(int dtype, const void* K, int64_t n, int64_t m, int64_t ld, int64_t H, const void* a,
-                            const void* B, const void* u_prev, const void* v_prev, void* u_new, void* v_new,
-                            double* stats_dev, void* scratch_dev, void* stream);
+int b2ot_multi_scaling_step(int dtype, int mode, const void* K, int64_t n, int64_t m, int64_t ld, int64_t H,
+                            const void* a, const void* B, const void* u_prev, const void* v_prev, void* u_new,
+                            void* v_new, int iter, int check_every, double stop_thr, double fi_1, double fi_2,
+                            double* stats_dev, double* err_hist_dev, int err_capacity, void* scratch_dev,
+                            void* stream);
 int b2ot_multi_absorb(int dtype, int64_t n, int64_t m, int64_t H, const void* u, const void* v, double* alpha_r,
                       double* beta_r, void* stream);
 int b2ot_dense_set_allreduce(b2ot_dense* handle, b2ot_allreduce_fn fn, void* ctx);

@@ -250,6 +250,56 @@ def plan_value(mode, u, v, *, K=None, M=None, reg=0.0, a=None, b=None, c=None, t
     return out, vals, rows
 
 
+def multi_hist_solve(mode, K, a, B, u0, v0, max_iter, stop_thr, check_every=10, fi=(1.0, 1.0), poll_every=50):
+    """H target histograms on ONE kernel matrix, decisions on the device (b2ot_multi_scaling_step).
+
+    mode "knopp": sinkhorn_knopp with a 2-D b (ot/bregman/_sinkhorn.py:626-663: v-then-u, joint guard, joint error
+    every `check_every` iterations); "unbalanced": sinkhorn_knopp_unbalanced with a 2-D b
+    (ot/unbalanced/_sinkhorn.py:749-787: u-then-v with exponents `fi`, joint guard, joint error every iteration).
+    K (n, m), a (n,), B (m, H), u0 (n, H), v0 (m, H).  Steps are enqueued `poll_every` at a time; once the status word
+    is set the remaining steps are no-ops.  Returns (u, v, errs, niter, status) with the reference's `ii` at the end of
+    its loop as niter and status in {_lib.ST_CONVERGED, ST_NUMERR, ST_MAXITER}; (u, v) is the iterate the reference
+    returns (the previous one after a guard stop)."""
+    lib = _lib.load()
+    n, m = K.shape
+    H = B.shape[1]
+    dt, dev = K.dtype, K.device
+    knopp = mode == "knopp"
+    code = _lib.MULTI_KNOPP if knopp else _lib.MULTI_UNBALANCED
+    max_iter, check_every = int(max_iter), int(check_every)
+    us = [u0.to(dt).contiguous().clone(), torch.empty((n, H), dtype=dt, device=dev)]
+    vs = [v0.to(dt).contiguous().clone(), torch.empty((m, H), dtype=dt, device=dev)]
+    err_cap = (max_iter // check_every + 2) if knopp else max_iter + 1
+    with torch.cuda.device(dev):
+        stats = torch.zeros(16, dtype=torch.float64, device=dev)
+        err_hist = torch.zeros(err_cap, dtype=torch.float64, device=dev)
+        scratch = torch.empty(lib.b2ot_multi_scratch_bytes(n, m, H), dtype=torch.uint8, device=dev)
+        stream = stream_ptr(dev)
+        # knopp: the error of iterate k comes out of step k + 1; one probe step when the last iterate is a checked one
+        steps = max_iter + (1 if knopp and (max_iter - 1) % check_every == 0 else 0)
+        k, st = 0, None
+        while k < steps:
+            for _ in range(min(int(poll_every), steps - k)):
+                s = k & 1
+                _lib.check(lib.b2ot_multi_scaling_step(
+                    dtype_code(dt), code, K.data_ptr(), n, m, K.stride(0), H, a.data_ptr(), B.data_ptr(),
+                    us[s].data_ptr(), vs[s].data_ptr(), us[s ^ 1].data_ptr(), vs[s ^ 1].data_ptr(), k, check_every,
+                    float(stop_thr), float(fi[0]), float(fi[1]), stats.data_ptr(), err_hist.data_ptr(), err_cap,
+                    scratch.data_ptr(), stream), "b2ot_multi_scaling_step")
+                k += 1
+            st = stats.tolist()  # synchronises
+            if st[12] != 0.0:
+                break
+        errs = err_hist[:min(int(st[14]), err_cap)].tolist()
+    status, at = int(st[12]), int(st[13])
+    if status == 1:  # converged: knopp at the checked iterate (read side of step at + 1), unbalanced at the new one
+        sel = (at + 1) & 1
+        return us[sel], vs[sel], errs, at, _lib.ST_CONVERGED
+    if status == 2 and at < max_iter:  # guard in step `at`: the iterate it started from
+        return us[at & 1], vs[at & 1], errs, at, _lib.ST_NUMERR
+    return us[max_iter & 1], vs[max_iter & 1], errs, max_iter - 1, _lib.ST_MAXITER
+
+
 def colsum(P):
     """Column marginal P^T 1 (b2ot_colsum), deterministic."""
     lib = _lib.load()

@@ -18,6 +18,7 @@ VARIANT_AUTO, VARIANT_FUSED, VARIANT_SPLIT, VARIANT_RESIDENT = 0, 1, 2, 3
 OP_SUM, OP_MAX = 0, 1
 BATCH_FORCE_EXACT = 1
 VALUE_LINEAR, VALUE_ENTROPY, VALUE_KL, VALUE_KMULQ = 1, 2, 4, 8
+MULTI_STATS, MULTI_KNOPP, MULTI_UNBALANCED = 0, 1, 2
 
 ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_void_p)
 
@@ -64,9 +65,10 @@ PROTOTYPES = {
     "b2ot_colsum": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
                               C.c_void_p]),
     "b2ot_multi_scratch_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int64]),
-    "b2ot_multi_scaling_step": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p,
+    "b2ot_multi_scaling_step": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64,
                                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
-                                          C.c_void_p, C.c_void_p]),
+                                          C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_void_p,
+                                          C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "b2ot_multi_absorb": (C.c_int, [C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.c_void_p, C.c_void_p]),
     "b2ot_colsum_static": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p,

@@ -171,46 +171,67 @@ def sinkhorn_log(a, b, M, reg, numItermax=1000, stopThr=1e-9, verbose=False, log
 
 
 def _multi_hist(fn, a, b, M, reg, numItermax, stopThr, verbose, log, warn, warmstart, kwargs, attach=None):
-    """2-D ``b``: one solve per histogram, losses only (_sinkhorn.py:676-681 and :819-854).
+    """2-D ``b``: losses only (_sinkhorn.py:676-681 and :819-854).
 
-    The reference's knopp runs the histograms jointly (joint stop test on the stacked error);
-    here each histogram stops on its own error, which is identical for a fixed iteration count.
-    The transformed cost (K or -M/reg) is built once and shared by all histograms; each loss <M, plan> is reduced
-    straight from (K, u, v) by the loss kernel, no plan is materialised.
+    sinkhorn_knopp keeps all histograms on ONE Gibbs kernel with a joint guard and a joint error / stop test
+    (:626-663): `_dense.multi_hist_solve` (two passes over K per iteration whatever the number of histograms,
+    decisions on the device).  sinkhorn_log solves one histogram after the other, like the reference (:819-854).
+    Each loss <M, plan> is reduced straight from (K, u, v) by the loss kernel, no plan is materialised.
     """
     from . import _lib
 
     k_h = b.shape[1]
     is_log = fn is sinkhorn_log
-    mode = "log" if is_log else "knopp"
-    ws = warmstart if warmstart is not None else [None] * k_h
-    if warmstart is not None and not is_log:
-        ws = [(warmstart[0][:, k], warmstart[1][:, k]) for k in range(k_h)]
-    variant = kwargs.get("b2ot_variant", "auto")
     Mc = _rowmajor(M)
+    if not is_log:
+        n, m = Mc.shape
+        dt, dev = Mc.dtype, Mc.device
+        with torch.cuda.device(dev):
+            Kt = _dense.cost_transform(Mc, reg, "kexp")
+            if warmstart is None:
+                u0 = torch.full((n, k_h), 1.0 / n, dtype=dt, device=dev)  # :610-613
+                v0 = torch.full((m, k_h), 1.0 / m, dtype=dt, device=dev)
+            else:
+                u0 = torch.exp(warmstart[0].detach().to(dt)).reshape(n, -1).expand(n, k_h)
+                v0 = torch.exp(warmstart[1].detach().to(dt)).reshape(m, -1).expand(m, k_h)
+            u, v, errs, niter, status = _dense.multi_hist_solve("knopp", Kt, a, b.contiguous(), u0, v0,
+                                                                int(numItermax), float(stopThr), poll_every=POLL_EVERY)
+            if status == _lib.ST_NUMERR:
+                warnings.warn("Warning: numerical errors at iteration %d" % niter)
+            elif status == _lib.ST_MAXITER and warn:
+                warnings.warn(_NOCONV)
+            if verbose:
+                _print_table(errs, after_stop_test=True, stop_thr=stopThr)
+            losses = []
+            for k in range(k_h):
+                uk, vk = u[:, k].contiguous(), v[:, k].contiguous()
+                loss_k = _dense.loss("knopp", Kt, Mc, uk, vk).to(M.dtype)
+                losses.append(loss_k if attach is None else attach(loss_k, Kt, uk, vk, k))
+        res = torch.stack(losses)
+        if not log:
+            return res
+        return res, {"err": [torch.tensor(e, dtype=dt, device=dev) for e in errs], "niter": niter, "u": u, "v": v}
+
+    ws = warmstart if warmstart is not None else [None] * k_h
+    variant = kwargs.get("b2ot_variant", "auto")
     Kt = None
     losses, us, vs = [], [], []
     for k in range(k_h):
-        Kt, u, v, errs, niter, status = _solve_dense(mode, a, b[:, k].contiguous(), M, reg, int(numItermax),
+        Kt, u, v, errs, niter, status = _solve_dense("log", a, b[:, k].contiguous(), M, reg, int(numItermax),
                                                      float(stopThr), ws[k], variant, Kt=Kt)
-        if status == _lib.ST_NUMERR:
-            warnings.warn("Warning: numerical errors at iteration %d" % niter)
-        elif status == _lib.ST_MAXITER and warn:
+        if status == _lib.ST_MAXITER and warn:
             warnings.warn(_NOCONV)
         if verbose:
-            _print_table(errs, after_stop_test=not is_log, stop_thr=None if is_log else stopThr)
-        loss_k = _dense.loss(mode, Kt, Mc, u, v).to(M.dtype)
+            _print_table(errs, after_stop_test=False, stop_thr=None)
+        loss_k = _dense.loss("log", Kt, Mc, u, v).to(M.dtype)
         losses.append(loss_k if attach is None else attach(loss_k, Kt, u, v, k))
         us.append(u)
         vs.append(v)
     res = torch.stack(losses)
     if not log:
         return res
-    if is_log:
-        out = {"log_u": torch.stack(us, 1), "log_v": torch.stack(vs, 1)}
-        out["u"], out["v"] = torch.exp(out["log_u"]), torch.exp(out["log_v"])
-    else:
-        out = {"u": torch.stack(us, 1), "v": torch.stack(vs, 1)}
+    out = {"log_u": torch.stack(us, 1), "log_v": torch.stack(vs, 1)}
+    out["u"], out["v"] = torch.exp(out["log_u"]), torch.exp(out["log_v"])
     return res, out
 
 

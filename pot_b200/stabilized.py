@@ -83,20 +83,20 @@ def _stabilized_multi(a, b, Mc, reg, numItermax, tau, stopThr, warmstart, print_
     un, vn = torch.empty_like(u), torch.empty_like(v)
     Mr = _dense.cost_transform(Mc, reg, "negscale")
     K = _dense.plan("log", Mr, alpha_r.to(dt), beta_r.to(dt))  # get_K, :1256-1258
-    stats = torch.zeros(8, dtype=f64, device=dev)
-    stats_host = torch.zeros(8, dtype=f64).pin_memory()
+    stats = torch.zeros(16, dtype=f64, device=dev)
+    stats_host = torch.zeros(16, dtype=f64).pin_memory()
     scratch = torch.empty(lib.b2ot_multi_scratch_bytes(n, m, H), dtype=torch.uint8, device=dev)
     stream = _dense.stream_ptr(dev)
     nan = float("nan")
     errs, err, ii, status = [], 1.0, 0, _lib.ST_MAXITER
     for ii in range(numItermax):
-        _lib.check(lib.b2ot_multi_scaling_step(code, K.data_ptr(), n, m, K.stride(0), H, a.data_ptr(), b.data_ptr(),
-                                               u.data_ptr(), v.data_ptr(), un.data_ptr(), vn.data_ptr(),
-                                               stats.data_ptr(), scratch.data_ptr(), stream),
-                   "b2ot_multi_scaling_step")
+        _lib.check(lib.b2ot_multi_scaling_step(code, _lib.MULTI_STATS, K.data_ptr(), n, m, K.stride(0), H,
+                                               a.data_ptr(), b.data_ptr(), u.data_ptr(), v.data_ptr(), un.data_ptr(),
+                                               vn.data_ptr(), ii, 1, 0.0, 1.0, 1.0, stats.data_ptr(), None, 0,
+                                               scratch.data_ptr(), stream), "b2ot_multi_scaling_step")
         stats_host.copy_(stats, non_blocking=True)
         torch.cuda.current_stream(dev).synchronize()
-        mu, mv, du, mup, dv, mvp, nan_u, nan_v = stats_host.tolist()
+        mu, mv, du, mup, dv, mvp, nan_u, nan_v = stats_host[:8].tolist()
         if nan_u:  # numpy's max propagates nan
             mu = du = nan
         if nan_v:

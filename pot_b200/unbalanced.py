@@ -126,35 +126,34 @@ def _print_errs(errs):
 
 
 def _multi_hist(a, b, M, K, fi_1, fi_2, warmstart, numItermax, stopThr, verbose, log):
-    """2-D b: losses only (:789-795).  One solve per histogram; the reference iterates them jointly with a joint
-    stop test (identical for a fixed iteration count)."""
+    """2-D b: losses only (:789-795).  All histograms iterate on ONE K = exp(-M/reg) with the joint guard and the joint
+    error / stop test of the reference loop (:749-787): `_dense.multi_hist_solve` (u-then-v with the exponents fi,
+    two passes over K per iteration whatever the number of histograms, decisions on the device)."""
     dt, dev = M.dtype, M.device
+    n, m = M.shape
     n_h = b.shape[1]
-    losses, lus, lvs, errs_all = [], [], [], []
-    for k in range(n_h):
-        bk = b[:, k].contiguous()
-        if warmstart is None:
-            u0 = torch.ones(M.shape[0], dtype=dt, device=dev)
-            v0 = torch.ones(M.shape[1], dtype=dt, device=dev)
-        else:
-            w0, w1 = warmstart[0].detach().to(dt), warmstart[1].detach().to(dt)
-            u0 = torch.exp(w0[:, k] if w0.dim() > 1 and w0.shape[1] > 1 else w0.reshape(-1)).contiguous()
-            v0 = torch.exp(w1[:, k] if w1.dim() > 1 else w1).contiguous()
-        u, v, errs, niter, status = _solve_one(K, a, bk, fi_1, fi_2, u0, v0, int(numItermax), float(stopThr))
-        if status == _lib.ST_NUMERR:
-            warnings.warn("Numerical errors at iteration %s" % niter)
-        _, vals, _ = _dense.plan_value("knopp", u, v, K=K, M=M, terms=("linear",), want_plan=False)
+    if warmstart is None:
+        u0 = torch.ones((n, n_h), dtype=dt, device=dev)  # :713-715 (the (dim_a, 1) column broadcasts)
+        v0 = torch.ones((m, n_h), dtype=dt, device=dev)
+    else:
+        u0 = torch.exp(warmstart[0].detach().to(dt)).reshape(n, -1).expand(n, n_h)
+        v0 = torch.exp(warmstart[1].detach().to(dt)).reshape(m, -1).expand(m, n_h)
+    u, v, errs, niter, status = _dense.multi_hist_solve("unbalanced", K, a, b.contiguous(), u0, v0, int(numItermax),
+                                                        float(stopThr), fi=(fi_1, fi_2), poll_every=POLL_EVERY)
+    if status == _lib.ST_NUMERR:
+        warnings.warn("Numerical errors at iteration %s" % niter)
+    if log and verbose:
+        _print_errs(errs)
+    losses = []
+    for k in range(n_h):  # einsum("ik,ij,jk,ij->k", u, K, v, M)
+        _, vals, _ = _dense.plan_value("knopp", u[:, k].contiguous(), v[:, k].contiguous(), K=K, M=M, terms=("linear",),
+                                       want_plan=False)
         losses.append(vals[0].to(dt))
-        lus.append(u)
-        lvs.append(v)
-        errs_all.append(errs)
     res = torch.stack(losses)
     if not log:
         return res
-    nerr = max(len(e) for e in errs_all)
-    err = [torch.tensor(max(e[i] for e in errs_all if i < len(e)), dtype=dt, device=dev) for i in range(nerr)]
-    return res, {"err": err, "logu": torch.log(torch.stack(lus, 1) + 1e-300),
-                 "logv": torch.log(torch.stack(lvs, 1) + 1e-300)}
+    return res, {"err": [torch.tensor(e, dtype=dt, device=dev) for e in errs], "logu": torch.log(u + 1e-300),
+                 "logv": torch.log(v + 1e-300)}
 
 
 def sinkhorn_unbalanced(a, b, M, reg, reg_m, method="sinkhorn", reg_type="kl", c=None, warmstart=None,

@@ -342,11 +342,12 @@ def test_multi_step_cabi(dtype):
         up = (torch.rand(n, h, generator=gen, dtype=torch.float64) + 0.1).to(dtype).to(DEV)
         vp = (torch.rand(m, h, generator=gen, dtype=torch.float64) + 0.1).to(dtype).to(DEV)
         un, vn = torch.full_like(up, float("nan")), torch.full_like(vp, float("nan"))
-        stats = torch.zeros(8, dtype=torch.float64, device=DEV)
+        stats = torch.zeros(16, dtype=torch.float64, device=DEV)
         scratch = torch.empty(lib.b2ot_multi_scratch_bytes(n, m, h), dtype=torch.uint8, device=DEV)
-        rc = lib.b2ot_multi_scaling_step(_dense.dtype_code(dtype), K.data_ptr(), n, m, K.stride(0), h, a.data_ptr(),
-                                         B.data_ptr(), up.data_ptr(), vp.data_ptr(), un.data_ptr(), vn.data_ptr(),
-                                         stats.data_ptr(), scratch.data_ptr(), _dense.stream_ptr(torch.device(DEV)))
+        rc = lib.b2ot_multi_scaling_step(_dense.dtype_code(dtype), _lib.MULTI_STATS, K.data_ptr(), n, m, K.stride(0), h,
+                                         a.data_ptr(), B.data_ptr(), up.data_ptr(), vp.data_ptr(), un.data_ptr(),
+                                         vn.data_ptr(), 0, 1, 0.0, 1.0, 1.0, stats.data_ptr(), None, 0,
+                                         scratch.data_ptr(), _dense.stream_ptr(torch.device(DEV)))
         assert rc == 0, lib.b2ot_last_error()
         Kd = K.double()
         vref = B.double() / (Kd.T @ up.double())
@@ -361,9 +362,10 @@ def test_multi_step_cabi(dtype):
         # a nan in the input shows up in the flags, the maxima skip it
         up2 = up.clone()
         up2[n // 2, 0] = float("nan")
-        rc = lib.b2ot_multi_scaling_step(_dense.dtype_code(dtype), K.data_ptr(), n, m, K.stride(0), h, a.data_ptr(),
-                                         B.data_ptr(), up2.data_ptr(), vp.data_ptr(), un.data_ptr(), vn.data_ptr(),
-                                         stats.data_ptr(), scratch.data_ptr(), _dense.stream_ptr(torch.device(DEV)))
+        rc = lib.b2ot_multi_scaling_step(_dense.dtype_code(dtype), _lib.MULTI_STATS, K.data_ptr(), n, m, K.stride(0), h,
+                                         a.data_ptr(), B.data_ptr(), up2.data_ptr(), vp.data_ptr(), un.data_ptr(),
+                                         vn.data_ptr(), 0, 1, 0.0, 1.0, 1.0, stats.data_ptr(), None, 0,
+                                         scratch.data_ptr(), _dense.stream_ptr(torch.device(DEV)))
         assert rc == 0
         assert stats[6].item() == 1.0 and stats[7].item() == 1.0 and bool(torch.isfinite(stats[:2]).all())
         # absorption
@@ -375,10 +377,12 @@ def test_multi_step_cabi(dtype):
         assert rc == 0
         torch.testing.assert_close(al, al0 + torch.log(up.double()).amax(1), rtol=1e-14, atol=1e-15)
         torch.testing.assert_close(be, be0 + torch.log(vp.double()).max(), rtol=1e-14, atol=1e-15)
-    # misuse
-    assert lib.b2ot_multi_scaling_step(_dense.dtype_code(dtype), K.data_ptr(), n, m, m - 1, h, a.data_ptr(),
-                                       B.data_ptr(), up.data_ptr(), vp.data_ptr(), un.data_ptr(), vn.data_ptr(),
-                                       stats.data_ptr(), scratch.data_ptr(), None) != 0
-    assert lib.b2ot_multi_scaling_step(_dense.dtype_code(dtype), K.data_ptr(), n, m, K.stride(0), h, a.data_ptr(),
-                                       B.data_ptr(), up.data_ptr(), vp.data_ptr(), up.data_ptr(), vn.data_ptr(),
-                                       stats.data_ptr(), scratch.data_ptr(), None) != 0
+    # misuse: leading dimension, in-place update, solver mode without its state block
+    def call(mode, ld, u_new, st, eh, cap):
+        return lib.b2ot_multi_scaling_step(_dense.dtype_code(dtype), mode, K.data_ptr(), n, m, ld, h, a.data_ptr(),
+                                           B.data_ptr(), up.data_ptr(), vp.data_ptr(), u_new.data_ptr(), vn.data_ptr(),
+                                           0, 10, 0.0, 1.0, 1.0, st, eh, cap, scratch.data_ptr(), None)
+    assert call(_lib.MULTI_STATS, m - 1, un, stats.data_ptr(), None, 0) != 0
+    assert call(_lib.MULTI_STATS, K.stride(0), up, stats.data_ptr(), None, 0) != 0
+    assert call(_lib.MULTI_KNOPP, K.stride(0), un, stats.data_ptr(), None, 0) != 0
+    assert call(7, K.stride(0), un, stats.data_ptr(), None, 0) != 0

@@ -94,6 +94,26 @@ def test_sinkhorn2_multi_histogram_gradients(gs):
     assert float(b.grad[:, 1].abs().max()) == 0.0
 
 
+def test_sinkhorn2_joint_histograms_gradients_scaling_domain(gs):
+    """2-D b with method="sinkhorn": the histograms iterate jointly on one kernel (b2ot_multi_scaling_step); each loss
+    carries the envelope gradient of its own histogram."""
+    case = "solve_f64_40x52"
+    M0, a0, b0 = gs(case, "M"), gs(case, "a"), gs(case, "b")
+    reg, its = float(gs(case, "reg")), int(gs(case, "its"))
+    b2 = np.stack([b0[::-1].copy(), b0], 1)
+    M, a, b = dev(M0, True), dev(a0, True), dev(b2, True)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        losses = ot.sinkhorn2(a, b, M, reg, method="sinkhorn", numItermax=its, stopThr=0)
+    assert losses.shape == (2,) and losses.requires_grad
+    losses[1].backward()
+    c = f"{case}/KL_envelope"
+    close(M.grad, gs(c, "gM"), 1e-6, "dM (histogram 1)")
+    close(b.grad[:, 1], gs(c, "gb"), 1e-6, "db (histogram 1)")
+    close(a.grad, gs(c, "ga"), 1e-6, "da (histogram 1)")
+    assert float(b.grad[:, 0].abs().max()) == 0.0
+
+
 @pytest.mark.parametrize("case", CASES)
 def test_empirical_sinkhorn2_dense_gradients(case):
     """X, Y -> dist kernel (differentiable) -> sinkhorn2 envelope: against the reference's

@@ -184,3 +184,20 @@ def test_multi_step_unbalanced_order_cabi():
     un.fill_(-1.0)
     assert step(2, 10.0) == 0
     assert float(un.min()) == -1.0 and stats.tolist()[14] == 2.0
+
+
+def test_knopp_joint_warmstart_and_sinkhorn2():
+    """warmstart = log-scalings of shape (dim, n_hists) (:614); ot.sinkhorn2 with a 2-D b returns the same losses."""
+    a, b, M = problem(45, 38, 3, np.float64, seed=13)
+    rng = np.random.RandomState(4)
+    ws = (0.1 * rng.randn(45, 3), 0.1 * rng.randn(38, 3))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        rr, lr = orc.sinkhorn_knopp(a, b, M, 0.1, numItermax=25, stopThr=0.0, log=True, warmstart=ws)
+        ad, bd, Md = to_dev(a, b, M)
+        rg, lg = ot.sinkhorn(ad, bd, Md, 0.1, numItermax=25, stopThr=0.0, log=True, warmstart=tuple(to_dev(*ws)))
+        r2 = ot.sinkhorn2(ad, bd, Md, 0.1, numItermax=25, stopThr=0.0, warmstart=tuple(to_dev(*ws)))
+    assert lg["niter"] == lr["niter"] == 24
+    assert_vec(rg, rr, 1e-10)
+    assert_vec(r2, rr, 1e-10)
+    assert_vec(torch.log(lg["v"]), np.log(lr["v"]), 1e-10)

@@ -22,7 +22,7 @@ def main():
     for dt, n, m in cases:
         K = torch.rand(n, m, device=dev, dtype=dt) + 0.1
         a = torch.full((n,), 1.0 / n, device=dev, dtype=dt)
-        for H in (1, 4, 8):
+        for H in (tuple(int(x) for x in sys.argv[2].split(",")) if len(sys.argv) > 2 else (1, 4, 8)):
             B = torch.full((m, H), 1.0 / m, device=dev, dtype=dt)
             u = [torch.full((n, H), 1.0 / n, device=dev, dtype=dt) for _ in range(2)]
             v = [torch.full((m, H), 1.0 / m, device=dev, dtype=dt) for _ in range(2)]

@@ -250,6 +250,26 @@ def plan_value(mode, u, v, *, K=None, M=None, reg=0.0, a=None, b=None, c=None, t
     return out, vals, rows
 
 
+def multi_hist_steps(knopp, max_iter, check_every):
+    """Steps to enqueue for `max_iter` iterations.  KNOPP: the error of iterate k comes out of step k + 1 (its column
+    pass), so one more (probe) step runs when the last iterate is a checked one."""
+    return max_iter + (1 if knopp and (max_iter - 1) % check_every == 0 else 0)
+
+
+def multi_hist_select(status, at, max_iter):
+    """Device state (stats[12], stats[13]) -> (buffer index of the result, reference `ii`, solver status).
+
+    Step k reads buffer k & 1 and writes the other one.  Status 1 (converged at `at`): KNOPP notices it in step at + 1,
+    which READ that iterate; UNBALANCED in step `at`, which WROTE it - buffer (at + 1) & 1 either way.  Status 2 (guard
+    in step `at`): the iterate that step started from - unless it was KNOPP's probe step (at == max_iter), whose own
+    update is not part of the solve."""
+    if status == 1:
+        return (at + 1) & 1, at, _lib.ST_CONVERGED
+    if status == 2 and at < max_iter:
+        return at & 1, at, _lib.ST_NUMERR
+    return max_iter & 1, max_iter - 1, _lib.ST_MAXITER
+
+
 def multi_hist_solve(mode, K, a, B, u0, v0, max_iter, stop_thr, check_every=10, fi=(1.0, 1.0), poll_every=50):
     """H target histograms on ONE kernel matrix, decisions on the device (b2ot_multi_scaling_step).
 
@@ -275,8 +295,7 @@ def multi_hist_solve(mode, K, a, B, u0, v0, max_iter, stop_thr, check_every=10, 
         err_hist = torch.zeros(err_cap, dtype=torch.float64, device=dev)
         scratch = torch.empty(lib.b2ot_multi_scratch_bytes(n, m, H), dtype=torch.uint8, device=dev)
         stream = stream_ptr(dev)
-        # knopp: the error of iterate k comes out of step k + 1; one probe step when the last iterate is a checked one
-        steps = max_iter + (1 if knopp and (max_iter - 1) % check_every == 0 else 0)
+        steps = multi_hist_steps(knopp, max_iter, check_every)
         k, st = 0, None
         while k < steps:
             for _ in range(min(int(poll_every), steps - k)):
@@ -291,13 +310,8 @@ def multi_hist_solve(mode, K, a, B, u0, v0, max_iter, stop_thr, check_every=10, 
             if st[12] != 0.0:
                 break
         errs = err_hist[:min(int(st[14]), err_cap)].tolist()
-    status, at = int(st[12]), int(st[13])
-    if status == 1:  # converged: knopp at the checked iterate (read side of step at + 1), unbalanced at the new one
-        sel = (at + 1) & 1
-        return us[sel], vs[sel], errs, at, _lib.ST_CONVERGED
-    if status == 2 and at < max_iter:  # guard in step `at`: the iterate it started from
-        return us[at & 1], vs[at & 1], errs, at, _lib.ST_NUMERR
-    return us[max_iter & 1], vs[max_iter & 1], errs, max_iter - 1, _lib.ST_MAXITER
+    sel, niter, status = multi_hist_select(int(st[12]), int(st[13]), max_iter)
+    return us[sel], vs[sel], errs, niter, status
 
 
 def colsum(P):

@@ -201,3 +201,64 @@ def test_knopp_joint_warmstart_and_sinkhorn2():
     assert_vec(rg, rr, 1e-10)
     assert_vec(r2, rr, 1e-10)
     assert_vec(torch.log(lg["v"]), np.log(lr["v"]), 1e-10)
+
+
+# ---- the reference's own multi-histogram tests (test/test_bregman.py), on the CUDA path ----
+def _multi_b_problem(n):
+    rng = np.random.RandomState(0)
+    x = rng.randn(n, 2)
+    u = np.full(n, 1.0 / n)
+    b = rng.rand(n, 3)
+    b = b / np.sum(b, 0, keepdims=True)
+    return u, b, orc.sqeuclidean(x, x)
+
+
+@pytest.mark.parametrize("method", ["sinkhorn", "sinkhorn_stabilized", "sinkhorn_log"])
+def test_reference_sinkhorn_multi_b(method):
+    """test/test_bregman.py:128-160: the losses of a 2-D b equal the sinkhorn2 values of its columns."""
+    u, b, M = _multi_b_problem(10)
+    ud, bd, Md = to_dev(u, b, M)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        loss0, log = ot.sinkhorn(ud, bd, Md, 0.1, method=method, stopThr=1e-10, log=True)
+        loss = [float(ot.sinkhorn2(ud, bd[:, k].contiguous(), Md, 0.1, method=method, stopThr=1e-10)) for k in range(3)]
+    np.testing.assert_allclose(loss0.cpu().numpy(), loss, atol=1e-4)
+
+
+def test_reference_sinkhorn_variants_multi_b():
+    """test/test_bregman.py:422-479: the three methods agree on a 2-D b (sinkhorn and sinkhorn2), and with numpy."""
+    u, b, M = _multi_b_problem(50)
+    ud, bd, Md = to_dev(u, b, M)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        G = orc.sinkhorn(u, b, M, 1, method="sinkhorn", stopThr=1e-10)
+        res = {m: ot.sinkhorn(ud, bd, Md, 1, method=m, stopThr=1e-10).cpu().numpy()
+               for m in ("sinkhorn", "sinkhorn_log", "sinkhorn_stabilized")}
+        res2 = {m: ot.sinkhorn2(ud, bd, Md, 1, method=m, stopThr=1e-10).cpu().numpy()
+                for m in ("sinkhorn", "sinkhorn_log", "sinkhorn_stabilized")}
+    for r in (res, res2):
+        np.testing.assert_allclose(G, r["sinkhorn"], atol=1e-5)
+        np.testing.assert_allclose(G, r["sinkhorn_log"], atol=1e-5)
+        np.testing.assert_allclose(r["sinkhorn"], r["sinkhorn_stabilized"], atol=1e-5)
+
+
+def test_reference_stabilized_vs_sinkhorn_multidim():
+    """test/test_bregman.py:1346-1374: 1-D Gaussians, two target histograms, stabilized == plain."""
+    n = 100
+    x = np.arange(n, dtype=np.float64)
+
+    def gauss(m, s):
+        h = np.exp(-((x - m) ** 2) / (2 * s**2))
+        return h / h.sum()
+
+    a, b = gauss(20, 5), np.vstack((gauss(60, 8), gauss(30, 4))).T
+    M = (x[:, None] - x[None, :]) ** 2
+    M /= np.median(M)
+    ad, bd, Md = to_dev(a, np.ascontiguousarray(b), M)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        G_np, _ = orc.sinkhorn_knopp(a, b, M, 0.1, log=True)
+        G, log = ot.bregman.sinkhorn(ad, bd, Md, reg=0.1, method="sinkhorn_stabilized", log=True)
+        G2, log2 = ot.bregman.sinkhorn(ad, bd, Md, 0.1, method="sinkhorn", log=True)
+    np.testing.assert_allclose(G_np, G2.cpu().numpy())
+    np.testing.assert_allclose(G.cpu().numpy(), G2.cpu().numpy())

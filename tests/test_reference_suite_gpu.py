@@ -46,7 +46,7 @@ def dist0(n):  # ot.utils.dist0
     return orc.sqeuclidean(x, x)
 
 
-@pytest.mark.parametrize("verbose, warn", product([True, False], [True, False]))
+@pytest.mark.parametrize("verbose, warn", list(product([True, False], [True, False])))
 def test_sinkhorn(verbose, warn):  # test/test_bregman.py:21-39
     n = 100
     rng = np.random.RandomState(0)
@@ -170,7 +170,7 @@ def test_sinkhorn_variants_log():  # :482-515
     np.testing.assert_allclose(to_np(G0), to_np(Ges), atol=1e-05)
 
 
-@pytest.mark.parametrize("verbose, warn", product([True, False], [True, False]))
+@pytest.mark.parametrize("verbose, warn", list(product([True, False], [True, False])))
 def test_sinkhorn_variants_log_multib(verbose, warn):  # :518-556
     n = 50
     rng = np.random.RandomState(0)
